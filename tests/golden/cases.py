@@ -1,0 +1,65 @@
+"""Definitions of the golden cases (shared by make_golden.py, the oracle tests and the GPU tests).
+
+Each span case: a span of ``n_layers`` layers of ``shape`` receives a ``[B, prefill, h]`` chunk for
+generation ``"g0"`` and then ``n_decode`` single-token chunks at absolute positions ``prefill..``.
+Inputs are regenerated from seeds (``synthetic.make_hidden``); only outputs are stored.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Tuple
+
+
+@dataclass(frozen=True)
+class SpanCase:
+    name: str
+    shape: str
+    n_layers: int
+    batch: int
+    prefill: int
+    n_decode: int
+    window: int
+    sinks: int
+    attn_implementation: str
+    rope: str
+    norm_jitter: float = 0.1
+    first_layer: int = 0          # global index of the first layer (weights seed 1234 + idx)
+
+
+SPAN_CASES: Tuple[SpanCase, ...] = (
+    # no eviction (window larger than the stream) — the cases the GPU path is compared with
+    SpanCase("gqa_eager_literal", "test_gqa", 3, 2, 9, 11, 4096, 4, "eager", "literal"),
+    SpanCase("gqa_eager_float", "test_gqa", 3, 2, 9, 11, 4096, 4, "eager", "float"),
+    SpanCase("gqa_sdpa_float", "test_gqa", 3, 2, 9, 11, 4096, 4, "sdpa", "float"),
+    SpanCase("gqa_sdpa_literal", "test_gqa", 3, 2, 9, 11, 4096, 4, "sdpa", "literal"),
+    SpanCase("hd128_eager_float", "test_hd128", 2, 3, 37, 6, 4096, 4, "eager", "float", first_layer=2),
+    SpanCase("hd128_long_prefill", "test_hd128", 1, 1, 200, 3, 4096, 4, "eager", "float", first_layer=1),
+    # attention-sink eviction + key re-rotation (cache.py:111-133)
+    SpanCase("gqa_evict_float", "test_gqa", 3, 2, 9, 11, 12, 2, "eager", "float"),
+    SpanCase("gqa_evict_literal", "test_gqa", 3, 2, 9, 11, 12, 2, "eager", "literal"),
+    # first chunk longer than the window (D14) then trimmed at the next update
+    SpanCase("gqa_overlong_first", "test_gqa", 2, 1, 8, 4, 6, 2, "eager", "float"),
+)
+
+
+@dataclass(frozen=True)
+class GreedyCase:
+    """BASELINE.json configs[0]: tiny Llama split into 2 spans, batch 1, 128-token prompt, 32 greedy
+    steps, through the harness client (embed -> spans -> norm -> lm_head -> argmax)."""
+    name: str
+    shape: str
+    spans: Tuple[Tuple[int, int], ...]   # [start, end) global layer ranges
+    batch: int
+    prompt: int
+    n_new: int
+    rope: str
+    attn_implementation: str = "eager"
+    window: int = 4096
+    sinks: int = 4
+    vocab_stride: int = 31               # logits stored at indices 0, 31, 62, ... plus per-step top-5
+
+
+GREEDY_CASES: Tuple[GreedyCase, ...] = (
+    GreedyCase("c1_tiny_float", "tiny", ((0, 6), (6, 12)), 1, 128, 32, "float"),
+    GreedyCase("c1_tiny_literal", "tiny", ((0, 6), (6, 12)), 1, 128, 32, "literal"),
+)
