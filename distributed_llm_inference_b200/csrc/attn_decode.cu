@@ -1,0 +1,202 @@
+// Split-K flash-decode attention over the paged KV cache (q_len == 1).
+//
+// Replaces modules.py:87-105 for a decode step: repeat_kv + QK^T/sqrt(hd) + fp32 softmax + PV + head
+// merge.  HBM-bound (every cached K and V element is read exactly once per step), so the kernel is built
+// around 128-bit loads of contiguous [token][head_dim] rows and warp-shuffle reductions; the GQA group
+// (H/KV query heads) shares each loaded K/V vector, so no repeat_kv copy is ever materialised.
+//
+// grid = (splits, KV heads, batch).  A CTA owns one (sequence, kv head, context split); its 4 warps are cut
+// into token groups of hd/8 lanes, each lane holding an 8-wide slice of head_dim.  Scores, running max,
+// running sum and the output accumulator stay in fp32 (online softmax in the exp2 domain).  Per-split
+// partials (unnormalised o, m, l) go to caller-provided fp32 scratch and a small combine kernel merges
+// them.
+#include "common.cuh"
+
+#include <math.h>
+
+namespace dli {
+
+constexpr int DEC_THREADS = 128;
+constexpr int DEC_MAX_SPLITS = 32;
+
+static int decode_splits(int batch, int KV, int max_ctx) {
+  const int by_ctx = (max_ctx + 63) / 64;
+  const int by_fill = (2 * sm_count() + batch * KV - 1) / (batch * KV);
+  int s = by_fill < by_ctx ? by_fill : by_ctx;
+  if (s > DEC_MAX_SPLITS) s = DEC_MAX_SPLITS;
+  return s < 1 ? 1 : s;
+}
+
+size_t decode_attn_scratch_bytes(int batch, int H, int hd, int max_ctx) {
+  int s = (max_ctx + 63) / 64;
+  if (s > DEC_MAX_SPLITS) s = DEC_MAX_SPLITS;
+  if (s < 1) s = 1;
+  return (size_t)batch * H * s * (hd + 2) * sizeof(float);
+}
+
+template <int HD, int G>
+__global__ void __launch_bounds__(DEC_THREADS) decode_attn_kernel(const __nv_bfloat16* __restrict__ q, KvView kv,
+                                                                  float* __restrict__ scratch, int H, int KV,
+                                                                  float scale_log2) {
+  constexpr int LPT = HD / 8;                // lanes per token
+  constexpr int GPW = 32 / LPT;              // token groups per warp
+  constexpr int NG = (DEC_THREADS / 32) * GPW;  // token groups per CTA
+  constexpr int UNROLL = G <= 2 ? 4 : 2;
+
+  const int split = blockIdx.x, n_splits = gridDim.x, kvh = blockIdx.y, b = blockIdx.z;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int grp = warp * GPW + lane / LPT;   // token group of this lane
+  const int dl = (lane % LPT) * 8;           // head_dim slice [dl, dl + 8)
+
+  const int T = kv.seq_lens[b] + 1;          // the step's own token is already appended
+  int chunk = (T + n_splits - 1) / n_splits;
+  chunk = (chunk + 31) & ~31;
+  const int t_begin = split * chunk;
+  const int t_end = min(T, t_begin + chunk);
+
+  float qf[G][8], o[G][8], m[G], l[G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    const uint4 a = *reinterpret_cast<const uint4*>(q + ((long long)b * H + kvh * G + g) * HD + dl);
+    qf[g][0] = bf16_lo(a.x) * scale_log2; qf[g][1] = bf16_hi(a.x) * scale_log2;
+    qf[g][2] = bf16_lo(a.y) * scale_log2; qf[g][3] = bf16_hi(a.y) * scale_log2;
+    qf[g][4] = bf16_lo(a.z) * scale_log2; qf[g][5] = bf16_hi(a.z) * scale_log2;
+    qf[g][6] = bf16_lo(a.w) * scale_log2; qf[g][7] = bf16_hi(a.w) * scale_log2;
+    m[g] = -INFINITY;
+    l[g] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[g][j] = 0.f;
+  }
+
+  const int32_t* bt = kv.block_table + (long long)b * kv.max_pages;
+  // warp-uniform trip count: every lane takes part in the shuffles of every iteration
+  for (int t0 = t_begin; t0 < t_end; t0 += NG * UNROLL) {
+    const int t = t0 + grp;
+    uint4 kk[UNROLL], vv[UNROLL];
+    bool ok[UNROLL];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const int tt = t + u * NG;
+      ok[u] = tt < t_end;
+      kk[u] = make_uint4(0, 0, 0, 0);
+      vv[u] = make_uint4(0, 0, 0, 0);
+      if (ok[u]) {
+        const int page = bt[tt / kv.page_tokens], slot = tt % kv.page_tokens;
+        const long long off = (((long long)page * KV + kvh) * kv.page_tokens + slot) * HD + dl;
+        kk[u] = ld_nc_v4(kv.k + off);
+        vv[u] = ld_nc_v4(kv.v + off);
+      }
+    }
+    float s[UNROLL][G];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const float kf[8] = {bf16_lo(kk[u].x), bf16_hi(kk[u].x), bf16_lo(kk[u].y), bf16_hi(kk[u].y),
+                           bf16_lo(kk[u].z), bf16_hi(kk[u].z), bf16_lo(kk[u].w), bf16_hi(kk[u].w)};
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        float acc = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc = fmaf(qf[g][j], kf[j], acc);
+#pragma unroll
+        for (int off = LPT / 2; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+        s[u][g] = ok[u] ? acc : -INFINITY;
+      }
+    }
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      float mn = m[g];
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) mn = fmaxf(mn, s[u][g]);
+      const float mref = mn == -INFINITY ? 0.f : mn;  // group has seen no token yet: keep everything at zero
+      const float corr = exp2f(m[g] - mref);
+      m[g] = mn;
+      l[g] *= corr;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[g][j] *= corr;
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) {
+        const float pw = exp2f(s[u][g] - mref);
+        l[g] += pw;
+        const float vf[8] = {bf16_lo(vv[u].x), bf16_hi(vv[u].x), bf16_lo(vv[u].y), bf16_hi(vv[u].y),
+                             bf16_lo(vv[u].z), bf16_hi(vv[u].z), bf16_lo(vv[u].w), bf16_hi(vv[u].w)};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[g][j] = fmaf(pw, vf[j], o[g][j]);
+      }
+    }
+  }
+
+  // merge the NG token groups of the CTA through shared memory
+  __shared__ float sm_o[NG][G][HD];
+  __shared__ float sm_m[NG][G], sm_l[NG][G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sm_o[grp][g][dl + j] = o[g][j];
+    if ((lane % LPT) == 0) { sm_m[grp][g] = m[g]; sm_l[grp][g] = l[g]; }
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < G * HD; idx += DEC_THREADS) {
+    const int g = idx / HD, d = idx - g * HD;
+    float M = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < NG; ++i) M = fmaxf(M, sm_m[i][g]);
+    float L = 0.f, O = 0.f;
+    if (M > -INFINITY) {
+#pragma unroll
+      for (int i = 0; i < NG; ++i) {
+        const float w = exp2f(sm_m[i][g] - M);  // groups that saw no token have m = -inf -> w = 0
+        L = fmaf(sm_l[i][g], w, L);
+        O = fmaf(sm_o[i][g][d], w, O);
+      }
+    }
+    float* dst = scratch + (((long long)b * H + kvh * G + g) * n_splits + split) * (HD + 2);
+    dst[d] = O;
+    if (d == 0) { dst[HD] = M; dst[HD + 1] = L; }
+  }
+}
+
+template <int HD>
+__global__ void __launch_bounds__(HD) decode_combine_kernel(const float* __restrict__ scratch, __nv_bfloat16* __restrict__ out,
+                                                            int H, int n_splits) {
+  const int h = blockIdx.x, b = blockIdx.y, d = threadIdx.x;
+  const float* src = scratch + ((long long)b * H + h) * n_splits * (HD + 2);
+  float M = -INFINITY;
+  for (int s = 0; s < n_splits; ++s) M = fmaxf(M, src[s * (HD + 2) + HD]);
+  float L = 0.f, O = 0.f;
+  for (int s = 0; s < n_splits; ++s) {
+    const float w = exp2f(src[s * (HD + 2) + HD] - M);
+    L = fmaf(src[s * (HD + 2) + HD + 1], w, L);
+    O = fmaf(src[s * (HD + 2) + d], w, O);
+  }
+  out[((long long)b * H + h) * HD + d] = __float2bfloat16_rn(O / L);
+}
+
+template <int HD, int G>
+static int launch_dec(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV, int splits,
+                      float* scratch, cudaStream_t st) {
+  const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
+  decode_attn_kernel<HD, G><<<dim3(splits, KV, batch), DEC_THREADS, 0, st>>>(q, kv, scratch, H, KV, scale_log2);
+  DLI_CHECK_LAUNCH("decode_attn_kernel");
+  decode_combine_kernel<HD><<<dim3(H, batch), HD, 0, st>>>(scratch, out, H, splits);
+  DLI_CHECK_LAUNCH("decode_combine_kernel");
+  return DLI_OK;
+}
+
+int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV, int hd,
+                            float* scratch, size_t scratch_bytes, cudaStream_t st) {
+  DLI_REQUIRE(q && out && scratch, "dli_decode_attention: null pointer");
+  DLI_REQUIRE(batch > 0 && H > 0 && KV > 0 && H % KV == 0, "dli_decode_attention: batch=%d H=%d KV=%d", batch, H, KV);
+  const int G = H / KV;
+  const int splits = decode_splits(batch, KV, kv.max_ctx);
+  const size_t need = (size_t)batch * H * splits * (hd + 2) * sizeof(float);
+  if (scratch_bytes < need)
+    return fail(DLI_ERR_WORKSPACE, "dli_decode_attention: scratch %zu bytes < %zu needed", scratch_bytes, need);
+#define DLI_DEC_CASE(HD_, G_) \
+  if (hd == HD_ && G == G_) return launch_dec<HD_, G_>(q, out, kv, batch, H, KV, splits, scratch, st)
+  DLI_DEC_CASE(128, 1); DLI_DEC_CASE(128, 2); DLI_DEC_CASE(128, 4); DLI_DEC_CASE(128, 8);
+  DLI_DEC_CASE(64, 1); DLI_DEC_CASE(64, 2); DLI_DEC_CASE(64, 4); DLI_DEC_CASE(64, 8);
+#undef DLI_DEC_CASE
+  return fail(DLI_ERR_UNSUPPORTED, "dli_decode_attention: head_dim %d with GQA group %d is not instantiated", hd, G);
+}
+
+}  // namespace dli

@@ -1,0 +1,233 @@
+// Prefill attention over the paged KV cache (q_len >= 1, optional cached past, causal flag).
+//
+// Replaces modules.py:87-105 for a multi-token chunk: softmax(Q K^T / sqrt(hd) [+ causal mask]) V with GQA by
+// indexing.  The [B, H, L, T] score tensor the reference materialises is never formed: flash-attention
+// tiling with fp32 online softmax (exp2 domain).  Scores and the running max/sum stay in fp32; P is
+// rounded to bf16 only as the tensor-core operand of P.V (the one rounding shared with modules.py:96).
+// `causal` == 0 reproduces the reference's default sdpa configuration, which adds no mask at all
+// (model.py:94-101 + modules.py:92-94); `causal` == 1 the eager mask of model.py:103-127.
+//
+// Round-1 implementation: warp-level mma.sync (m16n8k16, bf16 -> fp32) with ldmatrix-fed fragments; one
+// CTA = 64 queries of one head (4 warps x 16 rows), K/V tiles of 64 keys gathered from pages with
+// cp.async into XOR-swizzled shared memory.  Attention is <= 7 % of prefill FLOPs at 8k context
+// (SURVEY 8d); the tcgen05 version is later work.
+#include "common.cuh"
+
+#include <math.h>
+
+namespace dli {
+
+constexpr int PF_THREADS = 128;
+constexpr int PF_BM = 64;
+constexpr int PF_BN = 64;
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+               : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+               : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// byte offset of 16-byte chunk `c` of row `r` in a [rows][HD] bf16 tile, XOR-swizzled against bank conflicts
+template <int HD>
+__device__ __forceinline__ uint32_t swz(int r, int c) {
+  return (uint32_t)(r * HD * 2 + ((c ^ (r & 7)) << 4));
+}
+
+template <int HD>
+__global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const __nv_bfloat16* __restrict__ q,
+                                                                  __nv_bfloat16* __restrict__ out, KvView kv, int q_len,
+                                                                  int H, int KV, int causal, float scale_log2) {
+  constexpr int CPR = HD / 8;  // 16-byte chunks per row
+  extern __shared__ __align__(128) uint8_t pf_smem[];
+  const uint32_t sQ = smem_u32(pf_smem), sK = sQ + PF_BM * HD * 2, sV = sK + PF_BN * HD * 2;
+
+  const int m0 = blockIdx.x * PF_BM, h = blockIdx.y, b = blockIdx.z;
+  const int kvh = h / (H / KV);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t4 = lane & 3;
+  const int past = kv.seq_lens[b];
+  const int T = past + q_len;
+  const int32_t* bt = kv.block_table + (long long)b * kv.max_pages;
+
+  // ---- Q tile -> smem (rows beyond q_len are zero) ----
+  for (int i = threadIdx.x; i < PF_BM * CPR; i += PF_THREADS) {
+    const int r = i / CPR, c = i - r * CPR;
+    const int qi = m0 + r;
+    const bool ok = qi < q_len;
+    const __nv_bfloat16* src = q + (((long long)b * q_len + (ok ? qi : 0)) * H + h) * HD + c * 8;
+    cp_async16(sQ + swz<HD>(r, c), src, ok ? 16 : 0);
+  }
+  cp_async_wait_all();
+  __syncthreads();
+
+  // Q fragments of this warp's 16 rows, all k-slices
+  uint32_t qa[HD / 16][4];
+#pragma unroll
+  for (int ks = 0; ks < HD / 16; ++ks) {
+    const int r = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+    const int c = ks * 2 + (lane >> 4);
+    ldsm_x4(sQ + swz<HD>(r, c), qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3]);
+  }
+
+  float o[HD / 8][4];
+#pragma unroll
+  for (int n = 0; n < HD / 8; ++n) o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f;
+  float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
+
+  const int pos0 = past + m0 + warp * 16 + g;  // absolute position of this thread's first row (second: +8)
+  int kv_end = T;
+  if (causal) kv_end = min(T, past + m0 + PF_BM);
+  const int n_tiles = (kv_end + PF_BN - 1) / PF_BN;
+
+  for (int tile = 0; tile < n_tiles; ++tile) {
+    const int j0 = tile * PF_BN;
+    __syncthreads();  // previous tile's K/V fully consumed
+    for (int i = threadIdx.x; i < PF_BN * CPR; i += PF_THREADS) {
+      const int r = i / CPR, c = i - r * CPR;
+      const int j = j0 + r;
+      const bool ok = j < T;
+      long long off = 0;
+      if (ok) {
+        const int page = bt[j / kv.page_tokens], slot = j % kv.page_tokens;
+        off = (((long long)page * KV + kvh) * kv.page_tokens + slot) * HD + c * 8;
+      }
+      cp_async16(sK + swz<HD>(r, c), kv.k + off, ok ? 16 : 0);
+      cp_async16(sV + swz<HD>(r, c), kv.v + off, ok ? 16 : 0);
+    }
+    cp_async_wait_all();
+    __syncthreads();
+
+    // ---- S = Q K^T (16 x 64 per warp) ----
+    float s[PF_BN / 8][4];
+#pragma unroll
+    for (int n = 0; n < PF_BN / 8; ++n) s[n][0] = s[n][1] = s[n][2] = s[n][3] = 0.f;
+#pragma unroll
+    for (int ks = 0; ks < HD / 16; ++ks) {
+#pragma unroll
+      for (int np = 0; np < PF_BN / 16; ++np) {
+        uint32_t b0, b1, b2, b3;
+        const int r = np * 16 + (lane & 7) + (lane >> 4) * 8;
+        const int c = ks * 2 + ((lane >> 3) & 1);
+        ldsm_x4(sK + swz<HD>(r, c), b0, b1, b2, b3);
+        mma_bf16_16816(s[2 * np], qa[ks], b0, b1);
+        mma_bf16_16816(s[2 * np + 1], qa[ks], b2, b3);
+      }
+    }
+
+    // ---- mask + online softmax ----
+    float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+    for (int n = 0; n < PF_BN / 8; ++n) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int j = j0 + n * 8 + 2 * t4 + (e & 1);
+        const int pos = pos0 + (e >> 1) * 8;
+        const bool ok = j < T && (!causal || j <= pos);
+        s[n][e] = ok ? s[n][e] * scale_log2 : -INFINITY;
+        mx[e >> 1] = fmaxf(mx[e >> 1], s[n][e]);
+      }
+    }
+    float corr[2], mref[2];
+#pragma unroll
+    for (int r2 = 0; r2 < 2; ++r2) {
+      mx[r2] = fmaxf(mx[r2], __shfl_xor_sync(0xffffffffu, mx[r2], 1));
+      mx[r2] = fmaxf(mx[r2], __shfl_xor_sync(0xffffffffu, mx[r2], 2));
+      const float mn = fmaxf(mrow[r2], mx[r2]);
+      mref[r2] = mn == -INFINITY ? 0.f : mn;
+      corr[r2] = exp2f(mrow[r2] - mref[r2]);
+      mrow[r2] = mn;
+      lrow[r2] *= corr[r2];
+    }
+#pragma unroll
+    for (int n = 0; n < HD / 8; ++n) {
+      o[n][0] *= corr[0]; o[n][1] *= corr[0];
+      o[n][2] *= corr[1]; o[n][3] *= corr[1];
+    }
+    uint32_t pa[PF_BN / 16][4];
+#pragma unroll
+    for (int n = 0; n < PF_BN / 8; ++n) {
+      const float p0 = exp2f(s[n][0] - mref[0]), p1 = exp2f(s[n][1] - mref[0]);
+      const float p2 = exp2f(s[n][2] - mref[1]), p3 = exp2f(s[n][3] - mref[1]);
+      lrow[0] += p0 + p1;
+      lrow[1] += p2 + p3;
+      // C layout of two adjacent 8-key tiles == A layout of one 16-key slice
+      pa[n >> 1][(n & 1) * 2 + 0] = pack_bf16(p0, p1);
+      pa[n >> 1][(n & 1) * 2 + 1] = pack_bf16(p2, p3);
+    }
+
+    // ---- O += P V ----
+#pragma unroll
+    for (int ks = 0; ks < PF_BN / 16; ++ks) {
+#pragma unroll
+      for (int np = 0; np < HD / 16; ++np) {
+        uint32_t b0, b1, b2, b3;
+        const int r = ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+        const int c = np * 2 + (lane >> 4);
+        ldsm_x4_trans(sV + swz<HD>(r, c), b0, b1, b2, b3);
+        mma_bf16_16816(o[2 * np], pa[ks], b0, b1);
+        mma_bf16_16816(o[2 * np + 1], pa[ks], b2, b3);
+      }
+    }
+  }
+
+  // ---- finalize: row sums across the quad, normalise, store ----
+#pragma unroll
+  for (int r2 = 0; r2 < 2; ++r2) {
+    lrow[r2] += __shfl_xor_sync(0xffffffffu, lrow[r2], 1);
+    lrow[r2] += __shfl_xor_sync(0xffffffffu, lrow[r2], 2);
+  }
+#pragma unroll
+  for (int r2 = 0; r2 < 2; ++r2) {
+    const int qi = m0 + warp * 16 + g + r2 * 8;
+    if (qi < q_len) {
+      const float inv = lrow[r2] > 0.f ? 1.f / lrow[r2] : 0.f;
+      __nv_bfloat16* dst = out + (((long long)b * q_len + qi) * H + h) * HD + 2 * t4;
+#pragma unroll
+      for (int n = 0; n < HD / 8; ++n)
+        *reinterpret_cast<uint32_t*>(dst + n * 8) = pack_bf16(o[n][r2 * 2] * inv, o[n][r2 * 2 + 1] * inv);
+    }
+  }
+}
+
+template <int HD>
+static int launch_pf(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H, int KV,
+                     bool causal, cudaStream_t st) {
+  const size_t smem = (size_t)(PF_BM + 2 * PF_BN) * HD * 2;
+  static bool configured = false;
+  if (!configured) {
+    DLI_CUDA_OK(cudaFuncSetAttribute(prefill_attn_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
+  dim3 grid((q_len + PF_BM - 1) / PF_BM, H, batch);
+  prefill_attn_kernel<HD><<<grid, PF_THREADS, smem, st>>>(q, out, kv, q_len, H, KV, causal ? 1 : 0, scale_log2);
+  DLI_CHECK_LAUNCH("prefill_attn_kernel");
+  return DLI_OK;
+}
+
+int launch_prefill_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H,
+                             int KV, int hd, bool causal, cudaStream_t st) {
+  DLI_REQUIRE(q && out, "dli_prefill_attention: null pointer");
+  DLI_REQUIRE(batch > 0 && q_len > 0 && H > 0 && KV > 0 && H % KV == 0, "dli_prefill_attention: batch=%d q_len=%d H=%d KV=%d",
+              batch, q_len, H, KV);
+  if (hd == 128) return launch_pf<128>(q, out, kv, batch, q_len, H, KV, causal, st);
+  if (hd == 64) return launch_pf<64>(q, out, kv, batch, q_len, H, KV, causal, st);
+  return fail(DLI_ERR_UNSUPPORTED, "dli_prefill_attention: head_dim %d is not instantiated (64, 128)", hd);
+}
+
+}  // namespace dli

@@ -1,0 +1,112 @@
+// Shared host/device helpers for libdli_b200 (sm_100a only).
+#pragma once
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/dli_b200.h"
+
+namespace dli {
+
+// ---- host-side error plumbing (thread-local message, never throws across the ABI) -----------------
+void set_error(const char* fmt, ...);
+int fail(int code, const char* fmt, ...);
+void count_launch(int n = 1);
+void reset_launch_count();
+
+#define DLI_CUDA_OK(expr)                                                                      \
+  do {                                                                                         \
+    cudaError_t _e = (expr);                                                                   \
+    if (_e != cudaSuccess)                                                                     \
+      return ::dli::fail(DLI_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                         __FILE__, __LINE__);                                                  \
+  } while (0)
+
+#define DLI_CHECK_LAUNCH(name)                                                                 \
+  do {                                                                                         \
+    cudaError_t _e = cudaGetLastError();                                                       \
+    if (_e != cudaSuccess)                                                                     \
+      return ::dli::fail(DLI_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(_e)); \
+    ::dli::count_launch();                                                                     \
+  } while (0)
+
+#define DLI_REQUIRE(cond, ...)                                   \
+  do {                                                           \
+    if (!(cond)) return ::dli::fail(DLI_ERR_ARG, __VA_ARGS__);   \
+  } while (0)
+
+int sm_count();  // SMs of the current device (cached)
+
+// ---- internal launchers shared between the op-level ABI and the span runner ------------------------
+struct KvView {
+  __nv_bfloat16* k;  // this layer's K pool [n_pages][KV][page_tokens][hd]
+  __nv_bfloat16* v;
+  const int32_t* block_table;
+  const int32_t* seq_lens;
+  int page_tokens, n_pages, max_pages, max_ctx;
+};
+int kv_view(const dli_kv_desc* kv, int layer, KvView* out);
+
+// ---- GEMM planning / launch (gemm_tcgen05.cu) --------------------------------------------------------
+struct GemmPlan {
+  bool swap;          // weights are the 128-row MMA operand (decode); else tokens are
+  int bn;             // MMA N
+  int a_box_rows, b_box_rows;  // TMA box rows of the A-role / B-role operand
+  int k_blocks, kb_per_split, splits, stages;
+  int grid_x, grid_y;
+};
+GemmPlan plan_gemm(int m, int n, int k, int epilogue);
+int make_tmap_bf16(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld, int box_rows);
+int launch_gemm_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const CUtensorMap& tmap_w, void* out,
+                        long long ldo, int m, int n, int epilogue, cudaStream_t st);
+int launch_gemm(const void* x, long long ldx, const void* w, void* out, long long ldo, int m, int n, int k,
+                int epilogue, cudaStream_t st);
+
+// ---- other launchers ----------------------------------------------------------------------------------
+int launch_rmsnorm(const void* x, bool x_is_f32, const __nv_bfloat16* w, __nv_bfloat16* y, float* resid_out,
+                   __nv_bfloat16* copy_out, int rows, int h, float eps, float pre_scale, cudaStream_t st);
+int launch_rope_kv_append(float* qkv, bool zero_after, const float* cos, const float* sin, __nv_bfloat16* q_out,
+                          const KvView& kv, int batch, int q_len, int H, int KV, int hd, cudaStream_t st);
+int launch_silu_mul(float* gu, __nv_bfloat16* act, int m, int n, bool zero_after, cudaStream_t st);
+int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st);
+size_t decode_attn_scratch_bytes(int batch, int H, int hd, int max_ctx);
+int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV,
+                            int hd, float* scratch, size_t scratch_bytes, cudaStream_t st);
+int launch_prefill_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len,
+                             int H, int KV, int hd, bool causal, cudaStream_t st);
+
+// ---- device helpers -------------------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
+// 128-bit streaming load that does not allocate in L1 (data read once: weights, KV pages)
+__device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+#endif
+
+}  // namespace dli

@@ -1,0 +1,472 @@
+// tcgen05 / TMEM GEMM fed by TMA:   out[m, n] (+)= sum_k x[m, k] * w[n, k]      (bf16 in, fp32 accumulate)
+//
+// Replaces the seven nn.Linear calls of a reference decoder layer (q/k/v_proj modules.py:61-63, o_proj
+// modules.py:112, LlamaMLP gate/up/down modules.py:181) together with the residual adds of
+// modules.py:173,182 and the silu(gate)*up product, which live in the epilogue.
+//
+// One kernel, two operand assignments:
+//   * token-major (prefill, m > 128):  A = 128 tokens x K,  B = BN features x K   -> D[token lane, feature col]
+//   * swap-AB     (decode,  m <= 128): A = 128 weight rows x K, B = BN (>= batch) tokens x K
+//                                                                            -> D[feature lane, token col]
+//     so that the weight matrix is the 128-row MMA operand and streams through the tensor core at HBM
+//     rate; split-K over gridDim.z fills all SMs and the fp32 partial sums meet in L2 (red.add).
+// Both operands are K-major in global memory (nn.Linear stores [out, in]; activations are [tokens, in]),
+// so neither needs a transpose: TMA lands 64-element (128-byte) K slices with the 128B swizzle and the
+// UMMA shared-memory descriptors consume them directly.
+//
+// Warp roles (192 threads): warp 0 = TMA producer (one lane), warp 1 = TMEM allocator + MMA issuer (one
+// lane), warps 2-5 = epilogue (warp w reads TMEM lanes 32*(w%4) .. +31, as the hardware requires).
+// Pipelines: smem full/empty mbarrier ring (TMA <-> MMA), one tmem_full mbarrier (MMA -> epilogue).
+#include "common.cuh"
+
+namespace dli {
+
+constexpr int BM = 128;  // A-tile rows = UMMA_M = TMEM lanes
+constexpr int BK = 64;   // bf16 per k-block: one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int A_TILE_BYTES = BM * BK * 2;
+constexpr int GEMM_THREADS = 192;
+constexpr int MAX_STAGES = 8;
+
+struct GemmParams {
+  void* out;
+  long long ldo;
+  int m_tokens, n_features;
+  int k_blocks, kb_per_split;
+  int stages;
+  int up_row_offset;  // SILU epilogue: row of w where up_proj starts (= n_features)
+};
+
+// ---- PTX wrappers ------------------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  uint32_t spins = 0;
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) break;
+    if (++spins > 4000000u) {  // a lost arrival must surface as a launch failure, never as a hung GPU
+      printf("dli gemm: mbarrier wait timed out (block %d,%d,%d thread %d)\n", blockIdx.x, blockIdx.y,
+             blockIdx.z, threadIdx.x);
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major, 128B-swizzled operand tile: rows at a 128-byte pitch, 8-row groups 1024 bytes apart.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);  // start address
+  d |= (uint64_t)1 << 16;                      // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;            // stride byte offset: next 8-row group
+  d |= (uint64_t)1 << 46;                      // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                      // SWIZZLE_128B
+  return d;
+}
+// kind::f16 instruction descriptor: D = fp32, A = B = bf16, both K-major, M = 128, N = bn.
+__host__ __device__ constexpr uint32_t umma_idesc_bf16(int bn) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+
+__device__ __forceinline__ float silu(float x) { return x / (1.0f + __expf(-x)); }
+
+// ---- kernel -------------------------------------------------------------------------------------------
+template <int BN, int EPI, bool SWAP>
+__global__ void __launch_bounds__(GEMM_THREADS, SWAP ? 2 : 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                    const GemmParams p) {
+  constexpr int B_TILE_BYTES = BN * BK * 2;
+  constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
+  constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
+  static_assert(!(SWAP && EPI == DLI_EPI_SILU_MUL_BF16), "SiLU epilogue is token-major only");
+
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t bars[2 * MAX_STAGES + 1];
+  __shared__ uint32_t tmem_base_slot;
+
+  const uint32_t tiles = (smem_u32(smem_raw) + 1023u) & ~1023u;  // 128B swizzle atoms need 1024-byte alignment
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int stages = p.stages;
+  const uint32_t full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[MAX_STAGES]);
+  const uint32_t tmem_full = smem_u32(&bars[2 * MAX_STAGES]);
+
+  const int kb0 = blockIdx.z * p.kb_per_split;
+  const int kb1 = min(kb0 + p.kb_per_split, p.k_blocks);
+  const int a_row0 = blockIdx.x * BM;
+  const int b_row0 = blockIdx.y * (EPI == DLI_EPI_SILU_MUL_BF16 ? BN / 2 : BN);
+
+  if (threadIdx.x == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, 1);
+    }
+    mbar_init(tmem_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {  // whole warp: allocate the accumulator columns
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)),
+                 "r"((uint32_t)TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_d = tmem_base_slot;
+
+  if (kb1 > kb0) {
+    if (warp == 0) {
+      if (lane == 0) {  // ===== TMA producer =====
+        int s = 0;
+        uint32_t ph = 0;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(empty0 + 8 * s, ph ^ 1);
+          const uint32_t a_dst = tiles + s * STAGE_BYTES, b_dst = a_dst + A_TILE_BYTES;
+          mbar_expect_tx(full0 + 8 * s, STAGE_BYTES);
+          tma_load_2d(a_dst, &tma_a, full0 + 8 * s, kb * BK, a_row0);
+          if (EPI == DLI_EPI_SILU_MUL_BF16) {  // gate rows then up rows of the same features
+            tma_load_2d(b_dst, &tma_b, full0 + 8 * s, kb * BK, b_row0);
+            tma_load_2d(b_dst + B_TILE_BYTES / 2, &tma_b, full0 + 8 * s, kb * BK, p.up_row_offset + b_row0);
+          } else {
+            tma_load_2d(b_dst, &tma_b, full0 + 8 * s, kb * BK, b_row0);
+          }
+          if (++s == stages) { s = 0; ph ^= 1; }
+        }
+      }
+    } else if (warp == 1) {
+      if (lane == 0) {  // ===== MMA issuer =====
+        constexpr uint32_t idesc = umma_idesc_bf16(BN);
+        int s = 0;
+        uint32_t ph = 0;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(full0 + 8 * s, ph);
+          tcgen05_fence_after();
+          const uint32_t a_src = tiles + s * STAGE_BYTES;
+          const uint64_t adesc = umma_desc_sw128(a_src), bdesc = umma_desc_sw128(a_src + A_TILE_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            // advancing 16 bf16 (32 bytes) along K inside the swizzle atom: +2 in the (addr >> 4) field
+            umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(empty0 + 8 * s);  // frees the smem slot once these MMAs have read it
+          if (++s == stages) { s = 0; ph ^= 1; }
+        }
+        umma_commit(tmem_full);  // accumulator complete
+      }
+    } else {  // ===== epilogue: TMEM -> registers -> global =====
+      mbar_wait(tmem_full, 0);
+      tcgen05_fence_after();
+      const int q = warp & 3;  // TMEM lane quarter this warp may read
+      const int arow = a_row0 + q * 32 + lane;
+      const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16);
+      uint32_t v[16];
+      if (SWAP) {
+        // lane = feature, column = token
+        const bool f_ok = arow < p.n_features;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 16) {
+          tmem_ld16(taddr + c0, v);
+          tmem_ld_wait();
+          if (f_ok) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int tok = b_row0 + c0 + j;
+              if (tok < p.m_tokens) {
+                const float acc = __uint_as_float(v[j]);
+                if (EPI == DLI_EPI_ADD_F32) {
+                  float* o = (float*)p.out + (long long)tok * p.ldo + arow;
+                  asm volatile("red.global.add.f32 [%0], %1;" ::"l"(o), "f"(acc) : "memory");
+                } else if (EPI == DLI_EPI_STORE_F32) {
+                  ((float*)p.out)[(long long)tok * p.ldo + arow] = acc;
+                } else {
+                  ((__nv_bfloat16*)p.out)[(long long)tok * p.ldo + arow] = __float2bfloat16_rn(acc);
+                }
+              }
+            }
+          }
+        }
+      } else if (EPI == DLI_EPI_SILU_MUL_BF16) {
+        // lane = token; columns [0, BN/2) = gate, [BN/2, BN) = up of features b_row0 ..
+        const bool t_ok = arow < p.m_tokens;
+        uint32_t u[16];
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN / 2; c0 += 16) {
+          tmem_ld16(taddr + c0, v);
+          tmem_ld16(taddr + BN / 2 + c0, u);
+          tmem_ld_wait();
+          const int f0 = b_row0 + c0;
+          if (t_ok && f0 < p.n_features) {
+            __nv_bfloat16* o = (__nv_bfloat16*)p.out + (long long)arow * p.ldo + f0;
+            if (f0 + 16 <= p.n_features) {
+              uint32_t w[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                w[j] = pack_bf16(silu(__uint_as_float(v[2 * j])) * __uint_as_float(u[2 * j]),
+                                 silu(__uint_as_float(v[2 * j + 1])) * __uint_as_float(u[2 * j + 1]));
+              *reinterpret_cast<uint4*>(o) = make_uint4(w[0], w[1], w[2], w[3]);
+              *reinterpret_cast<uint4*>(o + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+            } else {
+              for (int j = 0; j < 16 && f0 + j < p.n_features; ++j)
+                o[j] = __float2bfloat16_rn(silu(__uint_as_float(v[j])) * __uint_as_float(u[j]));
+            }
+          }
+        }
+      } else {
+        // lane = token, column = feature
+        const bool t_ok = arow < p.m_tokens;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 16) {
+          tmem_ld16(taddr + c0, v);
+          tmem_ld_wait();
+          const int f0 = b_row0 + c0;
+          if (t_ok && f0 < p.n_features) {
+            const bool full = f0 + 16 <= p.n_features;
+            if (EPI == DLI_EPI_STORE_BF16) {
+              __nv_bfloat16* o = (__nv_bfloat16*)p.out + (long long)arow * p.ldo + f0;
+              if (full) {
+                uint32_t w[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) w[j] = pack_bf16(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+                *reinterpret_cast<uint4*>(o) = make_uint4(w[0], w[1], w[2], w[3]);
+                *reinterpret_cast<uint4*>(o + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+              } else {
+                for (int j = 0; j < 16 && f0 + j < p.n_features; ++j) o[j] = __float2bfloat16_rn(__uint_as_float(v[j]));
+              }
+            } else {
+              float* o = (float*)p.out + (long long)arow * p.ldo + f0;
+              if (full) {
+#pragma unroll
+                for (int j = 0; j < 16; j += 4) {
+                  if (EPI == DLI_EPI_ADD_F32) {
+                    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o + j), "f"(__uint_as_float(v[j])),
+                                 "f"(__uint_as_float(v[j + 1])), "f"(__uint_as_float(v[j + 2])),
+                                 "f"(__uint_as_float(v[j + 3]))
+                                 : "memory");
+                  } else {
+                    *reinterpret_cast<float4*>(o + j) =
+                        make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                                    __uint_as_float(v[j + 3]));
+                  }
+                }
+              } else {
+                for (int j = 0; j < 16 && f0 + j < p.n_features; ++j) {
+                  if (EPI == DLI_EPI_ADD_F32) atomicAdd(o + j, __uint_as_float(v[j]));
+                  else o[j] = __uint_as_float(v[j]);
+                }
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TMEM_COLS) : "memory");
+  }
+}
+
+// ---- host side ----------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+// 2-D bf16 tensor [rows, cols] with row pitch ld elements; box = [box_rows, 64 cols], 128B swizzle.
+int make_tmap_bf16(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return fail(DLI_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld % 8) != 0)
+    return fail(DLI_ERR_ARG, "TMA operand needs a 16-byte aligned base and a row pitch that is a multiple of 8 elements");
+  if (box_rows < 1 || box_rows > 256) return fail(DLI_ERR_ARG, "TMA box rows %d out of range", box_rows);
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(DLI_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return DLI_OK;
+}
+
+template <int BN, int EPI, bool SWAP>
+static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid, cudaStream_t st) {
+  constexpr int STAGE_BYTES = A_TILE_BYTES + BN * BK * 2;
+  const size_t smem = (size_t)p.stages * STAGE_BYTES + 1024;
+  static bool configured = false;  // per instantiation
+  auto kern = gemm_tcgen05_kernel<BN, EPI, SWAP>;
+  if (!configured) {
+    DLI_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+    configured = true;
+  }
+  kern<<<grid, GEMM_THREADS, smem, st>>>(ta, tb, p);
+  DLI_CHECK_LAUNCH("gemm_tcgen05_kernel");
+  return DLI_OK;
+}
+
+template <int BN, bool SWAP>
+static int launch_epi(int epi, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid, cudaStream_t st) {
+  switch (epi) {
+    case DLI_EPI_STORE_F32: return launch_variant<BN, DLI_EPI_STORE_F32, SWAP>(ta, tb, p, grid, st);
+    case DLI_EPI_ADD_F32: return launch_variant<BN, DLI_EPI_ADD_F32, SWAP>(ta, tb, p, grid, st);
+    case DLI_EPI_STORE_BF16: return launch_variant<BN, DLI_EPI_STORE_BF16, SWAP>(ta, tb, p, grid, st);
+    default: return fail(DLI_ERR_ARG, "unknown epilogue %d", epi);
+  }
+}
+
+GemmPlan plan_gemm(int m, int n, int k, int epilogue) {
+  GemmPlan g{};
+  g.k_blocks = (k + BK - 1) / BK;
+  const int sms = sm_count();
+  if (m <= 128 && epilogue != DLI_EPI_SILU_MUL_BF16) {
+    g.swap = true;
+    g.bn = m <= 16 ? 16 : m <= 32 ? 32 : m <= 64 ? 64 : 128;
+    g.a_box_rows = BM;       // weights
+    g.b_box_rows = g.bn;     // tokens
+    const int tiles = (n + BM - 1) / BM;
+    int splits = 1;
+    if (epilogue == DLI_EPI_ADD_F32) {
+      // two co-resident CTAs per SM keep ~200 KB of weight tiles in flight per SM; every split keeps >= 4 k-blocks
+      const int want = (2 * sms) / tiles;
+      splits = max(1, min(want, g.k_blocks / 4));
+      splits = min(splits, 32);
+    }
+    g.kb_per_split = (g.k_blocks + splits - 1) / splits;
+    g.splits = (g.k_blocks + g.kb_per_split - 1) / g.kb_per_split;
+    const int stage_bytes = A_TILE_BYTES + g.bn * BK * 2;
+    g.stages = min(MAX_STAGES, (112 * 1024 - 2048) / stage_bytes);
+    g.stages = max(2, min(g.stages, g.kb_per_split));
+    g.grid_x = tiles;
+    g.grid_y = (m + g.bn - 1) / g.bn;
+  } else {
+    g.swap = false;
+    const int tm = (m + BM - 1) / BM;
+    if (epilogue == DLI_EPI_SILU_MUL_BF16) {
+      g.bn = 256;               // 128 gate + 128 up columns
+      g.b_box_rows = 128;
+      g.grid_y = (n + 127) / 128;
+    } else {
+      auto waves = [&](int bn) { return (double)(((long long)tm * ((n + bn - 1) / bn) + sms - 1) / sms) * bn; };
+      g.bn = (n % 256 == 0 && waves(256) * 0.95 <= waves(128)) ? 256 : 128;
+      g.b_box_rows = g.bn;
+      g.grid_y = (n + g.bn - 1) / g.bn;
+    }
+    g.a_box_rows = BM;
+    g.grid_x = tm;
+    g.splits = 1;
+    g.kb_per_split = g.k_blocks;
+    const int stage_bytes = A_TILE_BYTES + g.bn * BK * 2;
+    g.stages = min(MAX_STAGES, (226 * 1024 - 2048) / stage_bytes);
+    g.stages = max(2, min(g.stages, g.k_blocks));
+  }
+  return g;
+}
+
+int launch_gemm_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const CUtensorMap& tmap_w, void* out, long long ldo,
+                        int m, int n, int epilogue, cudaStream_t st) {
+  GemmParams p{};
+  p.out = out;
+  p.ldo = ldo;
+  p.m_tokens = m;
+  p.n_features = n;
+  p.k_blocks = g.k_blocks;
+  p.kb_per_split = g.kb_per_split;
+  p.stages = g.stages;
+  p.up_row_offset = n;
+  dim3 grid(g.grid_x, g.grid_y, g.splits);
+  if (g.swap) {
+    // A = weights, B = tokens
+    switch (g.bn) {
+      case 16: return launch_epi<16, true>(epilogue, tmap_w, tmap_x, p, grid, st);
+      case 32: return launch_epi<32, true>(epilogue, tmap_w, tmap_x, p, grid, st);
+      case 64: return launch_epi<64, true>(epilogue, tmap_w, tmap_x, p, grid, st);
+      default: return launch_epi<128, true>(epilogue, tmap_w, tmap_x, p, grid, st);
+    }
+  }
+  if (epilogue == DLI_EPI_SILU_MUL_BF16) return launch_variant<256, DLI_EPI_SILU_MUL_BF16, false>(tmap_x, tmap_w, p, grid, st);
+  if (g.bn == 256) return launch_epi<256, false>(epilogue, tmap_x, tmap_w, p, grid, st);
+  return launch_epi<128, false>(epilogue, tmap_x, tmap_w, p, grid, st);
+}
+
+int launch_gemm(const void* x, long long ldx, const void* w, void* out, long long ldo, int m, int n, int k, int epilogue,
+                cudaStream_t st) {
+  DLI_REQUIRE(x && w && out, "dli_gemm: null pointer");
+  DLI_REQUIRE(m > 0 && n > 0 && k > 0, "dli_gemm: empty problem (m=%d n=%d k=%d)", m, n, k);
+  DLI_REQUIRE(k % 8 == 0 && ldx % 8 == 0, "dli_gemm: k and ldx must be multiples of 8 (k=%d ldx=%lld)", k, ldx);
+  DLI_REQUIRE(epilogue >= 0 && epilogue <= DLI_EPI_SILU_MUL_BF16, "dli_gemm: unknown epilogue %d", epilogue);
+  const bool f32_out = epilogue == DLI_EPI_STORE_F32 || epilogue == DLI_EPI_ADD_F32;
+  DLI_REQUIRE((reinterpret_cast<uintptr_t>(out) & 15) == 0 && ldo % (f32_out ? 4 : 8) == 0,
+              "dli_gemm: output must be 16-byte aligned with ldo a multiple of %d", f32_out ? 4 : 8);
+  int epi = epilogue;
+  GemmPlan g = plan_gemm(m, n, k, epi);
+  if (g.swap && epi == DLI_EPI_STORE_F32) {
+    // weight-streaming path accumulates split-K partials in L2: clear the destination, then add
+    DLI_CUDA_OK(cudaMemset2DAsync(out, (size_t)ldo * 4, 0, (size_t)n * 4, (size_t)m, st));
+    count_launch();
+    epi = DLI_EPI_ADD_F32;
+    g = plan_gemm(m, n, k, epi);
+  }
+  const long long w_rows = epilogue == DLI_EPI_SILU_MUL_BF16 ? 2LL * n : n;
+  CUtensorMap tx, tw;
+  int rc = make_tmap_bf16(&tx, x, m, k, ldx, g.swap ? g.b_box_rows : g.a_box_rows);
+  if (rc) return rc;
+  rc = make_tmap_bf16(&tw, w, w_rows, k, k, g.swap ? g.a_box_rows : g.b_box_rows);
+  if (rc) return rc;
+  return launch_gemm_planned(g, tx, tw, out, ldo, m, n, epi, st);
+}
+
+}  // namespace dli

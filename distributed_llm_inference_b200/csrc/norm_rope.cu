@@ -1,0 +1,200 @@
+// HBM-bound element-wise kernels of the span: RMSNorm, RoPE + paged KV append, SiLU*up, fp32->bf16 cast.
+#include "common.cuh"
+
+#include <algorithm>
+
+namespace dli {
+
+// ---------------------------------------------------------------------------------------------------
+// RMSNorm (LlamaRMSNorm.forward as called at modules.py:162 and :179).  One CTA per row; fp32 math;
+// y = bf16(w * (s x) * rsqrt(mean((s x)^2) + eps)).  s = 2 reproduces the reference's norm of h + h.
+// Optional side outputs: fp32 copy (bf16 hand-off -> fp32 residual stream at span entry) and bf16 copy
+// (output_hidden_states, model.py:57-61).
+// ---------------------------------------------------------------------------------------------------
+constexpr int NORM_THREADS = 256;
+
+template <bool F32IN>
+__device__ __forceinline__ void load8(const void* x, long long i, float (&v)[8]) {
+  if (F32IN) {
+    const float4 a = *reinterpret_cast<const float4*>((const float*)x + i);
+    const float4 b = *reinterpret_cast<const float4*>((const float*)x + i + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  } else {
+    const uint4 a = *reinterpret_cast<const uint4*>((const __nv_bfloat16*)x + i);
+    v[0] = bf16_lo(a.x); v[1] = bf16_hi(a.x); v[2] = bf16_lo(a.y); v[3] = bf16_hi(a.y);
+    v[4] = bf16_lo(a.z); v[5] = bf16_hi(a.z); v[6] = bf16_lo(a.w); v[7] = bf16_hi(a.w);
+  }
+}
+
+template <bool F32IN>
+__global__ void __launch_bounds__(NORM_THREADS) rmsnorm_kernel(const void* __restrict__ x, const __nv_bfloat16* __restrict__ w,
+                                                               __nv_bfloat16* __restrict__ y, float* __restrict__ resid_out,
+                                                               __nv_bfloat16* __restrict__ copy_out, int h, float eps,
+                                                               float s) {
+  __shared__ float red[NORM_THREADS / 32];
+  __shared__ float rinv;
+  const long long base = (long long)blockIdx.x * h;
+  float ss = 0.f;
+  float v[8];
+  for (int i = threadIdx.x * 8; i < h; i += NORM_THREADS * 8) {
+    load8<F32IN>(x, base + i, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) ss += v[j] * v[j];
+    if (resid_out) {
+      *reinterpret_cast<float4*>(resid_out + base + i) = make_float4(v[0], v[1], v[2], v[3]);
+      *reinterpret_cast<float4*>(resid_out + base + i + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    }
+    if (copy_out) {
+      *reinterpret_cast<uint4*>(copy_out + base + i) =
+          make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+    }
+  }
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = threadIdx.x < NORM_THREADS / 32 ? red[threadIdx.x] : 0.f;
+    t = warp_sum(t);
+    if (threadIdx.x == 0) rinv = rsqrtf(t * s * s / (float)h + eps);
+  }
+  __syncthreads();
+  const float r = rinv * s;
+  for (int i = threadIdx.x * 8; i < h; i += NORM_THREADS * 8) {
+    load8<F32IN>(x, base + i, v);  // second pass hits L1/L2
+    const uint4 wv = *reinterpret_cast<const uint4*>(w + i);
+    const float g[8] = {bf16_lo(wv.x), bf16_hi(wv.x), bf16_lo(wv.y), bf16_hi(wv.y),
+                        bf16_lo(wv.z), bf16_hi(wv.z), bf16_lo(wv.w), bf16_hi(wv.w)};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o[j] = pack_bf16(g[2 * j] * (v[2 * j] * r), g[2 * j + 1] * (v[2 * j + 1] * r));
+    *reinterpret_cast<uint4*>(y + base + i) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+int launch_rmsnorm(const void* x, bool x_is_f32, const __nv_bfloat16* w, __nv_bfloat16* y, float* resid_out,
+                   __nv_bfloat16* copy_out, int rows, int h, float eps, float pre_scale, cudaStream_t st) {
+  DLI_REQUIRE(x && w && y, "dli_rmsnorm: null pointer");
+  DLI_REQUIRE(rows > 0 && h > 0 && h % 8 == 0, "dli_rmsnorm: rows=%d h=%d (h must be a positive multiple of 8)", rows, h);
+  if (x_is_f32)
+    rmsnorm_kernel<true><<<rows, NORM_THREADS, 0, st>>>(x, w, y, resid_out, copy_out, h, eps, pre_scale);
+  else
+    rmsnorm_kernel<false><<<rows, NORM_THREADS, 0, st>>>(x, w, y, resid_out, copy_out, h, eps, pre_scale);
+  DLI_CHECK_LAUNCH("rmsnorm_kernel");
+  return DLI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// RoPE (modules.py:17-20: x*cos + rotate_half(x)*sin, rotate_half = cat(-x2, x1)) fused with the KV
+// append (cache.py:103-109).  One CTA per token; each thread rotates two adjacent (d, d + hd/2) pairs.
+// q goes to a dense bf16 [tokens, H*hd] buffer, rotated k and raw v go to the sequence's pages.
+// ---------------------------------------------------------------------------------------------------
+constexpr int ROPE_THREADS = 256;
+
+__global__ void __launch_bounds__(ROPE_THREADS) rope_kv_append_kernel(float* __restrict__ qkv, int zero_after,
+                                                                      const float* __restrict__ cosT,
+                                                                      const float* __restrict__ sinT,
+                                                                      __nv_bfloat16* __restrict__ q_out, KvView kv,
+                                                                      int q_len, int H, int KV, int hd) {
+  const int t = blockIdx.x;
+  const int b = t / q_len, l = t - b * q_len;
+  const int half = hd >> 1;
+  const int n_all = (H + 2 * KV) * hd;
+  float* row = qkv + (long long)t * n_all;
+  const int pos = kv.seq_lens[b] + l;
+  const int page = kv.block_table[(long long)b * kv.max_pages + pos / kv.page_tokens];
+  const int slot = pos % kv.page_tokens;
+  const float* cs = cosT + (long long)l * hd;
+  const float* sn = sinT + (long long)l * hd;
+
+  const int pairs2 = (H + KV) * half / 2;  // work items: two adjacent d per thread
+  for (int it = threadIdx.x; it < pairs2; it += ROPE_THREADS) {
+    const int p = it * 2;
+    const int head = p / half, d = p - head * half;
+    float* x = row + head * hd + d;
+    const float2 x1 = *reinterpret_cast<const float2*>(x);
+    const float2 x2 = *reinterpret_cast<const float2*>(x + half);
+    const float2 c1 = *reinterpret_cast<const float2*>(cs + d), c2 = *reinterpret_cast<const float2*>(cs + d + half);
+    const float2 s1 = *reinterpret_cast<const float2*>(sn + d), s2 = *reinterpret_cast<const float2*>(sn + d + half);
+    const float o1x = x1.x * c1.x - x2.x * s1.x, o1y = x1.y * c1.y - x2.y * s1.y;
+    const float o2x = x2.x * c2.x + x1.x * s2.x, o2y = x2.y * c2.y + x1.y * s2.y;
+    __nv_bfloat16* dst;
+    if (head < H) {
+      dst = q_out + (long long)t * H * hd + head * hd + d;
+    } else {
+      dst = kv.k + (((long long)page * KV + (head - H)) * kv.page_tokens + slot) * hd + d;
+    }
+    *reinterpret_cast<uint32_t*>(dst) = pack_bf16(o1x, o1y);
+    *reinterpret_cast<uint32_t*>(dst + half) = pack_bf16(o2x, o2y);
+    if (zero_after) {
+      *reinterpret_cast<float2*>(x) = make_float2(0.f, 0.f);
+      *reinterpret_cast<float2*>(x + half) = make_float2(0.f, 0.f);
+    }
+  }
+  float* vrow = row + (H + KV) * hd;
+  for (int e = threadIdx.x * 4; e < KV * hd; e += ROPE_THREADS * 4) {
+    const float4 a = *reinterpret_cast<const float4*>(vrow + e);
+    const int kvh = e / hd, d = e - kvh * hd;
+    __nv_bfloat16* dst = kv.v + (((long long)page * KV + kvh) * kv.page_tokens + slot) * hd + d;
+    *reinterpret_cast<uint2*>(dst) = make_uint2(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w));
+    if (zero_after) *reinterpret_cast<float4*>(vrow + e) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+int launch_rope_kv_append(float* qkv, bool zero_after, const float* cos, const float* sin, __nv_bfloat16* q_out,
+                          const KvView& kv, int batch, int q_len, int H, int KV, int hd, cudaStream_t st) {
+  DLI_REQUIRE(qkv && cos && sin && q_out, "dli_rope_kv_append: null pointer");
+  DLI_REQUIRE(batch > 0 && q_len > 0, "dli_rope_kv_append: batch=%d q_len=%d", batch, q_len);
+  DLI_REQUIRE(hd % 8 == 0 && H % KV == 0, "dli_rope_kv_append: head_dim %% 8 and H %% KV must be 0 (hd=%d H=%d KV=%d)", hd, H, KV);
+  rope_kv_append_kernel<<<batch * q_len, ROPE_THREADS, 0, st>>>(qkv, zero_after ? 1 : 0, cos, sin, q_out, kv, q_len, H, KV, hd);
+  DLI_CHECK_LAUNCH("rope_kv_append_kernel");
+  return DLI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// act = silu(gate) * up from the fp32 split-K accumulation buffer [m, 2n] (LlamaMLP.forward, modules.py:181)
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) silu_mul_kernel(float* __restrict__ gu, __nv_bfloat16* __restrict__ act, int m, int n,
+                                                       int zero_after) {
+  const long long total4 = (long long)m * n / 4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (long long)gridDim.x * blockDim.x) {
+    const long long e = i * 4;
+    const int r = (int)(e / n), c = (int)(e - (long long)r * n);
+    float* g = gu + (long long)r * 2 * n + c;
+    const float4 a = *reinterpret_cast<const float4*>(g);
+    const float4 u = *reinterpret_cast<const float4*>(g + n);
+    const float o0 = a.x / (1.f + __expf(-a.x)) * u.x, o1 = a.y / (1.f + __expf(-a.y)) * u.y;
+    const float o2 = a.z / (1.f + __expf(-a.z)) * u.z, o3 = a.w / (1.f + __expf(-a.w)) * u.w;
+    *reinterpret_cast<uint2*>(act + (long long)r * n + c) = make_uint2(pack_bf16(o0, o1), pack_bf16(o2, o3));
+    if (zero_after) {
+      *reinterpret_cast<float4*>(g) = make_float4(0.f, 0.f, 0.f, 0.f);
+      *reinterpret_cast<float4*>(g + n) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+}
+
+int launch_silu_mul(float* gu, __nv_bfloat16* act, int m, int n, bool zero_after, cudaStream_t st) {
+  DLI_REQUIRE(gu && act, "dli_silu_mul: null pointer");
+  DLI_REQUIRE(m > 0 && n > 0 && n % 4 == 0, "dli_silu_mul: m=%d n=%d (n must be a multiple of 4)", m, n);
+  const long long total4 = (long long)m * n / 4;
+  const int blocks = (int)std::min<long long>((total4 + 255) / 256, (long long)sm_count() * 8);
+  silu_mul_kernel<<<blocks, 256, 0, st>>>(gu, act, m, n, zero_after ? 1 : 0);
+  DLI_CHECK_LAUNCH("silu_mul_kernel");
+  return DLI_OK;
+}
+
+__global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long n4) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    const float4 a = *reinterpret_cast<const float4*>(in + i * 4);
+    *reinterpret_cast<uint2*>(out + i * 4) = make_uint2(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w));
+  }
+}
+
+int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st) {
+  DLI_REQUIRE(in && out && n > 0 && n % 4 == 0, "dli_cast_f32_bf16: n=%lld must be a positive multiple of 4", n);
+  const int blocks = (int)std::min<long long>((n / 4 + 255) / 256, (long long)sm_count() * 8);
+  cast_kernel<<<blocks, 256, 0, st>>>(in, out, n / 4);
+  DLI_CHECK_LAUNCH("cast_kernel");
+  return DLI_OK;
+}
+
+}  // namespace dli

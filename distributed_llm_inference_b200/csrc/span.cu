@@ -1,0 +1,339 @@
+// extern "C" surface of libdli_b200 and the span runner (LlamaBlock.forward, model.py:25-76, as one call).
+#include "common.cuh"
+
+#include <stdarg.h>
+#include <string.h>
+
+#include <new>
+#include <vector>
+
+namespace dli {
+
+// ---- error / bookkeeping --------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+static thread_local int g_launches = 0;
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+void count_launch(int n) { g_launches += n; }
+void reset_launch_count() { g_launches = 0; }
+
+int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+  }
+  return n;
+}
+
+int kv_view(const dli_kv_desc* kv, int layer, KvView* out) {
+  DLI_REQUIRE(kv && kv->k_pages && kv->v_pages && kv->block_table && kv->seq_lens, "kv descriptor has a null pointer");
+  DLI_REQUIRE(kv->page_tokens > 0 && kv->n_pages > 0 && kv->max_pages > 0 && kv->max_ctx > 0,
+              "kv descriptor: page_tokens=%d n_pages=%d max_pages=%d max_ctx=%d", kv->page_tokens, kv->n_pages,
+              kv->max_pages, kv->max_ctx);
+  DLI_REQUIRE(layer >= 0, "negative layer index");
+  out->k = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(kv->k_pages) + (long long)layer * kv->layer_stride_bytes);
+  out->v = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(kv->v_pages) + (long long)layer * kv->layer_stride_bytes);
+  out->block_table = kv->block_table;
+  out->seq_lens = kv->seq_lens;
+  out->page_tokens = kv->page_tokens;
+  out->n_pages = kv->n_pages;
+  out->max_pages = kv->max_pages;
+  out->max_ctx = kv->max_ctx;
+  return DLI_OK;
+}
+
+// ---- span object ------------------------------------------------------------------------------------
+struct WeightMaps {
+  CUtensorMap box128, box256;
+};
+struct Layer {
+  dli_layer_weights w{};
+  bool bound = false;
+  WeightMaps qkv, o, gu, down;
+};
+struct ActMapKey {
+  const void* ptr;
+  int rows, cols, box;
+  CUtensorMap map;
+};
+
+}  // namespace dli
+
+struct dli_span {
+  dli_span_desc d;
+  int n_qkv;  // (H + 2 KV) * hd
+  std::vector<dli::Layer> layers;
+  std::vector<dli::ActMapKey> act_maps;  // activation-side TMA descriptors, keyed by (pointer, shape, box)
+};
+
+namespace dli {
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+// Layout: the two split-K accumulation buffers come first, at offsets that do not depend on the call's
+// shape, because they carry an invariant across calls (all zeros on entry and on exit); everything behind
+// them is per-call scratch.
+struct Workspace {
+  float* qkv_acc;  // [128, n_qkv] fp32, zero between calls
+  float* gu_acc;   // [128, 2i]    fp32, zero between calls
+  float* resid;
+  __nv_bfloat16* xn;
+  float* qkv;
+  __nv_bfloat16* qbuf;
+  __nv_bfloat16* attn;
+  __nv_bfloat16* act;
+  float* dec_scratch;
+  size_t dec_scratch_bytes;
+  size_t total;
+};
+
+static Workspace carve(const dli_span* s, void* base, int max_tokens, int max_batch, int max_ctx) {
+  const dli_span_desc& d = s->d;
+  char* p = static_cast<char*>(base);
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    char* r = p ? p + off : nullptr;
+    off += align256(bytes);
+    return r;
+  };
+  Workspace w{};
+  const size_t M = (size_t)max_tokens;
+  w.qkv_acc = (float*)take((size_t)128 * s->n_qkv * 4);
+  w.gu_acc = (float*)take((size_t)128 * 2 * d.intermediate_size * 4);
+  w.resid = (float*)take(M * d.hidden_size * 4);
+  w.xn = (__nv_bfloat16*)take(M * d.hidden_size * 2);
+  w.qkv = (float*)take(max_tokens > 128 ? M * s->n_qkv * 4 : 0);
+  w.qbuf = (__nv_bfloat16*)take(M * d.n_heads * d.head_dim * 2);
+  w.attn = (__nv_bfloat16*)take(M * d.n_heads * d.head_dim * 2);
+  w.act = (__nv_bfloat16*)take(M * d.intermediate_size * 2);
+  w.dec_scratch_bytes = decode_attn_scratch_bytes(max_batch, d.n_heads, d.head_dim, max_ctx);
+  w.dec_scratch = (float*)take(w.dec_scratch_bytes);
+  w.total = off;
+  return w;
+}
+
+static int act_map(dli_span* s, const void* ptr, int rows, int cols, int box, const CUtensorMap** out) {
+  for (auto& e : s->act_maps)
+    if (e.ptr == ptr && e.rows == rows && e.cols == cols && e.box == box) {
+      *out = &e.map;
+      return DLI_OK;
+    }
+  if (s->act_maps.size() >= 64) s->act_maps.clear();
+  ActMapKey k{ptr, rows, cols, box, {}};
+  int rc = make_tmap_bf16(&k.map, ptr, rows, cols, cols, box);
+  if (rc) return rc;
+  s->act_maps.push_back(k);
+  *out = &s->act_maps.back().map;
+  return DLI_OK;
+}
+
+// one linear layer of the span: out (+)= x[m, k] . w[n, k]^T through the planned tcgen05 kernel
+static int span_gemm(dli_span* s, const void* x, const WeightMaps& wm, void* out, long long ldo, int m, int n, int k,
+                     int epilogue, cudaStream_t st) {
+  const GemmPlan g = plan_gemm(m, n, k, epilogue);
+  const int x_box = g.swap ? g.b_box_rows : g.a_box_rows;
+  const int w_box = g.swap ? g.a_box_rows : g.b_box_rows;
+  const CUtensorMap* tx = nullptr;
+  int rc = act_map(s, x, m, k, x_box, &tx);
+  if (rc) return rc;
+  const CUtensorMap& tw = w_box == 256 ? wm.box256 : wm.box128;
+  return launch_gemm_planned(g, *tx, tw, out, ldo, m, n, epilogue, st);
+}
+
+}  // namespace dli
+
+using namespace dli;
+
+extern "C" {
+
+int dli_version(void) { return DLI_VERSION; }
+const char* dli_last_error(void) { return g_err; }
+int dli_last_launch_count(void) { return g_launches; }
+
+int dli_rmsnorm(const void* x, int x_is_f32, const void* weight_bf16, void* y_bf16, float* resid_out, int rows, int h,
+                float eps, float pre_scale, dli_stream_t stream) {
+  return launch_rmsnorm(x, x_is_f32 != 0, (const __nv_bfloat16*)weight_bf16, (__nv_bfloat16*)y_bf16, resid_out, nullptr,
+                        rows, h, eps, pre_scale, (cudaStream_t)stream);
+}
+
+int dli_gemm(const void* x_bf16, int64_t ldx, const void* w_bf16, void* out, int64_t ldo, int m, int n, int k,
+             int epilogue, dli_stream_t stream) {
+  return launch_gemm(x_bf16, ldx, w_bf16, out, ldo, m, n, k, epilogue, (cudaStream_t)stream);
+}
+
+int dli_rope_kv_append(float* qkv_f32, int zero_after, const float* cos, const float* sin, void* q_bf16,
+                       const dli_kv_desc* kv, int layer, int batch, int q_len, int n_heads, int n_kv_heads,
+                       int head_dim, dli_stream_t stream) {
+  KvView v;
+  int rc = kv_view(kv, layer, &v);
+  if (rc) return rc;
+  return launch_rope_kv_append(qkv_f32, zero_after != 0, cos, sin, (__nv_bfloat16*)q_bf16, v, batch, q_len, n_heads,
+                               n_kv_heads, head_dim, (cudaStream_t)stream);
+}
+
+size_t dli_decode_attention_scratch_bytes(int batch, int n_heads, int head_dim, int max_ctx) {
+  return decode_attn_scratch_bytes(batch, n_heads, head_dim, max_ctx);
+}
+
+int dli_decode_attention(const void* q_bf16, void* out_bf16, const dli_kv_desc* kv, int layer, int batch, int n_heads,
+                         int n_kv_heads, int head_dim, float* scratch, size_t scratch_bytes, dli_stream_t stream) {
+  KvView v;
+  int rc = kv_view(kv, layer, &v);
+  if (rc) return rc;
+  return launch_decode_attention((const __nv_bfloat16*)q_bf16, (__nv_bfloat16*)out_bf16, v, batch, n_heads, n_kv_heads,
+                                 head_dim, scratch, scratch_bytes, (cudaStream_t)stream);
+}
+
+int dli_prefill_attention(const void* q_bf16, void* out_bf16, const dli_kv_desc* kv, int layer, int batch, int q_len,
+                          int n_heads, int n_kv_heads, int head_dim, int causal, dli_stream_t stream) {
+  KvView v;
+  int rc = kv_view(kv, layer, &v);
+  if (rc) return rc;
+  return launch_prefill_attention((const __nv_bfloat16*)q_bf16, (__nv_bfloat16*)out_bf16, v, batch, q_len, n_heads,
+                                  n_kv_heads, head_dim, causal != 0, (cudaStream_t)stream);
+}
+
+int dli_silu_mul(float* gu_f32, void* act_bf16, int m, int n, int zero_after, dli_stream_t stream) {
+  return launch_silu_mul(gu_f32, (__nv_bfloat16*)act_bf16, m, n, zero_after != 0, (cudaStream_t)stream);
+}
+
+int dli_cast_f32_bf16(const float* in, void* out_bf16, int64_t n, dli_stream_t stream) {
+  return launch_cast(in, (__nv_bfloat16*)out_bf16, n, (cudaStream_t)stream);
+}
+
+int dli_span_create(const dli_span_desc* desc, dli_span** out) {
+  DLI_REQUIRE(desc && out, "dli_span_create: null pointer");
+  DLI_REQUIRE(desc->dtype == DLI_BF16, "dli_span_create: only DLI_BF16 is implemented");
+  DLI_REQUIRE(desc->hidden_size > 0 && desc->hidden_size % 8 == 0 && desc->intermediate_size > 0 &&
+                  desc->intermediate_size % 8 == 0,
+              "dli_span_create: hidden/intermediate sizes must be positive multiples of 8");
+  DLI_REQUIRE(desc->n_heads > 0 && desc->n_kv_heads > 0 && desc->n_heads % desc->n_kv_heads == 0,
+              "dli_span_create: n_heads must be a multiple of n_kv_heads");
+  DLI_REQUIRE(desc->head_dim == 64 || desc->head_dim == 128, "dli_span_create: head_dim must be 64 or 128");
+  const int G = desc->n_heads / desc->n_kv_heads;
+  DLI_REQUIRE(G == 1 || G == 2 || G == 4 || G == 8, "dli_span_create: GQA group size %d not supported (1, 2, 4, 8)", G);
+  DLI_REQUIRE(desc->n_layers > 0, "dli_span_create: n_layers must be positive");
+  dli_span* s = new (std::nothrow) dli_span();
+  if (!s) return fail(DLI_ERR_ARG, "dli_span_create: out of host memory");
+  s->d = *desc;
+  s->n_qkv = (desc->n_heads + 2 * desc->n_kv_heads) * desc->head_dim;
+  s->layers.resize(desc->n_layers);
+  s->act_maps.reserve(64);
+  *out = s;
+  return DLI_OK;
+}
+
+int dli_span_destroy(dli_span* span) {
+  delete span;
+  return DLI_OK;
+}
+
+int dli_span_bind_weights(dli_span* s, int layer, const dli_layer_weights* w) {
+  DLI_REQUIRE(s && w, "dli_span_bind_weights: null pointer");
+  DLI_REQUIRE(layer >= 0 && layer < s->d.n_layers, "dli_span_bind_weights: layer %d out of range", layer);
+  DLI_REQUIRE(w->wqkv && w->wo && w->wgu && w->wdown && w->g_in && w->g_post, "dli_span_bind_weights: null weight pointer");
+  Layer& L = s->layers[layer];
+  const dli_span_desc& d = s->d;
+  const int qdim = d.n_heads * d.head_dim;
+  struct { const void* p; long long rows, cols; WeightMaps* m; } items[4] = {
+      {w->wqkv, s->n_qkv, d.hidden_size, &L.qkv},
+      {w->wo, d.hidden_size, qdim, &L.o},
+      {w->wgu, 2LL * d.intermediate_size, d.hidden_size, &L.gu},
+      {w->wdown, d.hidden_size, d.intermediate_size, &L.down}};
+  for (auto& it : items) {
+    int rc = make_tmap_bf16(&it.m->box128, it.p, it.rows, it.cols, it.cols, 128);
+    if (rc) return rc;
+    rc = make_tmap_bf16(&it.m->box256, it.p, it.rows, it.cols, it.cols, 256);
+    if (rc) return rc;
+  }
+  L.w = *w;
+  L.bound = true;
+  return DLI_OK;
+}
+
+size_t dli_span_workspace_bytes(const dli_span* span, int max_tokens, int max_batch, int max_ctx) {
+  if (!span || max_tokens <= 0 || max_batch <= 0 || max_ctx <= 0) return 0;
+  return carve(span, nullptr, max_tokens, max_batch, max_ctx).total;
+}
+
+int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, int causal, const void* hidden_in,
+                     void* hidden_out, const float* cos, const float* sin, void* all_hidden, void* workspace,
+                     size_t workspace_bytes, dli_stream_t stream) {
+  reset_launch_count();
+  DLI_REQUIRE(s && kv && hidden_in && hidden_out && cos && sin && workspace, "dli_span_forward: null pointer");
+  DLI_REQUIRE(batch > 0 && q_len > 0, "dli_span_forward: batch=%d q_len=%d", batch, q_len);
+  DLI_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "dli_span_forward: workspace must be 256-byte aligned");
+  const dli_span_desc& d = s->d;
+  const int M = batch * q_len;
+  const Workspace w = carve(s, workspace, M, batch, kv->max_ctx);
+  if (w.total > workspace_bytes)
+    return fail(DLI_ERR_WORKSPACE, "dli_span_forward: workspace %zu bytes < %zu needed", workspace_bytes, w.total);
+  for (int j = 0; j < d.n_layers; ++j)
+    DLI_REQUIRE(s->layers[j].bound, "dli_span_forward: layer %d has no weights bound", j);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int h = d.hidden_size, inter = d.intermediate_size, qdim = d.n_heads * d.head_dim;
+  const bool skinny = M <= 128;  // weight-streaming GEMM path accumulates into pre-zeroed fp32 buffers
+  __nv_bfloat16* hs = static_cast<__nv_bfloat16*>(all_hidden);
+  int rc;
+
+  for (int j = 0; j < d.n_layers; ++j) {
+    Layer& L = s->layers[j];
+    KvView view;
+    if ((rc = kv_view(kv, j, &view))) return rc;
+    // input_layernorm (modules.py:162); layer 0 also opens the fp32 residual stream
+    rc = launch_rmsnorm(j == 0 ? hidden_in : (const void*)w.resid, j != 0, (const __nv_bfloat16*)L.w.g_in, w.xn,
+                        j == 0 ? w.resid : nullptr, hs ? hs + (size_t)j * M * h : nullptr, M, h, d.eps_input, 1.0f, st);
+    if (rc) return rc;
+    // q|k|v projection (modules.py:61-63)
+    float* qkv = skinny ? w.qkv_acc : w.qkv;
+    rc = span_gemm(s, w.xn, L.qkv, qkv, s->n_qkv, M, s->n_qkv, h, skinny ? DLI_EPI_ADD_F32 : DLI_EPI_STORE_F32, st);
+    if (rc) return rc;
+    // RoPE + cache append (modules.py:73-85, cache.py:103-109); re-zeroes the split-K accumulation buffer behind itself
+    rc = launch_rope_kv_append(qkv, skinny, cos, sin, w.qbuf, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim, st);
+    if (rc) return rc;
+    // attention core (modules.py:87-105)
+    if (q_len == 1)
+      rc = launch_decode_attention(w.qbuf, w.attn, view, batch, d.n_heads, d.n_kv_heads, d.head_dim, w.dec_scratch,
+                                   w.dec_scratch_bytes, st);
+    else
+      rc = launch_prefill_attention(w.qbuf, w.attn, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim, causal != 0, st);
+    if (rc) return rc;
+    // o_proj + residual (modules.py:112,173)
+    rc = span_gemm(s, w.attn, L.o, w.resid, h, M, h, qdim, DLI_EPI_ADD_F32, st);
+    if (rc) return rc;
+    // post_attention_layernorm of h + h (modules.py:179)
+    rc = launch_rmsnorm(w.resid, true, (const __nv_bfloat16*)L.w.g_post, w.xn, nullptr, nullptr, M, h, d.eps_post,
+                        d.post_prescale, st);
+    if (rc) return rc;
+    // MLP (modules.py:181): gate|up with silu*up, then down + residual (modules.py:182)
+    if (skinny) {
+      rc = span_gemm(s, w.xn, L.gu, w.gu_acc, 2LL * inter, M, 2 * inter, h, DLI_EPI_ADD_F32, st);
+      if (rc) return rc;
+      rc = launch_silu_mul(w.gu_acc, w.act, M, inter, true, st);
+    } else {
+      rc = span_gemm(s, w.xn, L.gu, w.act, inter, M, inter, h, DLI_EPI_SILU_MUL_BF16, st);
+    }
+    if (rc) return rc;
+    rc = span_gemm(s, w.act, L.down, w.resid, h, M, h, inter, DLI_EPI_ADD_F32, st);
+    if (rc) return rc;
+  }
+  if ((rc = launch_cast(w.resid, static_cast<__nv_bfloat16*>(hidden_out), (long long)M * h, st))) return rc;
+  if (hs && (rc = launch_cast(w.resid, hs + (size_t)d.n_layers * M * h, (long long)M * h, st))) return rc;
+  return DLI_OK;
+}
+
+}  // extern "C"

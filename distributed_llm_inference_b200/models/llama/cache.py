@@ -1,0 +1,187 @@
+"""Paged, per-generation KV cache with the reference's ``PartialLlamaSinkCache`` interface.
+
+Reference: distributed_llm_inference/models/llama/cache.py:7-135.  There, every generation owns Python
+lists of ``[B, KV, S, hd]`` tensors that are re-allocated with ``torch.cat`` on every step (cache.py:107-109;
+22 % of the reference's CPU decode time).  Here every layer owns a pool of fixed-size pages
+``[n_pages, KV, page_tokens, hd]`` (bf16, keys stored rotated exactly as the reference stores them,
+modules.py:76-85); a generation is a block table (one row of page ids per sequence) plus a length, both
+mirrored on the device so that the kernels — and a replayed CUDA graph — read them from HBM.
+
+Same constructor signature ``(window_length, num_sink_tokens)`` (cache.py:11), same errors
+(``ValueError`` when the generation id is missing: cache.py:24-30,51-52,71-72), same
+``get_seq_length(layer_idx, generation_id)`` (cache.py:50-62), many concurrent generations keyed by
+``generation_id`` (cache.py:14-19).  Deviations, all deliberate:
+  * the constructor works (the reference's raises, cache.py:12 / SURVEY D1);
+  * layers are indexed by their LOCAL position in the span;
+  * attention-sink eviction (cache.py:111-133) is not implemented on the CUDA path yet: a generation that
+    would reach ``window_length`` raises ``NotImplementedError`` instead of silently diverging;
+  * ``update()`` (the per-layer tensor API of cache.py:64-135) is provided for callers that hold K/V
+    tensors themselves; the span forward does not use it — its fused kernel appends in place.
+"""
+from __future__ import annotations
+
+from typing import Any, Dict, List, Optional, Tuple
+
+import torch
+
+
+class _Generation:
+    __slots__ = ("batch", "length", "pages", "block_table", "seq_lens", "max_pages", "seen_tokens")
+
+    def __init__(self, batch: int, max_pages: int, device):
+        self.batch = batch
+        self.length = 0                      # tokens stored (same for every sequence of the generation)
+        self.seen_tokens = 0                 # cache.py:86-87
+        self.pages: List[List[int]] = [[] for _ in range(batch)]
+        self.max_pages = max_pages
+        self.block_table = torch.zeros(batch, max_pages, dtype=torch.int32, device=device)
+        self.seq_lens = torch.zeros(batch, dtype=torch.int32, device=device)
+
+
+class PartialLlamaSinkCache:
+    """Distributed sink cache: many generations at once, paged storage (reference cache.py:7-10)."""
+
+    def __init__(self, window_length: int, num_sink_tokens: int, *, page_tokens: int = 16,
+                 capacity_tokens: Optional[int] = None) -> None:
+        if window_length <= 0 or num_sink_tokens < 0:
+            raise ValueError("window_length must be positive and num_sink_tokens non-negative")
+        self.window_length = window_length
+        self.num_sink_tokens = num_sink_tokens
+        self.page_tokens = page_tokens
+        self.capacity_tokens = capacity_tokens
+        self._gens: Dict[str, _Generation] = {}
+        self._k: Optional[torch.Tensor] = None      # [n_layers, n_pages, KV, page_tokens, hd]
+        self._v: Optional[torch.Tensor] = None
+        self._free: List[int] = []
+        self._shape: Optional[Tuple[int, int, int]] = None   # (n_layers, KV, hd)
+
+    # ------------------------------------------------------------------ storage
+    def bind(self, n_layers: int, n_kv_heads: int, head_dim: int, device, dtype=torch.bfloat16) -> None:
+        """Allocate the page pools (once).  Called by ``LlamaBlock`` on first use; idempotent."""
+        shape = (n_layers, n_kv_heads, head_dim)
+        if self._k is not None:
+            if self._shape != shape or self._k.device != torch.device(device):
+                raise ValueError(f"cache already bound to {self._shape} on {self._k.device}")
+            return
+        cap = self.capacity_tokens if self.capacity_tokens is not None else min(self.window_length, 4096) * 4
+        n_pages = max(1, -(-cap // self.page_tokens))
+        self._k = torch.empty(n_layers, n_pages, n_kv_heads, self.page_tokens, head_dim, dtype=dtype, device=device)
+        self._v = torch.empty_like(self._k)
+        self._free = list(range(n_pages - 1, -1, -1))
+        self._shape = shape
+
+    @property
+    def n_pages(self) -> int:
+        return 0 if self._k is None else self._k.shape[1]
+
+    @property
+    def free_pages(self) -> int:
+        return len(self._free)
+
+    def _max_pages_per_seq(self) -> int:
+        return min(-(-self.window_length // self.page_tokens) + 1, max(1, self.n_pages))
+
+    # ------------------------------------------------------------------ generations
+    def open(self, generation_id: str, batch: int) -> _Generation:
+        if not generation_id:
+            raise ValueError("generation_id not provided")
+        if self._k is None:
+            raise RuntimeError("cache is not bound to a span yet")
+        g = self._gens.get(generation_id)
+        if g is None:
+            g = _Generation(batch, self._max_pages_per_seq(), self._k.device)
+            self._gens[generation_id] = g
+        elif g.batch != batch:
+            raise ValueError(f"generation {generation_id!r} was opened with batch {g.batch}, got {batch}")
+        return g
+
+    def close(self, generation_id: str) -> None:
+        """Return the generation's pages to the pool (the reference never frees; sessions end with the process)."""
+        g = self._gens.pop(generation_id, None)
+        if g is not None:
+            for row in g.pages:
+                self._free.extend(row)
+
+    def reserve(self, generation_id: str, batch: int, total_tokens: int) -> _Generation:
+        """Make sure pages exist for ``total_tokens`` tokens per sequence (so that a captured graph can be
+        replayed without touching the block table)."""
+        g = self.open(generation_id, batch)
+        if total_tokens >= self.window_length and g.length > 0:
+            raise NotImplementedError(
+                f"generation {generation_id!r} would reach window_length={self.window_length}: attention-sink "
+                "eviction (reference cache.py:111-133) is not implemented on the CUDA path")
+        need = -(-total_tokens // self.page_tokens)
+        if need > g.max_pages:
+            raise ValueError(f"{total_tokens} tokens exceed the block table ({g.max_pages} pages of {self.page_tokens})")
+        have = len(g.pages[0])
+        if need > have:
+            n_new = (need - have) * g.batch
+            if n_new > len(self._free):
+                raise RuntimeError(f"KV page pool exhausted: need {n_new} pages, {len(self._free)} free "
+                                   f"(capacity_tokens={self.n_pages * self.page_tokens})")
+            for b in range(g.batch):
+                g.pages[b].extend(self._free.pop() for _ in range(need - have))
+            host = torch.tensor([row + [0] * (g.max_pages - len(row)) for row in g.pages], dtype=torch.int32)
+            g.block_table.copy_(host, non_blocking=False)
+        return g
+
+    def advance(self, generation_id: str, n_tokens: int, local_first_layer: bool = True) -> None:
+        g = self._gens[generation_id]
+        g.length += n_tokens
+        g.seq_lens.add_(n_tokens)
+        if local_first_layer:
+            g.seen_tokens += n_tokens
+
+    def generation(self, generation_id: str) -> Optional[_Generation]:
+        return self._gens.get(generation_id)
+
+    # ------------------------------------------------------------------ reference API
+    def get_seq_length(self, layer_idx: Optional[int] = 0, generation_id: Optional[str] = None) -> int:
+        """cache.py:50-62."""
+        if not generation_id:
+            raise ValueError("generation_id not provided")
+        g = self._gens.get(generation_id)
+        if g is None:
+            return 0
+        if self._shape is not None and layer_idx is not None and layer_idx >= self._shape[0]:
+            return 0
+        return g.length
+
+    def get_max_length(self) -> Optional[int]:
+        return self.window_length
+
+    def update(self, key_states: torch.Tensor, value_states: torch.Tensor, layer_idx: int,
+               cache_kwargs: Optional[Dict[str, Any]] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+        """Per-layer tensor API of cache.py:64-135 for callers that hold rotated K and V ``[B, KV, n, hd]``
+        themselves: appends them to the pages of local layer ``layer_idx`` and returns the gathered
+        ``[B, KV, S, hd]`` views' copies.  The last layer of the span advances the generation length."""
+        if cache_kwargs is None or "generation_id" not in cache_kwargs:
+            raise ValueError("generation_id not found in cache_kwargs")
+        gid = cache_kwargs.get("generation_id")
+        B, KV, n, hd = key_states.shape
+        if self._k is None:
+            raise RuntimeError("cache is not bound to a span yet (call bind(n_layers, n_kv_heads, head_dim, device))")
+        g = self.reserve(gid, B, (self._gens[gid].length if gid in self._gens else 0) + n)
+        pt = self.page_tokens
+        pos = torch.arange(g.length, g.length + n, device=self._k.device)
+        table = g.block_table.long()
+        page = table[:, pos // pt]                              # [B, n]
+        slot = (pos % pt)[None, :].expand(B, n)
+        self._k[layer_idx][page, :, slot] = key_states.transpose(1, 2).to(self._k.dtype)
+        self._v[layer_idx][page, :, slot] = value_states.transpose(1, 2).to(self._v.dtype)
+        total = g.length + n
+        allpos = torch.arange(total, device=self._k.device)
+        pg, sl = table[:, allpos // pt], (allpos % pt)[None, :].expand(B, total)
+        k_all = self._k[layer_idx][pg, :, sl].transpose(1, 2)
+        v_all = self._v[layer_idx][pg, :, sl].transpose(1, 2)
+        if layer_idx == self._shape[0] - 1:
+            self.advance(gid, n)
+        return k_all, v_all
+
+    # ------------------------------------------------------------------ kernel-side view
+    def kv_desc(self, g: _Generation, max_ctx: int):
+        from distributed_llm_inference_b200 import _ffi
+
+        k = self._k
+        return _ffi.KvDesc(k.data_ptr(), self._v.data_ptr(), k.stride(0) * k.element_size(), self.page_tokens,
+                           k.shape[1], g.block_table.data_ptr(), g.seq_lens.data_ptr(), g.max_pages, max_ctx)

@@ -1,0 +1,205 @@
+"""``LlamaBlock`` — a contiguous span of Llama decoder layers executed by one C call into libdli_b200.
+
+Drop-in for distributed_llm_inference/models/llama/model.py:16-144: same constructor
+``LlamaBlock(config, layer_ids)`` (model.py:17), same ``forward`` signature and return tuple
+(model.py:25-34,76), same parameter names.  What differs is underneath: the layer loop of model.py:59-71
+runs as ``dli_span_forward`` (hand-written sm_100a kernels behind a C ABI), the KV cache is paged
+(``PartialLlamaSinkCache`` in this package), the additive mask of model.py:78-144 collapses to a ``causal``
+flag, and cos/sin (model.py:55) are gathered from a table so that both the reference's literal behaviour
+(int64-truncated tables, SURVEY D4: ``rope="literal"``) and the intended one (``rope="float"``) are host-side
+choices.
+
+There is NO CPU or PyTorch fallback: inputs must be bf16 CUDA tensors on a B200 and the shared library
+must be present; anything else raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional
+
+import torch
+from torch import nn
+
+from .cache import PartialLlamaSinkCache
+from .modules import OptimizedLlamaDecoderLayer
+
+_NOCACHE_ID = "__dli_no_cache__"
+
+
+def rope_table(head_dim: int, theta: float, max_pos: int, mode: str, device) -> torch.Tensor:
+    """``[2, max_pos, head_dim]`` fp32 (cos, sin) following transformers ``LlamaRotaryEmbedding.forward`` as the
+    reference calls it (model.py:55).  ``literal``: the reference passes ``position_ids`` as the dtype carrier,
+    so the tables are truncated toward zero to int64 — stored here as the same integers in fp32."""
+    inv_freq = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.int64).float() / head_dim))
+    pos = torch.arange(max_pos, dtype=torch.float32)
+    freqs = (inv_freq[None, :, None].float() @ pos[None, None, :].float()).transpose(1, 2)[0]   # [max_pos, hd/2]
+    emb = torch.cat((freqs, freqs), dim=-1)
+    cos, sin = emb.cos(), emb.sin()
+    if mode == "literal":
+        cos, sin = cos.to(torch.int64).float(), sin.to(torch.int64).float()
+    elif mode != "float":
+        raise ValueError(f"rope must be 'literal' or 'float', got {mode!r}")
+    return torch.stack([cos, sin]).contiguous().to(device)
+
+
+class LlamaBlock(nn.Module):
+    def __init__(self, config, layer_ids: List[int], *, rope: str = "literal", dtype=torch.bfloat16):
+        """``rope="literal"`` reproduces model.py:55 as written (int64 tables); ``rope="float"`` is what the
+        reference evidently intended."""
+        super().__init__()
+        if dtype != torch.bfloat16:
+            raise NotImplementedError("the B200 span kernels are bf16 (the north-star dtype)")
+        self.config = config
+        self.padding_idx = getattr(config, "pad_token_id", None)       # model.py:19
+        self.vocab_size = getattr(config, "vocab_size", None)          # model.py:20
+        self.layer_ids = list(layer_ids)
+        self.rope = rope
+        # layers keep their GLOBAL id as in model.py:22; the cache is indexed by local position
+        self.layers = nn.ModuleList([OptimizedLlamaDecoderLayer(config, idx, dtype=dtype) for idx in self.layer_ids])
+        self.head_dim = getattr(config, "head_dim", None) or config.hidden_size // config.num_attention_heads
+        rp = getattr(config, "rope_parameters", None) or {}
+        self.rope_theta = float(rp.get("rope_theta", getattr(config, "rope_theta", 10000.0)))
+        if rp.get("rope_type", "default") != "default":
+            raise NotImplementedError("only rope_type='default' is implemented")
+        self.max_positions = int(getattr(config, "max_position_embeddings", 4096))
+        self._span = None           # dli_span* (ctypes void pointer)
+        self._bound_ptrs = None
+        self._table: Optional[torch.Tensor] = None
+        self._ws: Optional[torch.Tensor] = None
+        self._ws_key = (0, 0, 0)
+        self._scratch_cache: Optional[PartialLlamaSinkCache] = None
+        self.last_launch_count = 0
+
+    # ------------------------------------------------------------------ native span object
+    def _ffi(self):
+        from distributed_llm_inference_b200 import _ffi
+
+        return _ffi
+
+    def _ensure_span(self, device):
+        ffi = self._ffi()
+        for layer in self.layers:
+            layer.fuse()
+        ptrs = tuple(p.data_ptr() for layer in self.layers for p in
+                     (layer._wqkv, layer.self_attn.o_proj.weight, layer._wgu, layer.mlp.down_proj.weight,
+                      layer.input_layernorm.weight, layer.post_attention_layernorm.weight))
+        if self._span is not None and ptrs == self._bound_ptrs:
+            return
+        cfg = self.config
+        if self._span is None:
+            desc = ffi.SpanDesc(cfg.hidden_size, cfg.intermediate_size, cfg.num_attention_heads,
+                                cfg.num_key_value_heads, self.head_dim, len(self.layers), 0,
+                                1e-6, 1e-6, 2.0)   # modules.py:124-125 (eps), modules.py:179 (norm of h + h)
+            out = C.c_void_p()
+            ffi.check(ffi.lib.dli_span_create(C.byref(desc), C.byref(out)))
+            self._span = out
+        for j, layer in enumerate(self.layers):
+            for p in layer.parameters():
+                if p.device != device or p.dtype != torch.bfloat16:
+                    raise ValueError(f"layer {j}: parameters must be bf16 on {device} (got {p.dtype} on {p.device})")
+            w = ffi.LayerWeights(*ptrs[6 * j: 6 * j + 6])
+            ffi.check(ffi.lib.dli_span_bind_weights(self._span, j, C.byref(w)))
+        self._bound_ptrs = ptrs
+
+    def __del__(self):
+        try:
+            if self._span is not None:
+                self._ffi().lib.dli_span_destroy(self._span)
+        except Exception:
+            pass
+
+    def _workspace(self, tokens: int, batch: int, max_ctx: int, device) -> torch.Tensor:
+        key = self._ws_key
+        if self._ws is None or tokens > key[0] or batch > key[1] or max_ctx > key[2] or self._ws.device != device:
+            key = (max(tokens, key[0]), max(batch, key[1]), max(-(-max_ctx // 1024) * 1024, key[2]))
+            nbytes = self._ffi().lib.dli_span_workspace_bytes(self._span, *key)
+            self._ws = torch.zeros(nbytes, dtype=torch.uint8, device=device)   # zero-filled once (C ABI contract)
+            self._ws_key = key
+        return self._ws
+
+    # ------------------------------------------------------------------ forward
+    def _causal_flag(self, attention_mask, q_len: int, past: int) -> int:
+        """model.py:78-144 reduced to one bit for the cases without padding."""
+        impl = getattr(self.config, "_attn_implementation", None) or "sdpa"
+        if attention_mask is not None:
+            if attention_mask.dim() != 2 or not bool(torch.all(attention_mask == 1)):
+                raise NotImplementedError("padding / custom 4-D attention masks are not supported by the B200 span")
+        if impl == "flash_attention_2":
+            return 0                                   # model.py:86-89: mask None -> modules.py:92-94 adds nothing
+        if impl == "sdpa" and (q_len == 1 or past == 0):
+            return 0                                   # model.py:94-101 (_ignore_causal_mask_sdpa) -> None
+        return 1                                       # model.py:103-127
+
+    @torch.no_grad()
+    def forward(
+        self,
+        generation_id: str,
+        hidden_states: torch.Tensor,
+        attention_mask: Optional[torch.Tensor] = None,
+        position_ids: Optional[torch.LongTensor] = None,
+        past_key_value: Optional[PartialLlamaSinkCache] = None,
+        output_hidden_states: Optional[bool] = None,
+        cache_position: Optional[torch.LongTensor] = None,
+    ):
+        ffi = self._ffi()
+        if not hidden_states.is_cuda:
+            raise RuntimeError("LlamaBlock (B200) needs CUDA tensors: there is no CPU fallback for the span forward")
+        if hidden_states.dtype != torch.bfloat16 or hidden_states.dim() != 3:
+            raise TypeError(f"hidden_states must be bf16 [B, L, h], got {hidden_states.dtype} {tuple(hidden_states.shape)}")
+        output_hidden_states = (output_hidden_states if output_hidden_states is not None
+                                else bool(getattr(self.config, "output_hidden_states", False)))   # model.py:35-37
+        device = hidden_states.device
+        B, L, h = hidden_states.shape
+        if h != self.config.hidden_size:
+            raise ValueError(f"hidden size {h} != config.hidden_size {self.config.hidden_size}")
+        self._ensure_span(device)
+
+        cache = past_key_value
+        gid = generation_id
+        if cache is None:                               # cache-less call: attention over the chunk only
+            sc = self._scratch_cache
+            need = B * (-(-L // 16)) * 16
+            if sc is None or sc.n_pages * sc.page_tokens < need or (sc._k is not None and sc._k.device != device):
+                sc = self._scratch_cache = PartialLlamaSinkCache(1 << 30, 0, page_tokens=16, capacity_tokens=need)
+            cache, gid = sc, _NOCACHE_ID
+            cache.close(gid)
+        elif not gid:
+            raise ValueError("generation_id not provided")   # cache.py:51-52 via model.py:91
+        cache.bind(len(self.layers), self.config.num_key_value_heads, self.head_dim, device)
+        gen = cache.generation(gid)
+        past = gen.length if gen is not None else 0
+
+        if cache_position is None:                      # model.py:39-42
+            if past != 0 and self._causal_flag(attention_mask, L, past):
+                raise ValueError("cache_position must be given when continuing a generation (the reference's default "
+                                 "arange(q_len) would mask by relative index, model.py:39-42,110)")
+            cache_position = torch.arange(0, L, device=device)
+        if position_ids is None:                        # model.py:52-53
+            position_ids = cache_position.unsqueeze(0)
+        if position_ids.dim() != 2 or position_ids.shape[0] != 1 or position_ids.shape[1] != L:
+            raise ValueError("position_ids must be [1, q_len]: the reference's apply_rotary_pos_emb broadcasts one "
+                             "position vector over the batch (modules.py:17-20)")
+        causal = self._causal_flag(attention_mask, L, past)
+
+        if self._table is None or self._table.device != device:
+            self._table = rope_table(self.head_dim, self.rope_theta, self.max_positions, self.rope, device)
+        cs = torch.index_select(self._table, 1, position_ids[0].to(device))       # [2, L, hd] fp32 (model.py:55)
+
+        gen = cache.reserve(gid, B, past + L)
+        max_ctx = past + L
+        ws = self._workspace(B * L, B, max_ctx, device)
+        x = hidden_states.contiguous()
+        out = torch.empty_like(x)
+        all_h = torch.empty(len(self.layers) + 1, B, L, h, dtype=x.dtype, device=device) if output_hidden_states else None
+        kv = cache.kv_desc(gen, max_ctx)
+        ffi.check(ffi.lib.dli_span_forward(
+            self._span, C.byref(kv), B, L, causal, x.data_ptr(), out.data_ptr(), cs[0].data_ptr(), cs[1].data_ptr(),
+            all_h.data_ptr() if all_h is not None else None, ws.data_ptr(), ws.numel(), ffi.current_stream()))
+        self.last_launch_count = ffi.lib.dli_last_launch_count()
+        cache.advance(gid, L)
+        if past_key_value is None:
+            cache.close(gid)
+        res = (out,)
+        if all_h is not None:
+            res = res + (tuple(all_h[i] for i in range(all_h.shape[0])),)
+        return res                                       # model.py:76

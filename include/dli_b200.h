@@ -1,0 +1,196 @@
+/*
+ * dli_b200.h — C ABI of the B200-native span forward (libdli_b200.so).
+ *
+ * The reference (Dylan102938/distributed-llm-inference) is pure Python: it has NO FFI / plugin boundary.
+ * The boundary this library sits behind is the Python interface of its hot path:
+ *   LlamaBlock.forward                     distributed_llm_inference/models/llama/model.py:25-76
+ *   OptimizedLlamaDecoderLayer.forward     distributed_llm_inference/models/llama/modules.py:146-184
+ *   OptimizedLlamaInferenceAttention.fwd   distributed_llm_inference/models/llama/modules.py:36-114
+ *   PartialLlamaSinkCache.update           distributed_llm_inference/models/llama/cache.py:64-135
+ * Each entry point below names the reference lines it replaces; the ctypes stub a maintainer of the
+ * reference would add is in INTEGRATION.md and shipped as distributed_llm_inference_b200/_ffi.py.
+ *
+ * Conventions
+ *   - plain C types only; every function returns an int status (0 = DLI_OK, negative = error) and never
+ *     throws; dli_last_error() returns a thread-local message for the last failure on this thread.
+ *   - every buffer is CALLER-ALLOCATED device memory (in practice PyTorch's allocator) and is never freed
+ *     or retained by the library beyond the call, except weights bound with dli_span_bind_weights, which
+ *     are borrowed until the span is destroyed.  Unless an entry point's comment says otherwise the
+ *     library allocates no device memory.
+ *   - explicit stream argument (a cudaStream_t passed as void*); no hidden synchronisation; the forward
+ *     path does no host allocation.  Per-call state that changes between decode steps (sequence lengths,
+ *     block tables, cos/sin rows) is read from DEVICE memory so that a captured CUDA graph can be replayed.
+ *   - calls that share a workspace must be serialised by the caller (the reference's runtime calls one
+ *     pool function at a time per device).
+ *   - activations and weights are bf16 (DLI_BF16).  Weights are row-major [out_features, in_features]
+ *     exactly as nn.Linear stores them.
+ */
+#ifndef DLI_B200_H
+#define DLI_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLI_VERSION 1
+
+enum dli_status {
+  DLI_OK = 0,
+  DLI_ERR_ARG = -1,          /* bad argument (null pointer, shape not supported, misalignment) */
+  DLI_ERR_CUDA = -2,         /* a CUDA runtime / driver call failed; message has the CUDA error string */
+  DLI_ERR_UNSUPPORTED = -3,  /* valid request outside what the sm_100a kernels implement */
+  DLI_ERR_WORKSPACE = -4     /* workspace too small */
+};
+
+enum dli_dtype { DLI_BF16 = 0 };
+
+typedef void* dli_stream_t; /* cudaStream_t */
+
+int dli_version(void);
+const char* dli_last_error(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Paged KV cache layout (replaces the per-generation torch.cat lists of cache.py:14-15,103-109).
+ * One pool per layer: K pages and V pages are arrays [n_pages][n_kv_heads][page_tokens][head_dim] bf16.
+ * Keys are stored ROTATED (post-RoPE), as the reference stores them (modules.py:76-85).
+ * block_table[b * max_pages + j] = physical page holding tokens [j*page_tokens, (j+1)*page_tokens) of
+ * sequence b.  seq_lens[b] = number of tokens stored for sequence b BEFORE this call.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct dli_kv_desc {
+  void* k_pages;              /* device, layer 0 */
+  void* v_pages;              /* device, layer 0 */
+  int64_t layer_stride_bytes; /* byte distance between consecutive layers' pools */
+  int32_t page_tokens;        /* 16, 32 or 64 */
+  int32_t n_pages;            /* pages per layer pool */
+  const int32_t* block_table; /* device [batch, max_pages] */
+  const int32_t* seq_lens;    /* device [batch]: tokens cached before this call */
+  int32_t max_pages;          /* row length of block_table */
+  int32_t max_ctx;            /* host-side upper bound on seq_lens[b] + q_len for every b (sizes the grid) */
+} dli_kv_desc;
+
+/* ------------------------------------------------------------------------------------------------
+ * Operator-level entry points (one per fused kernel).  Used by the parity tests and by callers that
+ * want to assemble their own layer; dli_span_forward chains the same kernels.
+ * ---------------------------------------------------------------------------------------------- */
+
+/* RMSNorm: y = bf16( w * (s*x) * rsqrt(mean((s*x)^2) + eps) ), fp32 math.  x is fp32 or bf16 [rows, h].
+ * If resid_out != NULL the fp32 copy of x is also written there (entry of a span: bf16 hand-off ->
+ * fp32 residual stream).
+ * Replaces LlamaRMSNorm.forward as called at modules.py:162 (s = 1) and modules.py:179 (s = 2: the
+ * reference normalises hidden_states + residual, i.e. 2*h). eps default there is 1e-6 (modules.py:124-125). */
+int dli_rmsnorm(const void* x, int x_is_f32, const void* weight_bf16, void* y_bf16, float* resid_out,
+                int rows, int h, float eps, float pre_scale, dli_stream_t stream);
+
+/* GEMM epilogues */
+enum dli_gemm_epilogue {
+  DLI_EPI_STORE_F32 = 0,  /* out_f32[m, n]  = acc                                   */
+  DLI_EPI_ADD_F32 = 1,    /* out_f32[m, n] += acc   (fp32 reduction in L2; split-K capable)  */
+  DLI_EPI_STORE_BF16 = 2, /* out_bf16[m, n] = acc                                   */
+  DLI_EPI_SILU_MUL_BF16 = 3 /* w = [gate; up] ([2*n, k]); out_bf16[m, n] = silu(x.gate_n) * (x.up_n) */
+};
+
+/* out[m, n] (+)= sum_k x[m, k] * w[n, k]  — tcgen05/TMEM GEMM fed by TMA, fp32 accumulation.
+ * x bf16 [m, k] row-major (ldx elements), w bf16 [n(*2), k] row-major (nn.Linear layout), out [m, n] (ldo).
+ * k % 8 == 0, ldx % 8 == 0; pointers 16-byte aligned.  m <= 128 takes the weight-streaming (swap-AB,
+ * split-K) path used at decode; larger m the 128x128-tile path used at prefill.
+ * Replaces the seven nn.Linear calls of a layer: q/k/v_proj modules.py:61-63, o_proj modules.py:112,
+ * LlamaMLP gate/up/down modules.py:181 — with the residual adds of modules.py:173,182 (ADD_F32) and
+ * silu(gate)*up (SILU_MUL_BF16) folded into the epilogue. */
+int dli_gemm(const void* x_bf16, int64_t ldx, const void* w_bf16, void* out, int64_t ldo, int m, int n,
+             int k, int epilogue, dli_stream_t stream);
+
+/* RoPE + KV append.  qkv_f32 [tokens, (H + 2*KV) * hd] is the fused q|k|v projection output, token
+ * t = b * q_len + l.  cos/sin are fp32 [q_len, hd] (one position vector shared by the batch, as in the
+ * reference: modules.py:17-20 broadcasts cos [1, L, hd]).  Writes rotated q (bf16 [tokens, H*hd]) and
+ * appends rotated k and v at positions seq_lens[b] + l of sequence b's pages of `layer`.  zero_after != 0
+ * clears qkv_f32 after reading it (it is a split-K accumulation buffer on the decode path).
+ * Replaces apply_rotary_pos_emb modules.py:17-20,73-76 and the append branch of
+ * PartialLlamaSinkCache.update cache.py:103-109. */
+int dli_rope_kv_append(float* qkv_f32, int zero_after, const float* cos, const float* sin, void* q_bf16,
+                       const dli_kv_desc* kv, int layer, int batch, int q_len, int n_heads,
+                       int n_kv_heads, int head_dim, dli_stream_t stream);
+
+/* Scratch floats needed by dli_decode_attention for the given problem (split-K partials). */
+size_t dli_decode_attention_scratch_bytes(int batch, int n_heads, int head_dim, int max_ctx);
+
+/* Decode attention (q_len == 1): out[b, h, :] = softmax(q[b,h,:] . K[b, h/G, 0:T_b, :]^T / sqrt(hd)) . V,
+ * T_b = seq_lens[b] + 1 (the new token must already be appended).  Split-K flash-decode over the
+ * paged cache with fp32 online softmax; GQA by indexing (no repeat_kv copy).  scratch: fp32, at least
+ * dli_decode_attention_scratch_bytes(...) bytes, caller-allocated.
+ * Replaces repeat_kv + QK^T + softmax + PV + head merge, modules.py:87-105, for q_len == 1. */
+int dli_decode_attention(const void* q_bf16, void* out_bf16, const dli_kv_desc* kv, int layer,
+                         int batch, int n_heads, int n_kv_heads, int head_dim, float* scratch,
+                         size_t scratch_bytes, dli_stream_t stream);
+
+/* Prefill attention (q_len >= 1, with or without cached past): queries of a chunk at positions
+ * seq_lens[b] .. seq_lens[b]+q_len-1 attend to keys [0, seq_lens[b] + q_len) (causal == 0: the
+ * reference's default sdpa configuration adds no mask, model.py:94-101) or to keys
+ * [0, seq_lens[b] + l] (causal == 1: eager mask of model.py:103-127).  The chunk's k/v must already be
+ * appended.  Tensor-core flash attention, fp32 online softmax.  Replaces modules.py:87-105. */
+int dli_prefill_attention(const void* q_bf16, void* out_bf16, const dli_kv_desc* kv, int layer,
+                          int batch, int q_len, int n_heads, int n_kv_heads, int head_dim, int causal,
+                          dli_stream_t stream);
+
+/* act_bf16[m, n] = silu(gu_f32[m, n]) * gu_f32[m, n_total + n]; gu is [m, 2*n].  Decode-path companion of
+ * the split-K gate|up GEMM (the activation of LlamaMLP.forward, modules.py:181). If zero_after != 0 the
+ * fp32 input is cleared after it is read (it is a split-K accumulation buffer). */
+int dli_silu_mul(float* gu_f32, void* act_bf16, int m, int n, int zero_after, dli_stream_t stream);
+
+/* out_bf16 = bf16(in_f32), n elements (span exit: fp32 residual stream -> bf16 hand-off tensor). */
+int dli_cast_f32_bf16(const float* in, void* out_bf16, int64_t n, dli_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Span-level entry point: the whole LlamaBlock.forward loop (model.py:59-71) in one call.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct dli_span dli_span; /* host-side object: shapes, borrowed weight pointers, TMA descriptors */
+
+typedef struct dli_span_desc {
+  int32_t hidden_size, intermediate_size, n_heads, n_kv_heads, head_dim, n_layers;
+  int32_t dtype;        /* DLI_BF16 */
+  float eps_input;      /* 1e-6: LlamaRMSNorm(hidden_size) default, modules.py:124 */
+  float eps_post;       /* 1e-6, modules.py:125 */
+  float post_prescale;  /* 2.0: post_attention_layernorm(hidden_states + residual), modules.py:179 */
+} dli_span_desc;
+
+typedef struct dli_layer_weights {
+  const void* wqkv;   /* [(H + 2*KV) * hd, h]  rows: q_proj | k_proj | v_proj   */
+  const void* wo;     /* [h, H * hd]                                            */
+  const void* wgu;    /* [2 * i, h]             rows: gate_proj | up_proj       */
+  const void* wdown;  /* [h, i]                                                 */
+  const void* g_in;   /* [h] input_layernorm.weight                             */
+  const void* g_post; /* [h] post_attention_layernorm.weight                    */
+} dli_layer_weights;
+
+int dli_span_create(const dli_span_desc* desc, dli_span** out);
+int dli_span_destroy(dli_span* span);
+int dli_span_bind_weights(dli_span* span, int layer, const dli_layer_weights* w);
+
+/* Bytes of caller-allocated device workspace dli_span_forward needs for chunks of up to max_tokens
+ * (= batch * q_len) tokens, batch <= max_batch, context <= max_ctx. */
+size_t dli_span_workspace_bytes(const dli_span* span, int max_tokens, int max_batch, int max_ctx);
+
+/* hidden_in / hidden_out: bf16 [batch * q_len, h] (may alias).  cos/sin fp32 [q_len, hd].
+ * Appends q_len tokens per sequence to the cache (the caller advances seq_lens afterwards) and runs
+ * every bound layer: norm -> qkv -> rope/append -> attention -> o_proj(+res) -> norm(2h) -> gate|up
+ * -> silu*up -> down(+res).  all_hidden (nullable): bf16 [n_layers + 1, tokens, h] receives the input of
+ * every layer and the final output (output_hidden_states, model.py:57-61,73-74).
+ * The workspace must be zero-filled ONCE after allocation: the split-K accumulation buffers at its
+ * front are re-zeroed by the kernels that consume them and must read zero at every entry (so a call
+ * that failed half-way requires a fresh memset).
+ * Replaces LlamaBlock.forward model.py:25-76 (mask construction model.py:78-144 is reduced to the
+ * `causal` flag; cos/sin of model.py:55 are inputs so that the reference's int64-truncated tables and
+ * the intended float tables are both host-side choices). */
+int dli_span_forward(dli_span* span, const dli_kv_desc* kv, int batch, int q_len, int causal,
+                     const void* hidden_in, void* hidden_out, const float* cos, const float* sin,
+                     void* all_hidden, void* workspace, size_t workspace_bytes, dli_stream_t stream);
+
+/* Number of kernel launches (incl. memset nodes) the last dli_span_forward on this thread issued. */
+int dli_last_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLI_B200_H */
