@@ -23,7 +23,8 @@ EXPORTS = (
     "dli_version", "dli_last_error", "dli_rmsnorm", "dli_gemm", "dli_rope_kv_append",
     "dli_decode_attention_scratch_bytes", "dli_decode_attention", "dli_prefill_attention", "dli_silu_mul",
     "dli_cast_f32_bf16", "dli_span_create", "dli_span_destroy", "dli_span_bind_weights",
-    "dli_span_workspace_bytes", "dli_span_forward", "dli_last_launch_count",
+    "dli_span_workspace_bytes", "dli_span_forward", "dli_last_launch_count", "dli_span_profile",
+    "dli_span_profile_read",
 )
 
 
@@ -73,6 +74,8 @@ def _load() -> C.CDLL:
         "dli_span_destroy": (C.c_int, [vp]),
         "dli_span_bind_weights": (C.c_int, [vp, i32, C.POINTER(LayerWeights)]),
         "dli_span_workspace_bytes": (sz, [vp, i32, i32, i32]),
+        "dli_span_profile": (C.c_int, [vp, i32]),
+        "dli_span_profile_read": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]),
         "dli_span_forward": (C.c_int, [vp, C.POINTER(KvDesc), i32, i32, i32, vp, vp, vp, vp, vp, vp, sz, vp]),
     }
     for name, (res, args) in sig.items():
@@ -82,6 +85,10 @@ def _load() -> C.CDLL:
 
 
 lib = _load()
+
+
+PROF_CLASSES = ("rmsnorm", "gemm_qkv", "rope_append", "attention", "gemm_o", "gemm_gate_up", "silu_mul",
+                "gemm_down", "cast")
 
 
 def check(rc: int) -> None:

@@ -65,6 +65,10 @@ struct Layer {
   bool bound = false;
   WeightMaps qkv, o, gu, down;
 };
+struct ProfMark {
+  cudaEvent_t ev;
+  int cls;  // DLI_PROF_* of the launches that follow this mark; -1 closes a forward
+};
 struct ActMapKey {
   const void* ptr;
   int rows, cols, box;
@@ -78,6 +82,10 @@ struct dli_span {
   int n_qkv;  // (H + 2 KV) * hd
   std::vector<dli::Layer> layers;
   std::vector<dli::ActMapKey> act_maps;  // activation-side TMA descriptors, keyed by (pointer, shape, box)
+  // optional per-kernel-class timing (dli_span_profile_*): one event at every class boundary of the forward
+  bool profiling = false;
+  std::vector<dli::ProfMark> marks;
+  size_t marks_used = 0;
 };
 
 namespace dli {
@@ -140,6 +148,20 @@ static int act_map(dli_span* s, const void* ptr, int rows, int cols, int box, co
   *out = &s->act_maps.back().map;
   return DLI_OK;
 }
+
+static int prof_mark(dli_span* s, int cls, cudaStream_t st) {
+  if (!s->profiling) return DLI_OK;
+  if (s->marks_used == s->marks.size()) {
+    ProfMark m{nullptr, -1};
+    DLI_CUDA_OK(cudaEventCreate(&m.ev));
+    s->marks.push_back(m);
+  }
+  ProfMark& m = s->marks[s->marks_used++];
+  m.cls = cls;
+  DLI_CUDA_OK(cudaEventRecord(m.ev, st));
+  return DLI_OK;
+}
+#define DLI_MARK(cls) do { if ((rc = prof_mark(s, cls, st))) return rc; } while (0)
 
 // one linear layer of the span: out (+)= x[m, k] . w[n, k]^T through the planned tcgen05 kernel
 static int span_gemm(dli_span* s, const void* x, const WeightMaps& wm, void* out, long long ldo, int m, int n, int k,
@@ -237,7 +259,32 @@ int dli_span_create(const dli_span_desc* desc, dli_span** out) {
   return DLI_OK;
 }
 
+int dli_span_profile(dli_span* s, int enable) {
+  DLI_REQUIRE(s, "dli_span_profile: null span");
+  s->profiling = enable != 0;
+  s->marks_used = 0;
+  return DLI_OK;
+}
+
+int dli_span_profile_read(dli_span* s, float* ms_by_class, int* intervals_by_class) {
+  DLI_REQUIRE(s && ms_by_class && intervals_by_class, "dli_span_profile_read: null pointer");
+  for (int c = 0; c < DLI_PROF_CLASSES; ++c) { ms_by_class[c] = 0.f; intervals_by_class[c] = 0; }
+  if (s->marks_used == 0) return DLI_OK;
+  DLI_CUDA_OK(cudaEventSynchronize(s->marks[s->marks_used - 1].ev));
+  for (size_t i = 0; i + 1 < s->marks_used; ++i) {
+    const int c = s->marks[i].cls;
+    if (c < 0 || c >= DLI_PROF_CLASSES) continue;
+    float ms = 0.f;
+    DLI_CUDA_OK(cudaEventElapsedTime(&ms, s->marks[i].ev, s->marks[i + 1].ev));
+    ms_by_class[c] += ms;
+    intervals_by_class[c] += 1;
+  }
+  s->marks_used = 0;
+  return DLI_OK;
+}
+
 int dli_span_destroy(dli_span* span) {
+  if (span) for (auto& m : span->marks) cudaEventDestroy(m.ev);
   delete span;
   return DLI_OK;
 }
@@ -295,17 +342,21 @@ int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, i
     KvView view;
     if ((rc = kv_view(kv, j, &view))) return rc;
     // input_layernorm (modules.py:162); layer 0 also opens the fp32 residual stream
+    DLI_MARK(DLI_PROF_RMSNORM);
     rc = launch_rmsnorm(j == 0 ? hidden_in : (const void*)w.resid, j != 0, (const __nv_bfloat16*)L.w.g_in, w.xn,
                         j == 0 ? w.resid : nullptr, hs ? hs + (size_t)j * M * h : nullptr, M, h, d.eps_input, 1.0f, st);
     if (rc) return rc;
     // q|k|v projection (modules.py:61-63)
     float* qkv = skinny ? w.qkv_acc : w.qkv;
+    DLI_MARK(DLI_PROF_GEMM_QKV);
     rc = span_gemm(s, w.xn, L.qkv, qkv, s->n_qkv, M, s->n_qkv, h, skinny ? DLI_EPI_ADD_F32 : DLI_EPI_STORE_F32, st);
     if (rc) return rc;
     // RoPE + cache append (modules.py:73-85, cache.py:103-109); re-zeroes the split-K accumulation buffer behind itself
+    DLI_MARK(DLI_PROF_ROPE_APPEND);
     rc = launch_rope_kv_append(qkv, skinny, cos, sin, w.qbuf, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim, st);
     if (rc) return rc;
     // attention core (modules.py:87-105)
+    DLI_MARK(DLI_PROF_ATTENTION);
     if (q_len == 1)
       rc = launch_decode_attention(w.qbuf, w.attn, view, batch, d.n_heads, d.n_kv_heads, d.head_dim, w.dec_scratch,
                                    w.dec_scratch_bytes, st);
@@ -313,26 +364,33 @@ int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, i
       rc = launch_prefill_attention(w.qbuf, w.attn, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim, causal != 0, st);
     if (rc) return rc;
     // o_proj + residual (modules.py:112,173)
+    DLI_MARK(DLI_PROF_GEMM_O);
     rc = span_gemm(s, w.attn, L.o, w.resid, h, M, h, qdim, DLI_EPI_ADD_F32, st);
     if (rc) return rc;
     // post_attention_layernorm of h + h (modules.py:179)
+    DLI_MARK(DLI_PROF_RMSNORM);
     rc = launch_rmsnorm(w.resid, true, (const __nv_bfloat16*)L.w.g_post, w.xn, nullptr, nullptr, M, h, d.eps_post,
                         d.post_prescale, st);
     if (rc) return rc;
     // MLP (modules.py:181): gate|up with silu*up, then down + residual (modules.py:182)
+    DLI_MARK(DLI_PROF_GEMM_GATE_UP);
     if (skinny) {
       rc = span_gemm(s, w.xn, L.gu, w.gu_acc, 2LL * inter, M, 2 * inter, h, DLI_EPI_ADD_F32, st);
       if (rc) return rc;
+      DLI_MARK(DLI_PROF_SILU_MUL);
       rc = launch_silu_mul(w.gu_acc, w.act, M, inter, true, st);
     } else {
       rc = span_gemm(s, w.xn, L.gu, w.act, inter, M, inter, h, DLI_EPI_SILU_MUL_BF16, st);
     }
     if (rc) return rc;
+    DLI_MARK(DLI_PROF_GEMM_DOWN);
     rc = span_gemm(s, w.act, L.down, w.resid, h, M, h, inter, DLI_EPI_ADD_F32, st);
     if (rc) return rc;
   }
+  DLI_MARK(DLI_PROF_CAST);
   if ((rc = launch_cast(w.resid, static_cast<__nv_bfloat16*>(hidden_out), (long long)M * h, st))) return rc;
   if (hs && (rc = launch_cast(w.resid, hs + (size_t)d.n_layers * M * h, (long long)M * h, st))) return rc;
+  DLI_MARK(-1);
   return DLI_OK;
 }
 

@@ -117,6 +117,22 @@ class LlamaBlock(nn.Module):
             self._ws_key = key
         return self._ws
 
+    # ------------------------------------------------------------------ instrumentation (bench.py)
+    def profile(self, enable: bool = True) -> None:
+        """Record a CUDA event at every kernel-class boundary of the following forwards (dli_span_profile)."""
+        ffi = self._ffi()
+        if self._span is None:
+            raise RuntimeError("run one forward before enabling profiling")
+        ffi.check(ffi.lib.dli_span_profile(self._span, int(enable)))
+
+    def profile_read(self):
+        """-> {class: (milliseconds, intervals)} accumulated since the last read."""
+        ffi = self._ffi()
+        ms = (C.c_float * len(ffi.PROF_CLASSES))()
+        cnt = (C.c_int * len(ffi.PROF_CLASSES))()
+        ffi.check(ffi.lib.dli_span_profile_read(self._span, ms, cnt))
+        return {name: (float(ms[i]), int(cnt[i])) for i, name in enumerate(ffi.PROF_CLASSES)}
+
     # ------------------------------------------------------------------ forward
     def _causal_flag(self, attention_mask, q_len: int, past: int) -> int:
         """model.py:78-144 reduced to one bit for the cases without padding."""

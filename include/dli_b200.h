@@ -187,6 +187,20 @@ int dli_span_forward(dli_span* span, const dli_kv_desc* kv, int batch, int q_len
                      const void* hidden_in, void* hidden_out, const float* cos, const float* sin,
                      void* all_hidden, void* workspace, size_t workspace_bytes, dli_stream_t stream);
 
+/* Per-kernel-class timing of dli_span_forward, measured with CUDA events recorded on the call's own stream
+ * at every class boundary (bench.py's roofline figures).  dli_span_profile(span, 1) starts collecting (host-side
+ * cudaEvent objects are created on demand; no device memory); every forward after that appends intervals;
+ * dli_span_profile_read synchronises on the last event, returns the summed milliseconds and the number of
+ * intervals per class since the last read, and resets.  Profiling adds an event record between kernels and is
+ * off by default.  No counterpart in the reference (it has no instrumentation). */
+enum dli_prof_class {
+  DLI_PROF_RMSNORM = 0, DLI_PROF_GEMM_QKV = 1, DLI_PROF_ROPE_APPEND = 2, DLI_PROF_ATTENTION = 3,
+  DLI_PROF_GEMM_O = 4, DLI_PROF_GEMM_GATE_UP = 5, DLI_PROF_SILU_MUL = 6, DLI_PROF_GEMM_DOWN = 7,
+  DLI_PROF_CAST = 8, DLI_PROF_CLASSES = 9
+};
+int dli_span_profile(dli_span* span, int enable);
+int dli_span_profile_read(dli_span* span, float* ms_by_class, int* intervals_by_class);
+
 /* Number of kernel launches (incl. memset nodes) the last dli_span_forward on this thread issued. */
 int dli_last_launch_count(void);
 

@@ -31,7 +31,9 @@ def span_case_inputs(case: SpanCase, dtype, device="cpu"):
 def span_case_weights(case: SpanCase, dtype, device="cpu"):
     shp = syn.SHAPES[case.shape]
     ids = list(range(case.first_layer, case.first_layer + case.n_layers))
-    return syn.make_span_weights(shp, ids, dtype=dtype, device=device, norm_jitter=case.norm_jitter)
+    # always drawn by the CPU generator (what the fixtures were made with), then moved
+    ws = syn.make_span_weights(shp, ids, dtype=dtype, device="cpu", norm_jitter=case.norm_jitter)
+    return [{k: v.to(device) for k, v in w.items()} for w in ws]
 
 
 def run_span_case(case: SpanCase, make_span: Callable, make_cache: Callable, dtype=torch.float32,
@@ -55,6 +57,7 @@ def run_span_case(case: SpanCase, make_span: Callable, make_cache: Callable, dty
 
 def greedy_case_weights(case: GreedyCase, dtype, device="cpu"):
     shp = syn.SHAPES[case.shape]
-    spans = [syn.make_span_weights(shp, list(range(a, b)), dtype=dtype, device=device) for a, b in case.spans]
-    client = syn.make_client_weights(shp, dtype=dtype, device=device)
+    spans = [[{k: v.to(device) for k, v in w.items()} for w in
+              syn.make_span_weights(shp, list(range(a, b)), dtype=dtype, device="cpu")] for a, b in case.spans]
+    client = {k: v.to(device) for k, v in syn.make_client_weights(shp, dtype=dtype, device="cpu").items()}
     return shp, spans, client

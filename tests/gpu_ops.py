@@ -99,7 +99,7 @@ def prefill_attention(q, kv: PagedKV, layer, batch, q_len, H, KV, hd, causal, ma
 
 
 def err_report(name, got, ref):
-    got, ref = got.float(), ref.float()
+    got, ref = got.float().cpu(), ref.float().cpu()
     d = (got - ref).abs()
     scale = ref.abs().max().item() + 1e-12
     idx = torch.nonzero(d == d.max())[0].tolist() if d.numel() else []
