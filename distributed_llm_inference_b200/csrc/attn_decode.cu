@@ -199,4 +199,60 @@ int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const Kv
   return fail(DLI_ERR_UNSUPPORTED, "dli_decode_attention: head_dim %d with GQA group %d is not instantiated", hd, G);
 }
 
+// -------------------------------------------------------------------------------------------------------
+// Allocation-free decode attention.
+//
+// Some users of this library are handed input and output buffers and nothing else: an operator plug-in
+// whose host framework has already claimed all of HBM for its own pool, or a serving loop that must not
+// hit cudaMalloc's implicit device synchronisation (or its failure when the pool is full) in the middle
+// of a request.  They cannot provide the split-K scratch that dli_decode_attention asks for.  For them
+// the partials live in the fixed array below, which is part of the library image: every GPU that loads
+// libdli_b200.so sets aside DLI_STATIC_SCRATCH_BYTES for it until the process exits.
+//
+// Host code must not pass `g_decode_scratch` itself to a kernel: on the host that name is only a handle
+// for the symbol, not a device address.  The address is looked up once per device with
+// cudaGetSymbolAddress while that device is current, and remembered.
+// -------------------------------------------------------------------------------------------------------
+constexpr size_t DLI_STATIC_SCRATCH_BYTES = (size_t)8 << 20;  // 8 MiB
+static __device__ __align__(256) float g_decode_scratch[DLI_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+constexpr int DLI_MAX_DEVICES = 64;
+static float* g_decode_scratch_addr[DLI_MAX_DEVICES] = {nullptr};
+
+static int static_scratch_for_current_device(float** out) {
+  int dev = -1;
+  DLI_CUDA_OK(cudaGetDevice(&dev));
+  DLI_REQUIRE(dev >= 0 && dev < DLI_MAX_DEVICES, "dli_decode_attention_static: device ordinal %d not supported", dev);
+  if (g_decode_scratch_addr[dev] == nullptr) {
+    void* p = nullptr;
+    DLI_CUDA_OK(cudaGetSymbolAddress(&p, g_decode_scratch));
+    DLI_REQUIRE(p != nullptr, "dli_decode_attention_static: cudaGetSymbolAddress returned a null address");
+    g_decode_scratch_addr[dev] = static_cast<float*>(p);
+  }
+  *out = g_decode_scratch_addr[dev];
+  return DLI_OK;
+}
+
 }  // namespace dli
+
+extern "C" int dli_decode_attention_static(const void* q_bf16, void* out_bf16, const dli_kv_desc* kv, int layer, int batch,
+                                           int n_heads, int n_kv_heads, int head_dim, dli_stream_t stream) {
+  using namespace dli;
+  DLI_REQUIRE(batch > 0 && n_heads > 0 && n_kv_heads > 0 && head_dim > 0, "dli_decode_attention_static: bad shape");
+  KvView v;
+  int rc = kv_view(kv, layer, &v);
+  if (rc) return rc;
+  // same split count the launcher will choose, so the size check here is exact
+  const size_t need = (size_t)batch * n_heads * decode_splits(batch, n_kv_heads, v.max_ctx) * (head_dim + 2) * sizeof(float);
+  if (need > DLI_STATIC_SCRATCH_BYTES)
+    return fail(DLI_ERR_WORKSPACE,
+                "dli_decode_attention_static: this problem needs %zu bytes of split-K scratch but the built-in array holds "
+                "%zu; use dli_decode_attention with caller-provided scratch",
+                need, (size_t)DLI_STATIC_SCRATCH_BYTES);
+  float* scratch = nullptr;
+  if ((rc = static_scratch_for_current_device(&scratch))) return rc;
+  // Nothing has to be cleared first: every partial slot the combine step reads is written by this same call
+  // (a split with no tokens still writes m = -inf, l = 0, o = 0), so what the previous call left is never read.
+  return launch_decode_attention((const __nv_bfloat16*)q_bf16, (__nv_bfloat16*)out_bf16, v, batch, n_heads, n_kv_heads,
+                                 head_dim, scratch, DLI_STATIC_SCRATCH_BYTES, (cudaStream_t)stream);
+}

@@ -125,6 +125,24 @@ int dli_decode_attention(const void* q_bf16, void* out_bf16, const dli_kv_desc* 
                          int batch, int n_heads, int n_kv_heads, int head_dim, float* scratch,
                          size_t scratch_bytes, dli_stream_t stream);
 
+/* Decode attention for callers that cannot allocate.  Same computation and arguments as dli_decode_attention,
+ * minus the scratch: the split-K partials go to an 8 MiB array that is built into the library (each GPU that
+ * loads libdli_b200.so holds those 8 MiB until the process exits).  Meant for code that receives only its input
+ * and output buffers — e.g. an operator plug-in inside a host framework that has reserved all of HBM for its own
+ * pool, or a serving loop that cannot afford cudaMalloc's device-wide synchronisation or its failure mid-request.
+ * It never calls cudaMalloc, cudaFree or any allocating library routine.
+ *   - Limit: batch * n_heads * splits * (head_dim + 2) * 4 bytes must fit in 8 MiB (splits <= 32 is chosen from
+ *     batch, n_kv_heads and kv->max_ctx as in dli_decode_attention); larger problems are refused with
+ *     DLI_ERR_WORKSPACE and a message naming both sizes.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress, with that device
+ *     current) and remembers it; make that first call before any stream capture begins.
+ *   - All calls on a device share the one array.  Nothing in it has to be zero beforehand (every slot a call
+ *     reads it has written itself), but two calls that overlap on the GPU — different streams, or graphs
+ *     replayed concurrently — race on it: serialise them.
+ * This entry point has no counterpart in the reference. */
+int dli_decode_attention_static(const void* q_bf16, void* out_bf16, const dli_kv_desc* kv, int layer,
+                                int batch, int n_heads, int n_kv_heads, int head_dim, dli_stream_t stream);
+
 /* Prefill attention (q_len >= 1, with or without cached past): queries of a chunk at positions
  * seq_lens[b] .. seq_lens[b]+q_len-1 attend to keys [0, seq_lens[b] + q_len) (causal == 0: the
  * reference's default sdpa configuration adds no mask, model.py:94-101) or to keys
