@@ -49,6 +49,16 @@ def measured_peaks():
     return 6650.0, 1400.0, "fallback"
 
 
+def measured_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the ncu --set full capture
+    summarised under profiles/ (mean over the four GEMM launches of a layer); None if no capture is recorded."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f).get("gemm_tcgen05_decode_bytes_per_launch")
+    return None
+
+
 class ClockSampler(threading.Thread):
     """Samples SM clock and throttle reasons through NVML while the timed region runs."""
 
@@ -120,6 +130,44 @@ def build_span(shape: syn.LlamaShape, layer_ids, device, rope="float"):
     return blk
 
 
+def gemm_chain_time(blk, shape: syn.LlamaShape, batch: int, dev, reps: int = 5):
+    """Average launch duration of the dominant kernel as it runs in the step: the span's own 4 GEMMs per layer, over
+    every layer's (distinct, 12.9 GB >> L2) weights, back to back on one stream through the C ABI (dli_gemm), CUDA
+    events around the chain.  Unlike the per-class events inside dli_span_forward this keeps programmatic dependent
+    launch active (an event record between two kernels serialises them)."""
+    from distributed_llm_inference_b200 import _ffi
+
+    h, i = shape.hidden_size, shape.intermediate_size
+    qd = shape.num_attention_heads * shape.head_dim
+    nqkv = qd + 2 * shape.num_key_value_heads * shape.head_dim
+    xh = torch.randn(batch, h, device=dev).to(torch.bfloat16)
+    xq = torch.randn(batch, qd, device=dev).to(torch.bfloat16)
+    xi = torch.randn(batch, i, device=dev).to(torch.bfloat16)
+    o_qkv = torch.zeros(batch, nqkv, device=dev)
+    o_h = torch.zeros(batch, h, device=dev)
+    o_act = torch.zeros(batch, i, device=dev, dtype=torch.bfloat16)
+    st = _ffi.current_stream()
+
+    def chain():
+        for layer in blk.layers:
+            a, m = layer.self_attn, layer.mlp
+            for x, w, out, n, k, epi in ((xh, layer._wqkv, o_qkv, nqkv, h, _ffi.EPI_ADD_F32),
+                                         (xq, a.o_proj.weight, o_h, h, qd, _ffi.EPI_ADD_F32),
+                                         (xh, layer._wgu, o_act, i, h, _ffi.EPI_SILU_MUL_BF16),
+                                         (xi, m.down_proj.weight, o_h, h, i, _ffi.EPI_ADD_F32)):
+                _ffi.check(_ffi.lib.dli_gemm(x.data_ptr(), k, w.data_ptr(), out.data_ptr(), n, batch, n, k, epi, st))
+
+    chain()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        chain()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / (reps * 4 * len(blk.layers))      # ms per launch
+
+
 # ---------------------------------------------------------------------------------------------------------
 # CPU baseline: the oracle port of the reference (torch fp32, all host threads) on a bounded sample
 # ---------------------------------------------------------------------------------------------------------
@@ -188,7 +236,7 @@ def run_ours(args):
     total_ctx = PROMPT + W + K + 8 + 32 + 8
 
     blk = build_span(shape, layer_ids, dev)
-    cache = PartialLlamaSinkCache(1 << 20, 4, page_tokens=16, capacity_tokens=n_mb * BATCH * (total_ctx + 16))
+    cache = PartialLlamaSinkCache(1 << 20, 4, page_tokens=16, capacity_tokens=n_mb * BATCH * (total_ctx + 16) + BATCH * 64)
     stage = PipelineStage(blk, cache, rank, world, dev)
     gids = [f"mb{m}" for m in range(n_mb)]
 
@@ -207,10 +255,18 @@ def run_ours(args):
         cache.reserve(g, BATCH, total_ctx)            # block tables stay fixed from here on
 
     # ---- decode: warm-up, then K timed steps ----
+    # one GPU: the whole stage step is one CUDA graph (LlamaBlock.graphed_decode); pipeline: eager + NCCL P2P
     xs = [syn.make_hidden(shape, BATCH, 1, seed=7 + m, device=dev) for m in range(n_mb)] if rank == 0 else None
     pos = PROMPT
+    graph = blk.graphed_decode(gids[0], cache, total_ctx) if (world == 1 and not args.no_graph) else None
+
+    def decode_round(xs, pos):
+        if graph is not None:
+            return [graph.step(xs[0])]
+        return stage.run_round(gids, xs, BATCH, 1, pos, feed_back=True)
+
     for _ in range(W):
-        xs = stage.run_round(gids, xs, BATCH, 1, pos, feed_back=True)
+        xs = decode_round(xs, pos)
         pos += 1
     torch.cuda.synchronize()
     if world > 1:
@@ -221,7 +277,7 @@ def run_ours(args):
     evs = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
     evs[0].record()
     for k in range(K):
-        xs = stage.run_round(gids, xs, BATCH, 1, pos, feed_back=True)
+        xs = decode_round(xs, pos)
         pos += 1
         evs[k + 1].record()
     torch.cuda.synchronize()
@@ -230,7 +286,7 @@ def run_ours(args):
         dist.barrier()
     total_ms = torch.tensor([evs[0].elapsed_time(evs[K])], device=dev)
     lat = sorted(evs[k].elapsed_time(evs[k + 1]) for k in range(K))
-    launches = stage.launches_per_round * K
+    launches = (graph.launches if graph is not None else stage.launches_per_round) * K
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(prefill_ms, op=dist.ReduceOp.MAX)
@@ -253,12 +309,16 @@ def run_ours(args):
     gemm_launches = sum(prof[c][1] for c in GEMM_CLASSES)
     step_prof_ms = sum(v[0] for v in prof.values()) / (n_prof * n_mb)
     gemm_bytes_per_launch = sum(sb["per_gemm_per_layer"].values()) / 4.0
-    gemm_ms_per_launch = gemm_ms / max(1, gemm_launches)
+    gemm_ms_serialised = gemm_ms / max(1, gemm_launches)
+    gemm_ms_per_launch = gemm_chain_time(blk, shape, BATCH, dev)
     achieved = gemm_bytes_per_launch / (gemm_ms_per_launch * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": "gemm_tcgen05_kernel (swap-AB split-K weight streaming; 4 launches/layer)",
                 "achieved": round(achieved, 1), "peak": hbm_peak, "unit": "GB/s", "frac": round(achieved / hbm_peak, 4),
-                "traffic": None, "peak_source": f"MEASURED_PEAKS.json ({peak_kind}, hbm_gbs)",
+                "traffic": measured_traffic(), "peak_source": f"MEASURED_PEAKS.json ({peak_kind}, hbm_gbs)",
                 "bytes_per_launch": gemm_bytes_per_launch, "ms_per_launch": round(gemm_ms_per_launch, 5),
+                "how": "CUDA events around the span's own 4 GEMMs/layer x all layers launched back to back through "
+                       "dli_gemm (programmatic dependent launch active, as in the step)",
+                "ms_per_launch_serialised": round(gemm_ms_serialised, 5),
                 "share_of_step": round(gemm_ms / max(1e-9, sum(v[0] for v in prof.values())), 4)}
     stage_gbs = sb["total"] / (ms_per_step / n_mb * 1e-3) / 1e9
     breakdown = {c: round(v[0] / (n_prof * n_mb), 4) for c, v in prof.items()}
@@ -275,7 +335,10 @@ def run_ours(args):
         t0 = time.perf_counter()
         for k in range(n_e2e):
             x = hin[k & 1].to(dev, non_blocking=True)
-            y = blk(gids[0], x, past_key_value=cache, cache_position=torch.tensor([pos], device=dev))[0]
+            if graph is not None:
+                y = graph.step(x)
+            else:
+                y = blk(gids[0], x, past_key_value=cache, cache_position=torch.tensor([pos], device=dev))[0]
             hout.copy_(y, non_blocking=True)
             torch.cuda.synchronize()               # the caller needs the result before the next token
             pos += 1
@@ -283,8 +346,9 @@ def run_ours(args):
         nbytes = BATCH * shape.hidden_size * 2
         e2e = {"value": round(BATCH * n_e2e / dt, 1), "unit": UNIT, "h2d_bytes_per_step": nbytes,
                "d2h_bytes_per_step": nbytes, "steps": n_e2e,
-               "how": "LlamaBlock.forward per step with pinned-host input copied H2D and output copied D2H, "
-                      "synchronised every step (wall clock)"}
+               "how": ("LlamaBlock.graphed_decode(...).step" if graph is not None else "LlamaBlock.forward") +
+                      " per step with pinned-host input copied H2D and output copied D2H, synchronised every step "
+                      "(wall clock)"}
 
     if rank == 0:
         cpu = cpu_reference_decode(shape, n_total, BATCH, PROMPT, budget_s=args.cpu_budget) if world == 1 else None
@@ -296,7 +360,8 @@ def run_ours(args):
                                    f"{n_mb} micro-batch(es) in flight, {PROMPT}-token prompt, context "
                                    f"{PROMPT + W}..{PROMPT + W + K}; random-init weights, synthetic hidden states",
                        "global_batch": tokens_per_step, "seq_len": PROMPT, "parallelism": f"pp{world}",
-                       "l2": "inputs larger than L2 (12.9 GB of weights streamed per step)", "page_tokens": 16},
+                       "l2": "inputs larger than L2 (12.9 GB of weights streamed per step)", "page_tokens": 16,
+                       "launch": "cuda_graph" if graph is not None else "eager"},
             "p50_ms_per_token": round(lat[len(lat) // 2] / n_mb, 4),
             "prefill_tokens_per_sec": round(n_mb * BATCH * PROMPT / (prefill_ms.item() * 1e-3), 1),
             "prefill_note": "first call, includes one-time descriptor/workspace set-up",
@@ -345,7 +410,12 @@ def main():
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline leg")
+    ap.add_argument("--batch", type=int, default=None, help="override the batch (experiments; the default is the config's 16)")
+    ap.add_argument("--no-graph", action="store_true", help="decode with eager launches instead of the CUDA graph")
     args = ap.parse_args()
+    if args.batch:
+        global BATCH
+        BATCH = args.batch
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -24,7 +24,7 @@ EXPORTS = (
     "dli_decode_attention_scratch_bytes", "dli_decode_attention", "dli_prefill_attention", "dli_silu_mul",
     "dli_cast_f32_bf16", "dli_span_create", "dli_span_destroy", "dli_span_bind_weights",
     "dli_span_workspace_bytes", "dli_span_forward", "dli_last_launch_count", "dli_span_profile",
-    "dli_span_profile_read", "dli_decode_attention_static",
+    "dli_span_profile_read", "dli_decode_attention_static", "dli_kv_evict",
 )
 
 
@@ -69,6 +69,7 @@ def _load() -> C.CDLL:
         "dli_decode_attention": (C.c_int, [vp, vp, C.POINTER(KvDesc), i32, i32, i32, i32, i32, vp, sz, vp]),
         "dli_decode_attention_static": (C.c_int, [vp, vp, C.POINTER(KvDesc), i32, i32, i32, i32, i32, vp]),
         "dli_prefill_attention": (C.c_int, [vp, vp, C.POINTER(KvDesc), i32, i32, i32, i32, i32, i32, i32, vp]),
+        "dli_kv_evict": (C.c_int, [C.POINTER(KvDesc), i32, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp]),
         "dli_silu_mul": (C.c_int, [vp, vp, i32, i32, i32, vp]),
         "dli_cast_f32_bf16": (C.c_int, [vp, vp, i64, vp]),
         "dli_span_create": (C.c_int, [C.POINTER(SpanDesc), C.POINTER(vp)]),

@@ -36,13 +36,16 @@ size_t decode_attn_scratch_bytes(int batch, int H, int hd, int max_ctx) {
 
 template <int HD, int G>
 __global__ void __launch_bounds__(DEC_THREADS) decode_attn_kernel(const __nv_bfloat16* __restrict__ q, KvView kv,
-                                                                  float* __restrict__ scratch, int H, int KV,
+                                                                  float* __restrict__ scratch,
+                                                                  __nv_bfloat16* __restrict__ out, int H, int KV,
                                                                   float scale_log2) {
   constexpr int LPT = HD / 8;                // lanes per token
   constexpr int GPW = 32 / LPT;              // token groups per warp
   constexpr int NG = (DEC_THREADS / 32) * GPW;  // token groups per CTA
   constexpr int UNROLL = G <= 2 ? 4 : 2;
 
+  pdl_trigger();
+  pdl_wait();
   const int split = blockIdx.x, n_splits = gridDim.x, kvh = blockIdx.y, b = blockIdx.z;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int grp = warp * GPW + lane / LPT;   // token group of this lane
@@ -69,24 +72,31 @@ __global__ void __launch_bounds__(DEC_THREADS) decode_attn_kernel(const __nv_bfl
   }
 
   const int32_t* bt = kv.block_table + (long long)b * kv.max_pages;
-  // warp-uniform trip count: every lane takes part in the shuffles of every iteration
-  for (int t0 = t_begin; t0 < t_end; t0 += NG * UNROLL) {
-    const int t = t0 + grp;
-    uint4 kk[UNROLL], vv[UNROLL];
-    bool ok[UNROLL];
+  // K/V rows of tokens t0 + grp + u * NG, u < UNROLL (zeros past the end of the split)
+  auto fetch = [&](int t0, uint4 (&kk)[UNROLL], uint4 (&vv)[UNROLL]) {
 #pragma unroll
     for (int u = 0; u < UNROLL; ++u) {
-      const int tt = t + u * NG;
-      ok[u] = tt < t_end;
+      const int tt = t0 + grp + u * NG;
       kk[u] = make_uint4(0, 0, 0, 0);
       vv[u] = make_uint4(0, 0, 0, 0);
-      if (ok[u]) {
+      if (tt < t_end) {
         const int page = bt[tt / kv.page_tokens], slot = tt % kv.page_tokens;
         const long long off = (((long long)page * KV + kvh) * kv.page_tokens + slot) * HD + dl;
         kk[u] = ld_nc_v4(kv.k + off);
         vv[u] = ld_nc_v4(kv.v + off);
       }
     }
+  };
+  uint4 kk[UNROLL], vv[UNROLL], nk[UNROLL], nv[UNROLL];
+  fetch(t_begin, kk, vv);
+  // warp-uniform trip count: every lane takes part in the shuffles of every iteration.  The next iteration's
+  // rows are requested before this iteration's arithmetic (register double buffering) so that HBM latency is
+  // overlapped instead of paid once per iteration.
+  for (int t0 = t_begin; t0 < t_end; t0 += NG * UNROLL) {
+    fetch(t0 + NG * UNROLL, nk, nv);
+    bool ok[UNROLL];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) ok[u] = t0 + grp + u * NG < t_end;
     float s[UNROLL][G];
 #pragma unroll
     for (int u = 0; u < UNROLL; ++u) {
@@ -123,6 +133,8 @@ __global__ void __launch_bounds__(DEC_THREADS) decode_attn_kernel(const __nv_bfl
         for (int j = 0; j < 8; ++j) o[g][j] = fmaf(pw, vf[j], o[g][j]);
       }
     }
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) { kk[u] = nk[u]; vv[u] = nv[u]; }
   }
 
   // merge the NG token groups of the CTA through shared memory
@@ -149,15 +161,21 @@ __global__ void __launch_bounds__(DEC_THREADS) decode_attn_kernel(const __nv_bfl
         O = fmaf(sm_o[i][g][d], w, O);
       }
     }
-    float* dst = scratch + (((long long)b * H + kvh * G + g) * n_splits + split) * (HD + 2);
-    dst[d] = O;
-    if (d == 0) { dst[HD] = M; dst[HD + 1] = L; }
+    if (n_splits == 1) {  // the whole context in one CTA: normalise and store, no combine pass
+      out[((long long)b * H + kvh * G + g) * HD + d] = __float2bfloat16_rn(O / L);
+    } else {
+      float* dst = scratch + (((long long)b * H + kvh * G + g) * n_splits + split) * (HD + 2);
+      dst[d] = O;
+      if (d == 0) { dst[HD] = M; dst[HD + 1] = L; }
+    }
   }
 }
 
 template <int HD>
 __global__ void __launch_bounds__(HD) decode_combine_kernel(const float* __restrict__ scratch, __nv_bfloat16* __restrict__ out,
                                                             int H, int n_splits) {
+  pdl_trigger();
+  pdl_wait();
   const int h = blockIdx.x, b = blockIdx.y, d = threadIdx.x;
   const float* src = scratch + ((long long)b * H + h) * n_splits * (HD + 2);
   float M = -INFINITY;
@@ -175,11 +193,11 @@ template <int HD, int G>
 static int launch_dec(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV, int splits,
                       float* scratch, cudaStream_t st) {
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
-  decode_attn_kernel<HD, G><<<dim3(splits, KV, batch), DEC_THREADS, 0, st>>>(q, kv, scratch, H, KV, scale_log2);
-  DLI_CHECK_LAUNCH("decode_attn_kernel");
-  decode_combine_kernel<HD><<<dim3(H, batch), HD, 0, st>>>(scratch, out, H, splits);
-  DLI_CHECK_LAUNCH("decode_combine_kernel");
-  return DLI_OK;
+  int rc = launch_kernel("decode_attn_kernel", decode_attn_kernel<HD, G>, dim3(splits, KV, batch), dim3(DEC_THREADS), 0, st, q,
+                         kv, scratch, out, H, KV, scale_log2);
+  if (rc || splits == 1) return rc;
+  return launch_kernel("decode_combine_kernel", decode_combine_kernel<HD>, dim3(H, batch), dim3(HD), 0, st,
+                       (const float*)scratch, out, H, splits);
 }
 
 int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV, int hd,

@@ -56,6 +56,8 @@ __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const __nv_bfl
   extern __shared__ __align__(128) uint8_t pf_smem[];
   const uint32_t sQ = smem_u32(pf_smem), sK = sQ + PF_BM * HD * 2, sV = sK + PF_BN * HD * 2;
 
+  pdl_trigger();
+  pdl_wait();
   const int m0 = blockIdx.x * PF_BM, h = blockIdx.y, b = blockIdx.z;
   const int kvh = h / (H / KV);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -215,9 +217,8 @@ static int launch_pf(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& k
   }
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
   dim3 grid((q_len + PF_BM - 1) / PF_BM, H, batch);
-  prefill_attn_kernel<HD><<<grid, PF_THREADS, smem, st>>>(q, out, kv, q_len, H, KV, causal ? 1 : 0, scale_log2);
-  DLI_CHECK_LAUNCH("prefill_attn_kernel");
-  return DLI_OK;
+  return launch_kernel("prefill_attn_kernel", prefill_attn_kernel<HD>, grid, dim3(PF_THREADS), smem, st, q, out, kv, q_len, H,
+                       KV, causal ? 1 : 0, scale_log2);
 }
 
 int launch_prefill_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H,

@@ -39,6 +39,29 @@ void reset_launch_count();
   } while (0)
 
 int sm_count();  // SMs of the current device (cached)
+bool pdl_enabled();  // programmatic dependent launch for the span's kernel chain (DLI_NO_PDL=1 turns it off)
+
+// Launch with the programmatic-stream-serialization attribute: the kernel may begin (prologue, weight prefetch)
+// while its predecessor in the stream is still running; it must execute pdl_wait() before touching anything the
+// predecessor produces or still reads.
+template <typename... KArgs, typename... Args>
+int launch_kernel(const char* name, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                  Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+  if (e != cudaSuccess) return fail(DLI_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(e));
+  count_launch();
+  return DLI_OK;
+}
 
 // ---- internal launchers shared between the op-level ABI and the span runner ------------------------
 struct KvView {
@@ -71,6 +94,8 @@ int launch_rmsnorm(const void* x, bool x_is_f32, const __nv_bfloat16* w, __nv_bf
 int launch_rope_kv_append(float* qkv, bool zero_after, const float* cos, const float* sin, __nv_bfloat16* q_out,
                           const KvView& kv, int batch, int q_len, int H, int KV, int hd, cudaStream_t st);
 int launch_silu_mul(float* gu, __nv_bfloat16* act, int m, int n, bool zero_after, cudaStream_t st);
+int launch_kv_evict(const dli_kv_desc* kv, int n_layers, int batch, int KV, int hd, int cur_len, int window, int sinks,
+                    int n_new, const float* cos_hist, const float* sin_hist, cudaStream_t st);
 int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st);
 size_t decode_attn_scratch_bytes(int batch, int H, int hd, int max_ctx);
 int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV,
@@ -80,6 +105,10 @@ int launch_prefill_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const K
 
 // ---- device helpers -------------------------------------------------------------------------------
 #ifdef __CUDACC__
+// Programmatic dependent launch: wait until the previous kernel of the stream has completed and its writes are
+// visible / let the next kernel of the stream start its prologue.  Both are no-ops without the launch attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

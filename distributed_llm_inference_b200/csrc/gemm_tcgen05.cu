@@ -19,6 +19,8 @@
 // Pipelines: smem full/empty mbarrier ring (TMA <-> MMA), one tmem_full mbarrier (MMA -> epilogue).
 #include "common.cuh"
 
+#include <stdlib.h>
+
 namespace dli {
 
 constexpr int BM = 128;  // A-tile rows = UMMA_M = TMEM lanes
@@ -116,7 +118,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
   constexpr int B_TILE_BYTES = BN * BK * 2;
   constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
   constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
-  static_assert(!(SWAP && EPI == DLI_EPI_SILU_MUL_BF16), "SiLU epilogue is token-major only");
 
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t bars[2 * MAX_STAGES + 1];
@@ -130,9 +131,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
 
   const int kb0 = blockIdx.z * p.kb_per_split;
   const int kb1 = min(kb0 + p.kb_per_split, p.k_blocks);
-  const int a_row0 = blockIdx.x * BM;
-  const int b_row0 = blockIdx.y * (EPI == DLI_EPI_SILU_MUL_BF16 ? BN / 2 : BN);
+  const int a_row0 = blockIdx.x * ((SWAP && EPI == DLI_EPI_SILU_MUL_BF16) ? BM / 2 : BM);
+  const int b_row0 = blockIdx.y * ((!SWAP && EPI == DLI_EPI_SILU_MUL_BF16) ? BN / 2 : BN);
 
+  pdl_trigger();  // the next kernel of the stream may start its own prologue / weight prefetch
   if (threadIdx.x == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
@@ -157,19 +159,42 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
   if (kb1 > kb0) {
     if (warp == 0) {
       if (lane == 0) {  // ===== TMA producer =====
-        int s = 0;
-        uint32_t ph = 0;
-        for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(empty0 + 8 * s, ph ^ 1);
+        // The weight operand does not depend on the previous kernel of the stream: under programmatic dependent
+        // launch its first `stages` tiles are requested BEFORE griddepcontrol.wait, so weights keep streaming from
+        // HBM while the predecessor drains; the activation operand is requested after the wait.
+        auto load_weights = [&](int s, int kb) {
           const uint32_t a_dst = tiles + s * STAGE_BYTES, b_dst = a_dst + A_TILE_BYTES;
-          mbar_expect_tx(full0 + 8 * s, STAGE_BYTES);
-          tma_load_2d(a_dst, &tma_a, full0 + 8 * s, kb * BK, a_row0);
-          if (EPI == DLI_EPI_SILU_MUL_BF16) {  // gate rows then up rows of the same features
+          if (SWAP && EPI == DLI_EPI_SILU_MUL_BF16) {  // 64 gate rows + 64 up rows of the same 64 features
+            tma_load_2d(a_dst, &tma_a, full0 + 8 * s, kb * BK, a_row0);
+            tma_load_2d(a_dst + A_TILE_BYTES / 2, &tma_a, full0 + 8 * s, kb * BK, p.up_row_offset + a_row0);
+          } else if (SWAP) {
+            tma_load_2d(a_dst, &tma_a, full0 + 8 * s, kb * BK, a_row0);
+          } else if (EPI == DLI_EPI_SILU_MUL_BF16) {  // gate rows then up rows of the same features
             tma_load_2d(b_dst, &tma_b, full0 + 8 * s, kb * BK, b_row0);
             tma_load_2d(b_dst + B_TILE_BYTES / 2, &tma_b, full0 + 8 * s, kb * BK, p.up_row_offset + b_row0);
           } else {
             tma_load_2d(b_dst, &tma_b, full0 + 8 * s, kb * BK, b_row0);
           }
+        };
+        auto load_acts = [&](int s, int kb) {
+          const uint32_t a_dst = tiles + s * STAGE_BYTES, b_dst = a_dst + A_TILE_BYTES;
+          if (SWAP) tma_load_2d(b_dst, &tma_b, full0 + 8 * s, kb * BK, b_row0);
+          else tma_load_2d(a_dst, &tma_a, full0 + 8 * s, kb * BK, a_row0);
+        };
+        const int n_pre = min(stages, kb1 - kb0);
+        for (int i = 0; i < n_pre; ++i) {  // fresh barriers: every slot is free
+          mbar_expect_tx(full0 + 8 * i, STAGE_BYTES);
+          load_weights(i, kb0 + i);
+        }
+        pdl_wait();
+        for (int i = 0; i < n_pre; ++i) load_acts(i, kb0 + i);
+        int s = n_pre == stages ? 0 : n_pre;
+        uint32_t ph = n_pre == stages ? 1 : 0;
+        for (int kb = kb0 + n_pre; kb < kb1; ++kb) {
+          mbar_wait(empty0 + 8 * s, ph ^ 1);
+          mbar_expect_tx(full0 + 8 * s, STAGE_BYTES);
+          load_weights(s, kb);
+          load_acts(s, kb);
           if (++s == stages) { s = 0; ph ^= 1; }
         }
       }
@@ -194,6 +219,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
         umma_commit(tmem_full);  // accumulator complete
       }
     } else {  // ===== epilogue: TMEM -> registers -> global =====
+      pdl_wait();  // the output buffers belong to the predecessor until it has completed
       mbar_wait(tmem_full, 0);
       tcgen05_fence_after();
       const int q = warp & 3;  // TMEM lane quarter this warp may read
@@ -201,25 +227,66 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16);
       uint32_t v[16];
       if (SWAP) {
-        // lane = feature, column = token
-        const bool f_ok = arow < p.n_features;
+        // lane = feature, column = token.  The accumulator is transposed through shared memory (the operand ring
+        // is idle once tmem_full has fired) so that global traffic is 128-bit and coalesced along the feature
+        // axis: one red.global.add.v4.f32 per 4 features instead of 4 scalar reductions.
+        float* stage_f = reinterpret_cast<float*>(smem_raw + (tiles - smem_u32(smem_raw)));  // [BN tokens][128 lanes]
+        const int lane_row = q * 32 + lane;
 #pragma unroll 1
         for (int c0 = 0; c0 < BN; c0 += 16) {
           tmem_ld16(taddr + c0, v);
           tmem_ld_wait();
-          if (f_ok) {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const int tok = b_row0 + c0 + j;
-              if (tok < p.m_tokens) {
-                const float acc = __uint_as_float(v[j]);
-                if (EPI == DLI_EPI_ADD_F32) {
-                  float* o = (float*)p.out + (long long)tok * p.ldo + arow;
-                  asm volatile("red.global.add.f32 [%0], %1;" ::"l"(o), "f"(acc) : "memory");
-                } else if (EPI == DLI_EPI_STORE_F32) {
-                  ((float*)p.out)[(long long)tok * p.ldo + arow] = acc;
+          for (int j = 0; j < 16; ++j) stage_f[(c0 + j) * BM + lane_row] = __uint_as_float(v[j]);
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
+        const int e = threadIdx.x - 64;  // 0..127
+        if (EPI == DLI_EPI_SILU_MUL_BF16) {
+          // lanes 0..63 hold gate, 64..127 up of features a_row0 .. a_row0 + 63; 4 features per thread and token
+          for (int idx = e; idx < BN * 16; idx += 128) {
+            const int t = idx >> 4, f = (idx & 15) * 4;
+            const int tok = b_row0 + t, feat = a_row0 + f;
+            if (tok < p.m_tokens && feat < p.n_features) {
+              const float4 g4 = *reinterpret_cast<const float4*>(stage_f + t * BM + f);
+              const float4 u4 = *reinterpret_cast<const float4*>(stage_f + t * BM + 64 + f);
+              __nv_bfloat16* o = (__nv_bfloat16*)p.out + (long long)tok * p.ldo + feat;
+              if (feat + 4 <= p.n_features) {
+                *reinterpret_cast<uint2*>(o) = make_uint2(pack_bf16(silu(g4.x) * u4.x, silu(g4.y) * u4.y),
+                                                          pack_bf16(silu(g4.z) * u4.z, silu(g4.w) * u4.w));
+              } else {
+                const float gg[4] = {g4.x, g4.y, g4.z, g4.w}, uu[4] = {u4.x, u4.y, u4.z, u4.w};
+                for (int j = 0; j < 4 && feat + j < p.n_features; ++j) o[j] = __float2bfloat16_rn(silu(gg[j]) * uu[j]);
+              }
+            }
+          }
+        } else {
+          for (int idx = e; idx < BN * 32; idx += 128) {
+            const int t = idx >> 5, f = (idx & 31) * 4;
+            const int tok = b_row0 + t, feat = a_row0 + f;
+            if (tok < p.m_tokens && feat < p.n_features) {
+              const float4 a4 = *reinterpret_cast<const float4*>(stage_f + t * BM + f);
+              const bool full = feat + 4 <= p.n_features;
+              if (EPI == DLI_EPI_STORE_BF16) {
+                __nv_bfloat16* o = (__nv_bfloat16*)p.out + (long long)tok * p.ldo + feat;
+                if (full) {
+                  *reinterpret_cast<uint2*>(o) = make_uint2(pack_bf16(a4.x, a4.y), pack_bf16(a4.z, a4.w));
                 } else {
-                  ((__nv_bfloat16*)p.out)[(long long)tok * p.ldo + arow] = __float2bfloat16_rn(acc);
+                  const float aa[4] = {a4.x, a4.y, a4.z, a4.w};
+                  for (int j = 0; j < 4 && feat + j < p.n_features; ++j) o[j] = __float2bfloat16_rn(aa[j]);
+                }
+              } else {
+                float* o = (float*)p.out + (long long)tok * p.ldo + feat;
+                if (full && EPI == DLI_EPI_ADD_F32) {
+                  asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o), "f"(a4.x), "f"(a4.y), "f"(a4.z), "f"(a4.w)
+                               : "memory");
+                } else if (full) {
+                  *reinterpret_cast<float4*>(o) = a4;
+                } else {
+                  const float aa[4] = {a4.x, a4.y, a4.z, a4.w};
+                  for (int j = 0; j < 4 && feat + j < p.n_features; ++j) {
+                    if (EPI == DLI_EPI_ADD_F32) atomicAdd(o + j, aa[j]);
+                    else o[j] = aa[j];
+                  }
                 }
               }
             }
@@ -353,9 +420,7 @@ static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const Ge
     DLI_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
     configured = true;
   }
-  kern<<<grid, GEMM_THREADS, smem, st>>>(ta, tb, p);
-  DLI_CHECK_LAUNCH("gemm_tcgen05_kernel");
-  return DLI_OK;
+  return launch_kernel("gemm_tcgen05_kernel", kern, grid, dim3(GEMM_THREADS), smem, st, ta, tb, p);
 }
 
 template <int BN, bool SWAP>
@@ -372,17 +437,25 @@ GemmPlan plan_gemm(int m, int n, int k, int epilogue) {
   GemmPlan g{};
   g.k_blocks = (k + BK - 1) / BK;
   const int sms = sm_count();
-  if (m <= 128 && epilogue != DLI_EPI_SILU_MUL_BF16) {
+  if (m <= 128) {
+    const bool fused_silu = epilogue == DLI_EPI_SILU_MUL_BF16;  // 64 gate + 64 up rows per CTA, never split
     g.swap = true;
     g.bn = m <= 16 ? 16 : m <= 32 ? 32 : m <= 64 ? 64 : 128;
-    g.a_box_rows = BM;       // weights
-    g.b_box_rows = g.bn;     // tokens
-    const int tiles = (n + BM - 1) / BM;
+    g.a_box_rows = fused_silu ? BM / 2 : BM;  // weights
+    g.b_box_rows = g.bn;                      // tokens
+    const int tiles = fused_silu ? (n + BM / 2 - 1) / (BM / 2) : (n + BM - 1) / BM;
     int splits = 1;
     if (epilogue == DLI_EPI_ADD_F32) {
       // two co-resident CTAs per SM keep ~200 KB of weight tiles in flight per SM; every split keeps >= 4 k-blocks
-      const int want = (2 * sms) / tiles;
-      splits = max(1, min(want, g.k_blocks / 4));
+      static int min_kb = 0, ctas_per_sm_x2 = 0;
+      if (!min_kb) {
+        const char* e = getenv("DLI_MIN_KB");
+        min_kb = e ? max(1, atoi(e)) : 4;
+        const char* f = getenv("DLI_FILL_X2");
+        ctas_per_sm_x2 = f ? max(1, atoi(f)) : 4;  // target CTAs per SM, times two
+      }
+      const int want = (ctas_per_sm_x2 * sms / 2) / tiles;
+      splits = max(1, min(want, g.k_blocks / min_kb));
       splits = min(splits, 32);
     }
     g.kb_per_split = (g.k_blocks + splits - 1) / splits;
@@ -428,6 +501,14 @@ int launch_gemm_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const CUte
   p.stages = g.stages;
   p.up_row_offset = n;
   dim3 grid(g.grid_x, g.grid_y, g.splits);
+  if (g.swap && epilogue == DLI_EPI_SILU_MUL_BF16) {
+    switch (g.bn) {
+      case 16: return launch_variant<16, DLI_EPI_SILU_MUL_BF16, true>(tmap_w, tmap_x, p, grid, st);
+      case 32: return launch_variant<32, DLI_EPI_SILU_MUL_BF16, true>(tmap_w, tmap_x, p, grid, st);
+      case 64: return launch_variant<64, DLI_EPI_SILU_MUL_BF16, true>(tmap_w, tmap_x, p, grid, st);
+      default: return launch_variant<128, DLI_EPI_SILU_MUL_BF16, true>(tmap_w, tmap_x, p, grid, st);
+    }
+  }
   if (g.swap) {
     // A = weights, B = tokens
     switch (g.bn) {

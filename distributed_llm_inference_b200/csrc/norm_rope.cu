@@ -33,6 +33,8 @@ __global__ void __launch_bounds__(NORM_THREADS) rmsnorm_kernel(const void* __res
                                                                float s) {
   __shared__ float red[NORM_THREADS / 32];
   __shared__ float rinv;
+  pdl_trigger();
+  pdl_wait();
   const long long base = (long long)blockIdx.x * h;
   float ss = 0.f;
   float v[8];
@@ -75,12 +77,8 @@ int launch_rmsnorm(const void* x, bool x_is_f32, const __nv_bfloat16* w, __nv_bf
                    __nv_bfloat16* copy_out, int rows, int h, float eps, float pre_scale, cudaStream_t st) {
   DLI_REQUIRE(x && w && y, "dli_rmsnorm: null pointer");
   DLI_REQUIRE(rows > 0 && h > 0 && h % 8 == 0, "dli_rmsnorm: rows=%d h=%d (h must be a positive multiple of 8)", rows, h);
-  if (x_is_f32)
-    rmsnorm_kernel<true><<<rows, NORM_THREADS, 0, st>>>(x, w, y, resid_out, copy_out, h, eps, pre_scale);
-  else
-    rmsnorm_kernel<false><<<rows, NORM_THREADS, 0, st>>>(x, w, y, resid_out, copy_out, h, eps, pre_scale);
-  DLI_CHECK_LAUNCH("rmsnorm_kernel");
-  return DLI_OK;
+  return launch_kernel("rmsnorm_kernel", x_is_f32 ? rmsnorm_kernel<true> : rmsnorm_kernel<false>, dim3(rows),
+                       dim3(NORM_THREADS), 0, st, x, w, y, resid_out, copy_out, h, eps, pre_scale);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -95,6 +93,8 @@ __global__ void __launch_bounds__(ROPE_THREADS) rope_kv_append_kernel(float* __r
                                                                       const float* __restrict__ sinT,
                                                                       __nv_bfloat16* __restrict__ q_out, KvView kv,
                                                                       int q_len, int H, int KV, int hd) {
+  pdl_trigger();
+  pdl_wait();
   const int t = blockIdx.x;
   const int b = t / q_len, l = t - b * q_len;
   const int half = hd >> 1;
@@ -107,7 +107,8 @@ __global__ void __launch_bounds__(ROPE_THREADS) rope_kv_append_kernel(float* __r
   const float* sn = sinT + (long long)l * hd;
 
   const int pairs2 = (H + KV) * half / 2;  // work items: two adjacent d per thread
-  for (int it = threadIdx.x; it < pairs2; it += ROPE_THREADS) {
+  const int tid = blockIdx.y * ROPE_THREADS + threadIdx.x, stride = gridDim.y * ROPE_THREADS;  // a token's work is cut over gridDim.y CTAs
+  for (int it = tid; it < pairs2; it += stride) {
     const int p = it * 2;
     const int head = p / half, d = p - head * half;
     float* x = row + head * hd + d;
@@ -131,7 +132,7 @@ __global__ void __launch_bounds__(ROPE_THREADS) rope_kv_append_kernel(float* __r
     }
   }
   float* vrow = row + (H + KV) * hd;
-  for (int e = threadIdx.x * 4; e < KV * hd; e += ROPE_THREADS * 4) {
+  for (int e = tid * 4; e < KV * hd; e += stride * 4) {
     const float4 a = *reinterpret_cast<const float4*>(vrow + e);
     const int kvh = e / hd, d = e - kvh * hd;
     __nv_bfloat16* dst = kv.v + (((long long)page * KV + kvh) * kv.page_tokens + slot) * hd + d;
@@ -145,9 +146,12 @@ int launch_rope_kv_append(float* qkv, bool zero_after, const float* cos, const f
   DLI_REQUIRE(qkv && cos && sin && q_out, "dli_rope_kv_append: null pointer");
   DLI_REQUIRE(batch > 0 && q_len > 0, "dli_rope_kv_append: batch=%d q_len=%d", batch, q_len);
   DLI_REQUIRE(hd % 8 == 0 && H % KV == 0, "dli_rope_kv_append: head_dim %% 8 and H %% KV must be 0 (hd=%d H=%d KV=%d)", hd, H, KV);
-  rope_kv_append_kernel<<<batch * q_len, ROPE_THREADS, 0, st>>>(qkv, zero_after ? 1 : 0, cos, sin, q_out, kv, q_len, H, KV, hd);
-  DLI_CHECK_LAUNCH("rope_kv_append_kernel");
-  return DLI_OK;
+  // few tokens (decode): spread each token over several CTAs so the kernel is not one latency chain per token
+  const int items = (H + KV) * hd / 4;
+  int ny = 1;
+  if (batch * q_len < 2 * sm_count()) ny = std::max(1, std::min(8, items / ROPE_THREADS));
+  return launch_kernel("rope_kv_append_kernel", rope_kv_append_kernel, dim3(batch * q_len, ny), dim3(ROPE_THREADS), 0, st, qkv,
+                       zero_after ? 1 : 0, cos, sin, q_out, kv, q_len, H, KV, hd);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -155,6 +159,8 @@ int launch_rope_kv_append(float* qkv, bool zero_after, const float* cos, const f
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) silu_mul_kernel(float* __restrict__ gu, __nv_bfloat16* __restrict__ act, int m, int n,
                                                        int zero_after) {
+  pdl_trigger();
+  pdl_wait();
   const long long total4 = (long long)m * n / 4;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (long long)gridDim.x * blockDim.x) {
     const long long e = i * 4;
@@ -177,12 +183,12 @@ int launch_silu_mul(float* gu, __nv_bfloat16* act, int m, int n, bool zero_after
   DLI_REQUIRE(m > 0 && n > 0 && n % 4 == 0, "dli_silu_mul: m=%d n=%d (n must be a multiple of 4)", m, n);
   const long long total4 = (long long)m * n / 4;
   const int blocks = (int)std::min<long long>((total4 + 255) / 256, (long long)sm_count() * 8);
-  silu_mul_kernel<<<blocks, 256, 0, st>>>(gu, act, m, n, zero_after ? 1 : 0);
-  DLI_CHECK_LAUNCH("silu_mul_kernel");
-  return DLI_OK;
+  return launch_kernel("silu_mul_kernel", silu_mul_kernel, dim3(blocks), dim3(256), 0, st, gu, act, m, n, zero_after ? 1 : 0);
 }
 
 __global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long n4) {
+  pdl_trigger();
+  pdl_wait();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
     const float4 a = *reinterpret_cast<const float4*>(in + i * 4);
     *reinterpret_cast<uint2*>(out + i * 4) = make_uint2(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w));
@@ -192,9 +198,98 @@ __global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ in,
 int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st) {
   DLI_REQUIRE(in && out && n > 0 && n % 4 == 0, "dli_cast_f32_bf16: n=%lld must be a positive multiple of 4", n);
   const int blocks = (int)std::min<long long>((n / 4 + 255) / 256, (long long)sm_count() * 8);
-  cast_kernel<<<blocks, 256, 0, st>>>(in, out, n / 4);
-  DLI_CHECK_LAUNCH("cast_kernel");
-  return DLI_OK;
+  return launch_kernel("cast_kernel", cast_kernel, dim3(blocks), dim3(256), 0, st, in, out, n / 4);
+}
+
+
+// ---------------------------------------------------------------------------------------------------
+// Attention-sink eviction (PartialLlamaSinkCache.update, cache.py:111-133, with _get_rerotation_cos_sin
+// cache.py:21-48): when n new tokens would reach the window W, the cache becomes
+//   [ first `sinks` tokens | re-rotated last (W - sinks - n) keys | (the n new tokens, appended afterwards) ]
+// and V is sliced the same way without rotation.  Done in place on the pages, for every layer of the span in one
+// launch: CTA = (kv head, sequence, layer) walks its kept tokens left to right in chunks (read chunk, barrier,
+// write chunk); destinations always lie at or before sources, so a chunk never overwrites unread data.
+// rc = cos[s+n+i] cos[s+i] + sin[s+n+i] sin[s+i],  rs = -sin[s+n+i] cos[s+i] + cos[s+n+i] sin[s+i]   (cache.py:36-41)
+// k' = k rc + rotate_half(k) rs                                                (SinkCache._apply_key_rotary_pos_emb)
+// cos/sin are the generation's cos/sin history (rows of its first W positions), fp32 [W, hd].
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) kv_evict_kernel(__nv_bfloat16* __restrict__ k_base, __nv_bfloat16* __restrict__ v_base,
+                                                       long long layer_stride, const int32_t* __restrict__ block_table,
+                                                       int max_pages, int page_tokens, int KV, int hd, int cur_len, int window,
+                                                       int sinks, int n_new, const float* __restrict__ cos_hist,
+                                                       const float* __restrict__ sin_hist) {
+  pdl_trigger();
+  pdl_wait();
+  const int kvh = blockIdx.x, b = blockIdx.y, layer = blockIdx.z;
+  __nv_bfloat16* kp = k_base + (long long)layer * layer_stride;
+  __nv_bfloat16* vp = v_base + (long long)layer * layer_stride;
+  const int32_t* bt = block_table + (long long)b * max_pages;
+  const int keep = window - sinks - n_new;
+  const int src0 = cur_len - keep, dst0 = sinks;
+  const int half = hd >> 1;
+  const int tpt = hd / 16;                 // threads per token: 8 elements of each half per thread
+  const int tpi = 256 / tpt;               // tokens per iteration
+  const int ti = threadIdx.x / tpt, d0 = (threadIdx.x % tpt) * 8;
+  auto addr = [&](int tok) {
+    const int page = bt[tok / page_tokens], slot = tok % page_tokens;
+    return (((long long)page * KV + kvh) * page_tokens + slot) * hd + d0;
+  };
+  for (int i0 = 0; i0 < keep; i0 += tpi) {
+    const int i = i0 + ti;
+    uint4 klo, khi, vlo, vhi;
+    uint32_t olo[4], ohi[4];
+    if (i < keep) {
+      const long long a = addr(src0 + i);
+      klo = *reinterpret_cast<const uint4*>(kp + a);
+      khi = *reinterpret_cast<const uint4*>(kp + a + half);
+      vlo = *reinterpret_cast<const uint4*>(vp + a);
+      vhi = *reinterpret_cast<const uint4*>(vp + a + half);
+      const float* co = cos_hist + (long long)(sinks + n_new + i) * hd;   // "original" rows
+      const float* so = sin_hist + (long long)(sinks + n_new + i) * hd;
+      const float* cs = cos_hist + (long long)(sinks + i) * hd;           // "shifted" rows
+      const float* ss = sin_hist + (long long)(sinks + i) * hd;
+      const uint32_t kl[4] = {klo.x, klo.y, klo.z, klo.w}, kh[4] = {khi.x, khi.y, khi.z, khi.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float lo[2] = {bf16_lo(kl[j]), bf16_hi(kl[j])}, hi[2] = {bf16_lo(kh[j]), bf16_hi(kh[j])}, rl[2], rh[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int dl = d0 + 2 * j + e, dh = dl + half;
+          const float rc_l = co[dl] * cs[dl] + so[dl] * ss[dl], rs_l = -so[dl] * cs[dl] + co[dl] * ss[dl];
+          const float rc_h = co[dh] * cs[dh] + so[dh] * ss[dh], rs_h = -so[dh] * cs[dh] + co[dh] * ss[dh];
+          rl[e] = lo[e] * rc_l - hi[e] * rs_l;   // rotate_half: first half pairs with -x2
+          rh[e] = hi[e] * rc_h + lo[e] * rs_h;   //              second half pairs with +x1
+        }
+        olo[j] = pack_bf16(rl[0], rl[1]);
+        ohi[j] = pack_bf16(rh[0], rh[1]);
+      }
+    }
+    __syncthreads();  // every source of this chunk is in registers before any destination is written
+    if (i < keep) {
+      const long long a = addr(dst0 + i);
+      *reinterpret_cast<uint4*>(kp + a) = make_uint4(olo[0], olo[1], olo[2], olo[3]);
+      *reinterpret_cast<uint4*>(kp + a + half) = make_uint4(ohi[0], ohi[1], ohi[2], ohi[3]);
+      *reinterpret_cast<uint4*>(vp + a) = vlo;
+      *reinterpret_cast<uint4*>(vp + a + half) = vhi;
+    }
+    __syncthreads();
+  }
+}
+
+int launch_kv_evict(const dli_kv_desc* kv, int n_layers, int batch, int KV, int hd, int cur_len, int window, int sinks,
+                    int n_new, const float* cos_hist, const float* sin_hist, cudaStream_t st) {
+  KvView v;
+  int rc = kv_view(kv, 0, &v);
+  if (rc) return rc;
+  DLI_REQUIRE(cos_hist && sin_hist, "dli_kv_evict: null cos/sin history");
+  DLI_REQUIRE(n_layers > 0 && batch > 0 && KV > 0 && (hd == 64 || hd == 128), "dli_kv_evict: bad shape");
+  DLI_REQUIRE(sinks >= 0 && n_new > 0 && window - sinks - n_new > 0, "dli_kv_evict: window %d too small for %d sinks + %d new tokens",
+              window, sinks, n_new);
+  DLI_REQUIRE(cur_len + n_new >= window && cur_len >= window - sinks - n_new,
+              "dli_kv_evict: nothing to evict (cur_len=%d n_new=%d window=%d)", cur_len, n_new, window);
+  return launch_kernel("kv_evict_kernel", kv_evict_kernel, dim3(KV, batch, n_layers), dim3(256), 0, st, v.k, v.v,
+                       (long long)(kv->layer_stride_bytes / 2), v.block_table, v.max_pages, v.page_tokens, KV, hd, cur_len,
+                       window, sinks, n_new, cos_hist, sin_hist);
 }
 
 }  // namespace dli

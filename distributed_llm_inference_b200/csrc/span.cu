@@ -2,6 +2,7 @@
 #include "common.cuh"
 
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
@@ -39,6 +40,15 @@ int sm_count() {
   return n;
 }
 
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DLI_NO_PDL");
+    v = (e && e[0] == '1') ? 0 : 1;
+  }
+  return v == 1;
+}
+
 int kv_view(const dli_kv_desc* kv, int layer, KvView* out) {
   DLI_REQUIRE(kv && kv->k_pages && kv->v_pages && kv->block_table && kv->seq_lens, "kv descriptor has a null pointer");
   DLI_REQUIRE(kv->page_tokens > 0 && kv->n_pages > 0 && kv->max_pages > 0 && kv->max_ctx > 0,
@@ -58,7 +68,7 @@ int kv_view(const dli_kv_desc* kv, int layer, KvView* out) {
 
 // ---- span object ------------------------------------------------------------------------------------
 struct WeightMaps {
-  CUtensorMap box128, box256;
+  CUtensorMap box64, box128, box256;
 };
 struct Layer {
   dli_layer_weights w{};
@@ -92,12 +102,11 @@ namespace dli {
 
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
-// Layout: the two split-K accumulation buffers come first, at offsets that do not depend on the call's
-// shape, because they carry an invariant across calls (all zeros on entry and on exit); everything behind
+// Layout: the split-K accumulation buffer comes first, at an offset that does not depend on the call's
+// shape, because it carries an invariant across calls (all zeros on entry and on exit); everything behind
 // them is per-call scratch.
 struct Workspace {
   float* qkv_acc;  // [128, n_qkv] fp32, zero between calls
-  float* gu_acc;   // [128, 2i]    fp32, zero between calls
   float* resid;
   __nv_bfloat16* xn;
   float* qkv;
@@ -121,7 +130,6 @@ static Workspace carve(const dli_span* s, void* base, int max_tokens, int max_ba
   Workspace w{};
   const size_t M = (size_t)max_tokens;
   w.qkv_acc = (float*)take((size_t)128 * s->n_qkv * 4);
-  w.gu_acc = (float*)take((size_t)128 * 2 * d.intermediate_size * 4);
   w.resid = (float*)take(M * d.hidden_size * 4);
   w.xn = (__nv_bfloat16*)take(M * d.hidden_size * 2);
   w.qkv = (float*)take(max_tokens > 128 ? M * s->n_qkv * 4 : 0);
@@ -172,7 +180,7 @@ static int span_gemm(dli_span* s, const void* x, const WeightMaps& wm, void* out
   const CUtensorMap* tx = nullptr;
   int rc = act_map(s, x, m, k, x_box, &tx);
   if (rc) return rc;
-  const CUtensorMap& tw = w_box == 256 ? wm.box256 : wm.box128;
+  const CUtensorMap& tw = w_box == 256 ? wm.box256 : w_box == 64 ? wm.box64 : wm.box128;
   return launch_gemm_planned(g, *tx, tw, out, ldo, m, n, epilogue, st);
 }
 
@@ -227,6 +235,12 @@ int dli_prefill_attention(const void* q_bf16, void* out_bf16, const dli_kv_desc*
   if (rc) return rc;
   return launch_prefill_attention((const __nv_bfloat16*)q_bf16, (__nv_bfloat16*)out_bf16, v, batch, q_len, n_heads,
                                   n_kv_heads, head_dim, causal != 0, (cudaStream_t)stream);
+}
+
+int dli_kv_evict(const dli_kv_desc* kv, int n_layers, int batch, int n_kv_heads, int head_dim, int cur_len, int window,
+                 int sinks, int n_new, const float* cos_hist, const float* sin_hist, dli_stream_t stream) {
+  return launch_kv_evict(kv, n_layers, batch, n_kv_heads, head_dim, cur_len, window, sinks, n_new, cos_hist, sin_hist,
+                         (cudaStream_t)stream);
 }
 
 int dli_silu_mul(float* gu_f32, void* act_bf16, int m, int n, int zero_after, dli_stream_t stream) {
@@ -304,6 +318,8 @@ int dli_span_bind_weights(dli_span* s, int layer, const dli_layer_weights* w) {
   for (auto& it : items) {
     int rc = make_tmap_bf16(&it.m->box128, it.p, it.rows, it.cols, it.cols, 128);
     if (rc) return rc;
+    rc = make_tmap_bf16(&it.m->box64, it.p, it.rows, it.cols, it.cols, 64);
+    if (rc) return rc;
     rc = make_tmap_bf16(&it.m->box256, it.p, it.rows, it.cols, it.cols, 256);
     if (rc) return rc;
   }
@@ -374,14 +390,9 @@ int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, i
     if (rc) return rc;
     // MLP (modules.py:181): gate|up with silu*up, then down + residual (modules.py:182)
     DLI_MARK(DLI_PROF_GEMM_GATE_UP);
-    if (skinny) {
-      rc = span_gemm(s, w.xn, L.gu, w.gu_acc, 2LL * inter, M, 2 * inter, h, DLI_EPI_ADD_F32, st);
-      if (rc) return rc;
-      DLI_MARK(DLI_PROF_SILU_MUL);
-      rc = launch_silu_mul(w.gu_acc, w.act, M, inter, true, st);
-    } else {
-      rc = span_gemm(s, w.xn, L.gu, w.act, inter, M, inter, h, DLI_EPI_SILU_MUL_BF16, st);
-    }
+    // one kernel on both paths: silu(gate) * up is the GEMM epilogue (64 gate + 64 up weight rows per CTA at
+    // decode, 128 + 128 accumulator columns per CTA at prefill)
+    rc = span_gemm(s, w.xn, L.gu, w.act, inter, M, inter, h, DLI_EPI_SILU_MUL_BF16, st);
     if (rc) return rc;
     DLI_MARK(DLI_PROF_GEMM_DOWN);
     rc = span_gemm(s, w.act, L.down, w.resid, h, M, h, inter, DLI_EPI_ADD_F32, st);

@@ -13,8 +13,10 @@ Same constructor signature ``(window_length, num_sink_tokens)`` (cache.py:11), s
 ``generation_id`` (cache.py:14-19).  Deviations, all deliberate:
   * the constructor works (the reference's raises, cache.py:12 / SURVEY D1);
   * layers are indexed by their LOCAL position in the span (SURVEY D3);
-  * attention-sink eviction (cache.py:111-133) is not implemented on the CUDA path yet: a generation that
-    would reach ``window_length`` raises ``NotImplementedError`` instead of silently diverging;
+  * attention-sink eviction (cache.py:111-133) runs as one in-place kernel over all layers of the span
+    (``evict`` -> ``dli_kv_evict``) for single-token steps; a multi-token chunk that would overflow the window
+    raises ``NotImplementedError`` (the reference's mask is then position-dependent in a way the kernels'
+    ``causal`` flag does not express);
   * ``update()`` (the per-layer tensor API of cache.py:64-135) is provided for callers that hold K/V
     tensors themselves; the span forward does not use it — its fused kernel appends in place.
 """
@@ -26,12 +28,15 @@ import torch
 
 
 class _Generation:
-    __slots__ = ("batch", "length", "pages", "block_table", "seq_lens", "max_pages", "seen_tokens")
+    __slots__ = ("batch", "length", "pages", "block_table", "seq_lens", "max_pages", "seen_tokens", "first_pos",
+                 "evictions")
 
     def __init__(self, batch: int, max_pages: int, device):
         self.batch = batch
         self.length = 0                      # tokens stored (same for every sequence of the generation)
         self.seen_tokens = 0                 # cache.py:86-87
+        self.first_pos = 0                   # absolute position of the generation's first token (cos/sin history)
+        self.evictions = 0
         self.pages: List[List[int]] = [[] for _ in range(batch)]
         self.max_pages = max_pages
         self.block_table = torch.zeros(batch, max_pages, dtype=torch.int32, device=device)
@@ -78,18 +83,20 @@ class PartialLlamaSinkCache:
     def free_pages(self) -> int:
         return len(self._free)
 
-    def _max_pages_per_seq(self) -> int:
-        return min(-(-self.window_length // self.page_tokens) + 1, max(1, self.n_pages))
+    def _max_pages_per_seq(self, min_tokens: int = 0) -> int:
+        # the first chunk of a generation is stored whole even when it is longer than the window (cache.py:103-105)
+        need = max(-(-self.window_length // self.page_tokens) + 1, -(-min_tokens // self.page_tokens))
+        return min(need, max(1, self.n_pages))
 
     # ------------------------------------------------------------------ generations
-    def open(self, generation_id: str, batch: int) -> _Generation:
+    def open(self, generation_id: str, batch: int, min_tokens: int = 0) -> _Generation:
         if not generation_id:
             raise ValueError("generation_id not provided")
         if self._k is None:
             raise RuntimeError("cache is not bound to a span yet")
         g = self._gens.get(generation_id)
         if g is None:
-            g = _Generation(batch, self._max_pages_per_seq(), self._k.device)
+            g = _Generation(batch, self._max_pages_per_seq(min_tokens), self._k.device)
             self._gens[generation_id] = g
         elif g.batch != batch:
             raise ValueError(f"generation {generation_id!r} was opened with batch {g.batch}, got {batch}")
@@ -105,11 +112,10 @@ class PartialLlamaSinkCache:
     def reserve(self, generation_id: str, batch: int, total_tokens: int) -> _Generation:
         """Make sure pages exist for ``total_tokens`` tokens per sequence (so that a captured graph can be
         replayed without touching the block table)."""
-        g = self.open(generation_id, batch)
-        if total_tokens >= self.window_length and g.length > 0:
-            raise NotImplementedError(
-                f"generation {generation_id!r} would reach window_length={self.window_length}: attention-sink "
-                "eviction (reference cache.py:111-133) is not implemented on the CUDA path")
+        g = self.open(generation_id, batch, total_tokens)
+        if total_tokens > self.window_length and g.length > 0:
+            raise ValueError(f"generation {generation_id!r}: {total_tokens} tokens exceed window_length="
+                             f"{self.window_length}; evict first (PartialLlamaSinkCache.evict)")
         need = -(-total_tokens // self.page_tokens)
         if need > g.max_pages:
             raise ValueError(f"{total_tokens} tokens exceed the block table ({g.max_pages} pages of {self.page_tokens})")
@@ -124,6 +130,34 @@ class PartialLlamaSinkCache:
             host = torch.tensor([row + [0] * (g.max_pages - len(row)) for row in g.pages], dtype=torch.int32)
             g.block_table.copy_(host, non_blocking=False)
         return g
+
+    def needs_eviction(self, generation_id: str, n_new: int) -> bool:
+        """cache.py:107: append while ``n + len < window``, otherwise evict (a first chunk is always stored whole)."""
+        g = self._gens.get(generation_id)
+        return g is not None and g.length > 0 and n_new + g.length >= self.window_length
+
+    def evict(self, generation_id: str, n_new: int, cos_hist: torch.Tensor, sin_hist: torch.Tensor) -> None:
+        """Attention-sink eviction for all layers (cache.py:111-133): keep the first ``num_sink_tokens`` tokens and
+        the last ``window - sinks - n_new``, re-rotating the kept keys back by ``n_new`` positions.  ``cos_hist`` /
+        ``sin_hist``: fp32 ``[window, hd]`` rows of the generation's first ``window`` positions (the reference's
+        ``_cos_cache`` / ``_sin_cache``).  Afterwards the generation holds ``window - n_new`` tokens."""
+        import ctypes as C
+
+        from distributed_llm_inference_b200 import _ffi
+
+        g = self._gens[generation_id]
+        W, s = self.window_length, self.num_sink_tokens
+        if W - s - n_new <= 0:
+            raise NotImplementedError(f"chunk of {n_new} tokens does not fit window {W} with {s} sink tokens")
+        if cos_hist.shape[0] < W or not cos_hist.is_contiguous() or cos_hist.dtype != torch.float32:
+            raise ValueError("cos/sin history must be contiguous fp32 [window, head_dim]")
+        n_layers, KV, hd = self._shape
+        kv = self.kv_desc(g, g.length)
+        _ffi.check(_ffi.lib.dli_kv_evict(C.byref(kv), n_layers, g.batch, KV, hd, g.length, W, s, n_new,
+                                         cos_hist.data_ptr(), sin_hist.data_ptr(), _ffi.current_stream()))
+        g.length = W - n_new
+        g.seq_lens.fill_(W - n_new)
+        g.evictions += 1
 
     def advance(self, generation_id: str, n_tokens: int, local_first_layer: bool = True) -> None:
         g = self._gens[generation_id]
@@ -161,6 +195,8 @@ class PartialLlamaSinkCache:
         B, KV, n, hd = key_states.shape
         if self._k is None:
             raise RuntimeError("cache is not bound to a span yet (call bind(n_layers, n_kv_heads, head_dim, device))")
+        if self.needs_eviction(gid, n):
+            raise NotImplementedError("the tensor-level update() does not evict; use LlamaBlock.forward or evict()")
         g = self.reserve(gid, B, (self._gens[gid].length if gid in self._gens else 0) + n)
         pt = self.page_tokens
         pos = torch.arange(g.length, g.length + n, device=self._k.device)

@@ -117,6 +117,17 @@ class LlamaBlock(nn.Module):
             self._ws_key = key
         return self._ws
 
+    # ------------------------------------------------------------------ whole-step CUDA graph
+    def graphed_decode(self, generation_id: str, cache: PartialLlamaSinkCache, max_ctx: int) -> "GraphedDecode":
+        """Capture ONE decode step (q_len = 1) of this span for a live generation into a CUDA graph.
+
+        The reference hides decode launch latency with three small per-layer graphs (utils/cuda.py:6-77 used at
+        modules.py:28-34,130-144); here the whole stage step — every kernel of every layer plus the rotary-table
+        gather and the length update — is one graph.  Everything that changes between steps (sequence lengths,
+        block table, position) lives in device memory, so the graph is replayed unchanged until ``max_ctx`` tokens.
+        """
+        return GraphedDecode(self, cache, generation_id, max_ctx)
+
     # ------------------------------------------------------------------ instrumentation (bench.py)
     def profile(self, enable: bool = True) -> None:
         """Record a CUDA event at every kernel-class boundary of the following forwards (dli_span_profile)."""
@@ -185,6 +196,7 @@ class LlamaBlock(nn.Module):
         gen = cache.generation(gid)
         past = gen.length if gen is not None else 0
 
+        cache_position_given, position_ids_given = cache_position is not None, position_ids is not None
         if cache_position is None:                      # model.py:39-42
             if past != 0 and self._causal_flag(attention_mask, L, past):
                 raise ValueError("cache_position must be given when continuing a generation (the reference's default "
@@ -201,7 +213,20 @@ class LlamaBlock(nn.Module):
             self._table = rope_table(self.head_dim, self.rope_theta, self.max_positions, self.rope, device)
         cs = torch.index_select(self._table, 1, position_ids[0].to(device))       # [2, L, hd] fp32 (model.py:55)
 
+        if gen is None:
+            pass
+        elif cache.needs_eviction(gid, L):              # cache.py:107-133: the window is full
+            if L != 1:
+                raise NotImplementedError("a multi-token chunk that overflows window_length is not supported by the "
+                                          "B200 span (the reference's mask becomes position-dependent there)")
+            p0, W = gen.first_pos, cache.window_length
+            if p0 + W > self._table.shape[1]:
+                raise ValueError("cos/sin history exceeds max_position_embeddings")
+            cache.evict(gid, L, self._table[0, p0:p0 + W], self._table[1, p0:p0 + W])
+            past = gen.length
         gen = cache.reserve(gid, B, past + L)
+        if gen.length == 0 and gen.seen_tokens == 0:
+            gen.first_pos = int(position_ids[0, 0].item()) if (cache_position_given or position_ids_given) else 0
         max_ctx = past + L
         ws = self._workspace(B * L, B, max_ctx, device)
         x = hidden_states.contiguous()
@@ -219,3 +244,60 @@ class LlamaBlock(nn.Module):
         if all_h is not None:
             res = res + (tuple(all_h[i] for i in range(all_h.shape[0])),)
         return res                                       # model.py:76
+
+
+class GraphedDecode:
+    """A captured decode step: ``out = step(x)`` appends one token per sequence and returns the span output
+    (a static buffer that the next ``step`` overwrites)."""
+
+    def __init__(self, block: LlamaBlock, cache: PartialLlamaSinkCache, generation_id: str, max_ctx: int):
+        gen = cache.generation(generation_id)
+        if gen is None or gen.length == 0:
+            raise ValueError("graphed_decode needs a generation that has been prefilled through this span")
+        ffi = block._ffi()
+        device = gen.seq_lens.device
+        B, h = gen.batch, block.config.hidden_size
+        self.block, self.cache, self.gid, self.max_ctx = block, cache, generation_id, max_ctx
+        if max_ctx >= cache.window_length:
+            raise ValueError("graphed decode cannot cross window_length (eviction is a separate launch)")
+        cache.reserve(generation_id, B, max_ctx)                    # block table fixed for the graph's lifetime
+        block._ensure_span(device)
+        if block._table is None or block._table.device != device:
+            block._table = rope_table(block.head_dim, block.rope_theta, block.max_positions, block.rope, device)
+        ws = block._workspace(B, B, max_ctx, device)
+        self.x = torch.zeros(B, 1, h, dtype=torch.bfloat16, device=device)
+        self.out = torch.empty_like(self.x)
+        self.pos = torch.tensor([gen.length], dtype=torch.long, device=device)
+        kv = cache.kv_desc(gen, max_ctx)
+
+        def launch():
+            cs = torch.index_select(block._table, 1, self.pos)                  # model.py:55
+            ffi.check(ffi.lib.dli_span_forward(block._span, C.byref(kv), B, 1, 1, self.x.data_ptr(), self.out.data_ptr(),
+                                               cs[0].data_ptr(), cs[1].data_ptr(), None, ws.data_ptr(), ws.numel(),
+                                               ffi.current_stream()))
+            gen.seq_lens.add_(1)
+            self.pos.add_(1)
+            return cs
+
+        # run the decode-path kernels once outside capture (one-time function attributes, descriptor caches) on a
+        # throw-away generation; the capture itself launches nothing, so the live generation is untouched
+        warm = "__dli_graph_warmup__"
+        block(warm, self.x, past_key_value=cache, cache_position=torch.zeros(1, dtype=torch.long, device=device))
+        cache.close(warm)
+        torch.cuda.synchronize(device)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._keep = launch()
+        self.launches = ffi.lib.dli_last_launch_count()
+
+    def step(self, x: Optional[torch.Tensor] = None) -> torch.Tensor:
+        gen = self.cache.generation(self.gid)
+        if gen.length + 1 > self.max_ctx:
+            raise RuntimeError(f"graphed decode captured for at most {self.max_ctx} tokens")
+        if x is not None and x.data_ptr() != self.x.data_ptr():
+            self.x.copy_(x)
+        self.graph.replay()
+        gen.length += 1                                                # host mirror of the device-side add
+        gen.seen_tokens += 1
+        self.block.last_launch_count = self.launches
+        return self.out

@@ -152,6 +152,17 @@ int dli_prefill_attention(const void* q_bf16, void* out_bf16, const dli_kv_desc*
                           int batch, int q_len, int n_heads, int n_kv_heads, int head_dim, int causal,
                           dli_stream_t stream);
 
+/* Attention-sink eviction for every layer of a span, in place on the pages (call BEFORE the forward that appends
+ * the n_new tokens, when cur_len + n_new >= window): the cache becomes [first `sinks` tokens | last
+ * (window - sinks - n_new) tokens with keys re-rotated back by n_new positions]; afterwards the caller sets
+ * seq_lens[b] = window - n_new.  cos_hist/sin_hist: fp32 [window, hd], the cos/sin rows of the generation's first
+ * `window` positions (the reference's _cos_cache/_sin_cache).  All sequences of the generation share cur_len.
+ * Replaces the eviction branch of PartialLlamaSinkCache.update, cache.py:111-133, and
+ * _get_rerotation_cos_sin, cache.py:21-48. */
+int dli_kv_evict(const dli_kv_desc* kv, int n_layers, int batch, int n_kv_heads, int head_dim, int cur_len,
+                 int window, int sinks, int n_new, const float* cos_hist, const float* sin_hist,
+                 dli_stream_t stream);
+
 /* act_bf16[m, n] = silu(gu_f32[m, n]) * gu_f32[m, n_total + n]; gu is [m, 2*n].  Decode-path companion of
  * the split-K gate|up GEMM (the activation of LlamaMLP.forward, modules.py:181). If zero_after != 0 the
  * fp32 input is cleared after it is read (it is a split-K accumulation buffer). */

@@ -112,8 +112,11 @@ def test_paged_cache_limits_are_loud():
     c.bind(1, 1, 8, "cpu", dtype=torch.float32)
     c.reserve("g", 1, 8)
     c.advance("g", 8)
-    with pytest.raises(NotImplementedError, match="eviction"):
-        c.reserve("g", 1, 10)                               # would reach window_length (cache.py:107,111-133)
+    assert c.needs_eviction("g", 2) and not c.needs_eviction("g", 1)    # cache.py:107: append while n + len < window
+    with pytest.raises(ValueError, match="evict first"):
+        c.reserve("g", 1, 11)
+    with pytest.raises(NotImplementedError):
+        c.update(torch.zeros(1, 1, 2, 8), torch.zeros(1, 1, 2, 8), 0, {"generation_id": "g"})
     c2 = PartialLlamaSinkCache(4096, 2, page_tokens=4, capacity_tokens=8)
     c2.bind(1, 1, 8, "cpu", dtype=torch.float32)
     with pytest.raises(RuntimeError, match="exhausted"):

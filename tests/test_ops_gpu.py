@@ -62,7 +62,8 @@ def test_gemm(m, n, k, epi):
     assert err <= tol, msg
 
 
-@pytest.mark.parametrize("m,n,k", [(129, 128, 512), (300, 1408, 512), (512, 2048, 768), (1000, 704, 1024)])
+@pytest.mark.parametrize("m,n,k", [(129, 128, 512), (300, 1408, 512), (512, 2048, 768), (1000, 704, 1024),
+                                   (1, 1408, 512), (16, 2048, 768), (100, 704, 1024), (8, 200, 512), (128, 11008, 4096)])
 def test_gemm_silu_mul(m, n, k):
     x = _randn(m, k, seed=6)
     w = _randn(2 * n, k, seed=7, scale=0.05)                                      # gate rows then up rows
