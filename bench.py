@@ -226,13 +226,15 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        # the hand-off kernels must get SM slots while the stage's own kernels keep every SM full: high-priority stream
+        opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+        dist.init_process_group("nccl", device_id=dev, pg_options=opts)
     shape = syn.SHAPES[MODEL]
     n_total = shape.num_hidden_layers
     per = n_total // world
     layer_ids = list(range(rank * per, (rank + 1) * per if rank < world - 1 else n_total))
     K, W = args.steps, max(args.warmup, 3)
-    n_mb = world                       # micro-batches in flight = pipeline depth
+    n_mb = args.micro_batches or world   # micro-batches in flight (default: the pipeline depth)
     total_ctx = PROMPT + W + K + 8 + 32 + 8
 
     blk = build_span(shape, layer_ids, dev)
@@ -258,11 +260,12 @@ def run_ours(args):
     # one GPU: the whole stage step is one CUDA graph (LlamaBlock.graphed_decode); pipeline: eager + NCCL P2P
     xs = [syn.make_hidden(shape, BATCH, 1, seed=7 + m, device=dev) for m in range(n_mb)] if rank == 0 else None
     pos = PROMPT
-    graph = blk.graphed_decode(gids[0], cache, total_ctx) if (world == 1 and not args.no_graph) else None
+    graph = None
+    if not args.no_graph:
+        stage.enable_graphs(gids, total_ctx, batch=BATCH, peer_store=not args.nccl_handoff)
+        graph = stage.graphs[gids[0]]
 
     def decode_round(xs, pos):
-        if graph is not None:
-            return [graph.step(xs[0])]
         return stage.run_round(gids, xs, BATCH, 1, pos, feed_back=True)
 
     for _ in range(W):
@@ -281,12 +284,23 @@ def run_ours(args):
         pos += 1
         evs[k + 1].record()
     torch.cuda.synchronize()
+    if os.environ.get("BENCH_TRACE"):
+        stage.trace = []
+        for _ in range(8):
+            xs = decode_round(xs, pos)
+            pos += 1
+        torch.cuda.synchronize()
+        tr = stage.trace[n_mb:]
+        print(f"[trace rank {rank}] recv-wait {sum(e[0].elapsed_time(e[1]) for e in tr) / len(tr):.3f} ms, step "
+              f"{sum(e[1].elapsed_time(e[2]) for e in tr) / len(tr):.3f} ms per micro-batch; between steps "
+              f"{sum(a[2].elapsed_time(b[0]) for a, b in zip(tr[:-1], tr[1:])) / (len(tr) - 1):.3f} ms", flush=True)
+        stage.trace = None
     clocks = sampler.finish()
     if world > 1:
         dist.barrier()
     total_ms = torch.tensor([evs[0].elapsed_time(evs[K])], device=dev)
     lat = sorted(evs[k].elapsed_time(evs[k + 1]) for k in range(K))
-    launches = (graph.launches if graph is not None else stage.launches_per_round) * K
+    launches = stage.launches_per_round * K
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(prefill_ms, op=dist.ReduceOp.MAX)
@@ -296,6 +310,8 @@ def run_ours(args):
     ctx_mid = PROMPT + W + K // 2
 
     # ---- instrumented pass: per-kernel-class time with CUDA events inside dli_span_forward ----
+    stage.drain(n_mb)
+    saved_graphs, stage.graphs = stage.graphs, {}          # events cannot be recorded inside a replayed graph
     blk.profile(True)
     n_prof = min(K, 8)
     for _ in range(n_prof):
@@ -303,6 +319,7 @@ def run_ours(args):
         pos += 1
     prof = blk.profile_read()
     blk.profile(False)
+    stage.graphs = saved_graphs
     hbm_peak, tc_peak, peak_kind = measured_peaks()
     sb = decode_step_bytes(shape, len(layer_ids), BATCH, ctx_mid)
     gemm_ms = sum(prof[c][0] for c in GEMM_CLASSES)
@@ -361,7 +378,8 @@ def run_ours(args):
                                    f"{PROMPT + W}..{PROMPT + W + K}; random-init weights, synthetic hidden states",
                        "global_batch": tokens_per_step, "seq_len": PROMPT, "parallelism": f"pp{world}",
                        "l2": "inputs larger than L2 (12.9 GB of weights streamed per step)", "page_tokens": 16,
-                       "launch": "cuda_graph" if graph is not None else "eager"},
+                       "launch": "cuda_graph" if graph is not None else "eager",
+                       "handoff": stage.handoff, "handoff_fallback_reason": stage.handoff_error},
             "p50_ms_per_token": round(lat[len(lat) // 2] / n_mb, 4),
             "prefill_tokens_per_sec": round(n_mb * BATCH * PROMPT / (prefill_ms.item() * 1e-3), 1),
             "prefill_note": "first call, includes one-time descriptor/workspace set-up",
@@ -411,6 +429,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--batch", type=int, default=None, help="override the batch (experiments; the default is the config's 16)")
+    ap.add_argument("--micro-batches", type=int, default=None, help="micro-batches in flight (default: number of stages)")
+    ap.add_argument("--nccl-handoff", action="store_true", help="hand off by NCCL isend/irecv instead of peer stores")
     ap.add_argument("--no-graph", action="store_true", help="decode with eager launches instead of the CUDA graph")
     args = ap.parse_args()
     if args.batch:

@@ -118,15 +118,19 @@ class LlamaBlock(nn.Module):
         return self._ws
 
     # ------------------------------------------------------------------ whole-step CUDA graph
-    def graphed_decode(self, generation_id: str, cache: PartialLlamaSinkCache, max_ctx: int) -> "GraphedDecode":
+    def graphed_decode(self, generation_id: str, cache: PartialLlamaSinkCache, max_ctx: int,
+                       x: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> "GraphedDecode":
         """Capture ONE decode step (q_len = 1) of this span for a live generation into a CUDA graph.
 
         The reference hides decode launch latency with three small per-layer graphs (utils/cuda.py:6-77 used at
         modules.py:28-34,130-144); here the whole stage step — every kernel of every layer plus the rotary-table
         gather and the length update — is one graph.  Everything that changes between steps (sequence lengths,
         block table, position) lives in device memory, so the graph is replayed unchanged until ``max_ctx`` tokens.
+        ``x`` / ``out`` (optional, bf16 ``[B, 1, h]``) replace the graph's own static input / output buffers; ``out`` may
+        be a peer GPU's mapped memory, in which case the span's last kernel stores the hand-off tensor straight into
+        the next pipeline stage's input over NVLink.
         """
-        return GraphedDecode(self, cache, generation_id, max_ctx)
+        return GraphedDecode(self, cache, generation_id, max_ctx, x=x, out=out)
 
     # ------------------------------------------------------------------ instrumentation (bench.py)
     def profile(self, enable: bool = True) -> None:
@@ -250,7 +254,8 @@ class GraphedDecode:
     """A captured decode step: ``out = step(x)`` appends one token per sequence and returns the span output
     (a static buffer that the next ``step`` overwrites)."""
 
-    def __init__(self, block: LlamaBlock, cache: PartialLlamaSinkCache, generation_id: str, max_ctx: int):
+    def __init__(self, block: LlamaBlock, cache: PartialLlamaSinkCache, generation_id: str, max_ctx: int,
+                 x: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None):
         gen = cache.generation(generation_id)
         if gen is None or gen.length == 0:
             raise ValueError("graphed_decode needs a generation that has been prefilled through this span")
@@ -265,9 +270,12 @@ class GraphedDecode:
         if block._table is None or block._table.device != device:
             block._table = rope_table(block.head_dim, block.rope_theta, block.max_positions, block.rope, device)
         ws = block._workspace(B, B, max_ctx, device)
-        self.x = torch.zeros(B, 1, h, dtype=torch.bfloat16, device=device)
-        self.out = torch.empty_like(self.x)
-        self.pos = torch.tensor([gen.length], dtype=torch.long, device=device)
+        for t in (x, out):
+            if t is not None and (tuple(t.shape) != (B, 1, h) or t.dtype != torch.bfloat16 or not t.is_contiguous()):
+                raise ValueError(f"graphed_decode buffers must be contiguous bf16 [{B}, 1, {h}]")
+        self.x = x if x is not None else torch.zeros(B, 1, h, dtype=torch.bfloat16, device=device)
+        self.out = out if out is not None else torch.empty(B, 1, h, dtype=torch.bfloat16, device=device)
+        self.pos = torch.tensor([gen.first_pos + gen.seen_tokens], dtype=torch.long, device=device)
         kv = cache.kv_desc(gen, max_ctx)
 
         def launch():
@@ -289,15 +297,19 @@ class GraphedDecode:
         with torch.cuda.graph(self.graph):
             self._keep = launch()
         self.launches = ffi.lib.dli_last_launch_count()
+        self._len = gen.length        # host mirror of the device-side position
 
     def step(self, x: Optional[torch.Tensor] = None) -> torch.Tensor:
         gen = self.cache.generation(self.gid)
         if gen.length + 1 > self.max_ctx:
             raise RuntimeError(f"graphed decode captured for at most {self.max_ctx} tokens")
+        if gen.length != self._len:                                    # eager steps ran in between: re-seed the position
+            self.pos.fill_(gen.first_pos + gen.seen_tokens)
         if x is not None and x.data_ptr() != self.x.data_ptr():
             self.x.copy_(x)
         self.graph.replay()
         gen.length += 1                                                # host mirror of the device-side add
+        self._len = gen.length
         gen.seen_tokens += 1
         self.block.last_launch_count = self.launches
         return self.out

@@ -28,13 +28,66 @@ class PipelineStage:
         self.dtype = dtype
         self.launches_per_round = 0
         self._pending = []          # (work, tensor) of sends still in flight: keep tensors alive
+        self.graphs = {}            # generation id -> GraphedDecode (whole stage step as one CUDA graph)
+        self.handoff = "nccl" if world > 1 else "local"
+        self.handoff_error = None
+        self._ring_pending = False
+        self.trace = None           # set to [] to collect (recv_wait_ms, step_ms) CUDA-event pairs per micro-batch
+
+    def enable_graphs(self, generation_ids: Sequence[str], max_ctx: int, batch: Optional[int] = None,
+                      peer_store: bool = True) -> str:
+        """Capture this stage's decode step of every (prefilled) micro-batch into a CUDA graph.
+
+        ``peer_store`` (multi-GPU, NVLink/NVSwitch): every stage owns an "inbox" ``[micro_batches, B, 1, h]`` in
+        symmetric memory (peer-mapped by all ranks).  Stage r's graph for micro-batch m reads its input from its own
+        inbox slot m and its LAST KERNEL writes the hand-off tensor directly into slot m of stage r+1's inbox over
+        NVLink — no send/recv kernel, no extra copy, nothing competing for SMs on a second stream; a one-word
+        semaphore per (edge, micro-batch) orders producer and consumer.  If symmetric memory cannot be set up the
+        stage falls back to NCCL ``isend/irecv`` into the graphs' static buffers.  Returns the hand-off mode."""
+        self.handoff = "local"
+        peer = None
+        if self.world > 1 and peer_store:
+            try:
+                import torch.distributed._symmetric_memory as symm_mem
+
+                if batch is None:
+                    batch = self.cache.generation(generation_ids[0]).batch
+                shape = (len(generation_ids), batch, 1, self.hidden_size)
+                if hasattr(symm_mem, "enable_symm_mem_for_group"):
+                    try:
+                        symm_mem.enable_symm_mem_for_group(dist.group.WORLD.group_name)
+                    except Exception:
+                        pass
+                self.inbox = symm_mem.empty(shape, dtype=self.dtype, device=self.device)
+                self.inbox.zero_()
+                self.hdl = symm_mem.rendezvous(self.inbox, dist.group.WORLD)
+                peer = self.hdl.get_buffer((self.rank + 1) % self.world, shape, self.dtype)
+                self.handoff = "peer_store"
+            except Exception as e:  # noqa: BLE001 - any failure means: use NCCL
+                self.handoff_error = repr(e)
+                peer = None
+        if self.world > 1 and peer is None:
+            self.handoff = "nccl"
+        ok = torch.tensor([1 if self.handoff != "nccl" else 0], device=self.device)
+        if self.world > 1:          # all stages must agree on the protocol
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if ok.item() == 0:
+                self.handoff, peer = "nccl", None
+        for m, gid in enumerate(generation_ids):
+            if peer is not None:
+                self.graphs[gid] = self.span.graphed_decode(gid, self.cache, max_ctx, x=self.inbox[m], out=peer[m])
+            else:
+                self.graphs[gid] = self.span.graphed_decode(gid, self.cache, max_ctx)
+        if self.world > 1:
+            dist.barrier()
+        return self.handoff
 
     # -- P2P ------------------------------------------------------------------------------------------
     def _send(self, t: torch.Tensor, dst: int) -> None:
         self._pending.append((dist.isend(t, dst), t))
 
-    def _recv(self, shape, src: int) -> torch.Tensor:
-        buf = torch.empty(shape, dtype=self.dtype, device=self.device)
+    def _recv(self, shape, src: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        buf = out if out is not None else torch.empty(shape, dtype=self.dtype, device=self.device)
         dist.irecv(buf, src).wait()       # NCCL: the current stream waits for the transfer, the host does not
         return buf
 
@@ -51,6 +104,8 @@ class PipelineStage:
         round's inputs when ``feed_back``); ``None`` elsewhere."""
         first, last = self.rank == 0, self.rank == self.world - 1
         self._reap()
+        if q_len == 1 and self.graphs:
+            return self._run_round_graphed(generation_ids, inputs, batch, feed_back)
         cp = torch.arange(start_pos, start_pos + q_len, device=self.device)
         shape = (batch, q_len, self.hidden_size)
         outs, launches = [], 0
@@ -70,3 +125,79 @@ class PipelineStage:
         if first and feed_back:
             return [self._recv(shape, self.world - 1) for _ in generation_ids]
         return outs if last else None
+
+    def _run_round_graphed(self, generation_ids, inputs, batch, feed_back):
+        if self.handoff == "peer_store":
+            return self._run_round_peer_store(generation_ids, inputs, feed_back)
+        first, last = self.rank == 0, self.rank == self.world - 1
+        shape = (batch, 1, self.hidden_size)
+        outs, launches = [], 0
+        for m, gid in enumerate(generation_ids):
+            g = self.graphs[gid]
+            if self.trace is not None:
+                ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+                ev[0].record()
+            if first:
+                if inputs[m].data_ptr() != g.x.data_ptr():
+                    g.x.copy_(inputs[m])
+            else:
+                self._recv(shape, self.rank - 1, out=g.x)
+            if self.trace is not None:
+                ev[1].record()
+            y = g.step()
+            if self.trace is not None:
+                ev[2].record()
+                self.trace.append(ev)
+            launches += g.launches
+            if not last:
+                self._send(y, self.rank + 1)
+            elif self.world > 1 and feed_back:
+                self._send(y, 0)
+            else:
+                outs.append(y)
+        self.launches_per_round = launches
+        if self.world == 1:
+            return outs
+        if first and feed_back:   # ring closure straight into the graphs' input buffers
+            return [self._recv(shape, self.world - 1, out=self.graphs[gid].x) for gid in generation_ids]
+        return outs if last else None
+
+    def _run_round_peer_store(self, generation_ids, inputs, feed_back):
+        """wait(prev, m) -> graph m (last kernel stores into the next stage's inbox) -> signal(next, m), all on one
+        stream.  A slot is never overwritten early: the producer's next write to it depends, through the ring, on the
+        consumer's previous step."""
+        first, last = self.rank == 0, self.rank == self.world - 1
+        prev, nxt = (self.rank - 1) % self.world, (self.rank + 1) % self.world
+        launches = 0
+        for m, gid in enumerate(generation_ids):
+            g = self.graphs[gid]
+            if self.trace is not None:
+                ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+                ev[0].record()
+            if first and not self._ring_pending:
+                if inputs[m].data_ptr() != g.x.data_ptr():
+                    g.x.copy_(inputs[m])                   # fresh input injected at the head of the pipe
+            else:
+                self.hdl.wait_signal(prev, m, 20000)
+            if self.trace is not None:
+                ev[1].record()
+            g.step()
+            if not last or feed_back:
+                self.hdl.put_signal(nxt, m, 20000)
+            if self.trace is not None:
+                ev[2].record()
+                self.trace.append(ev)
+            launches += g.launches + 2
+        self.launches_per_round = launches
+        if first:
+            self._ring_pending = feed_back
+        if first and feed_back:
+            return [self.graphs[gid].x for gid in generation_ids]   # filled by the last stage; waited on next round
+        return None
+
+    def drain(self, n_micro_batches: int) -> None:
+        """Stage 0: consume the ring-closure signals of the last round (before switching hand-off mode)."""
+        if self.handoff == "peer_store" and self.rank == 0 and self._ring_pending:
+            for m in range(n_micro_batches):
+                self.hdl.wait_signal(self.world - 1, m, 20000)
+            self._ring_pending = False
