@@ -230,7 +230,7 @@ def run_ours(args):
         opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
         dist.init_process_group("nccl", device_id=dev, pg_options=opts)
     shape = syn.SHAPES[MODEL]
-    n_total = shape.num_hidden_layers
+    n_total = args.layers or shape.num_hidden_layers
     per = n_total // world
     layer_ids = list(range(rank * per, (rank + 1) * per if rank < world - 1 else n_total))
     K, W = args.steps, max(args.warmup, 3)
@@ -238,7 +238,8 @@ def run_ours(args):
     total_ctx = PROMPT + W + K + 8 + 32 + 8
 
     blk = build_span(shape, layer_ids, dev)
-    cache = PartialLlamaSinkCache(1 << 20, 4, page_tokens=16, capacity_tokens=n_mb * BATCH * (total_ctx + 16) + BATCH * 64)
+    cache = PartialLlamaSinkCache(1 << 20, 4, page_tokens=16,
+                                  capacity_tokens=n_mb * BATCH * (total_ctx + 16) + BATCH * 64 + BATCH * (PROMPT + 16))
     stage = PipelineStage(blk, cache, rank, world, dev)
     gids = [f"mb{m}" for m in range(n_mb)]
 
@@ -255,6 +256,39 @@ def run_ours(args):
     prefill_ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
     for g in gids:
         cache.reserve(g, BATCH, total_ctx)            # block tables stay fixed from here on
+
+    # ---- warm prefill of the same chunk shape (tensor-core roofline), one GPU only ----
+    prefill = None
+    if world == 1:
+        x_pf = prompts[0]
+        times = []
+        for rep in range(3):
+            torch.cuda.synchronize()
+            e0.record()
+            blk("warm_prefill", x_pf, past_key_value=cache)
+            e1.record()
+            torch.cuda.synchronize()
+            times.append(e0.elapsed_time(e1))
+            if rep == 2:
+                blk.profile(True)
+                cache.close("warm_prefill")
+                blk("warm_prefill", x_pf, past_key_value=cache)
+                pf_prof = blk.profile_read()
+                blk.profile(False)
+            cache.close("warm_prefill")
+        ms = min(times)
+        h, i = shape.hidden_size, shape.intermediate_size
+        H, KV, hd = shape.num_attention_heads, shape.num_key_value_heads, shape.head_dim
+        T = PROMPT
+        flops = len(layer_ids) * (2 * BATCH * T * (h * H * hd + 2 * h * KV * hd + H * hd * h + 3 * h * i)
+                                  + BATCH * 2 * T * T * H * hd)
+        _, tc_peak, pk = measured_peaks()
+        prefill = {"tokens_per_sec": round(BATCH * T / (ms * 1e-3), 1), "ms": round(ms, 3),
+                   "tflops": round(flops / (ms * 1e-3) / 1e12, 1), "peak_tflops": tc_peak,
+                   "frac": round(flops / (ms * 1e-3) / 1e12 / tc_peak, 4),
+                   "peak_source": f"MEASURED_PEAKS.json ({pk}, bf16_tflops_sustained)",
+                   "flops": flops, "chunk": f"{BATCH} x {T} tokens, causal, warm (best of 3)",
+                   "kernel_ms": {c: round(v[0], 3) for c, v in pf_prof.items()}}
 
     # ---- decode: warm-up, then K timed steps ----
     # one GPU: the whole stage step is one CUDA graph (LlamaBlock.graphed_decode); pipeline: eager + NCCL P2P
@@ -368,12 +402,13 @@ def run_ours(args):
                       "(wall clock)"}
 
     if rank == 0:
-        cpu = cpu_reference_decode(shape, n_total, BATCH, PROMPT, budget_s=args.cpu_budget) if world == 1 else None
+        cpu = (cpu_reference_decode(shape, n_total, BATCH, PROMPT, budget_s=args.cpu_budget)
+               if (world == 1 and args.cpu_budget > 0) else None)
         line = {
             "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"Llama-2-7B-shaped span ({n_total} layers) KV-cached decode, batch {BATCH} x "
+            "config": {"workload": f"{shape.name}-shaped span ({n_total} layers) KV-cached decode, batch {BATCH} x "
                                    f"{n_mb} micro-batch(es) in flight, {PROMPT}-token prompt, context "
                                    f"{PROMPT + W}..{PROMPT + W + K}; random-init weights, synthetic hidden states",
                        "global_batch": tokens_per_step, "seq_len": PROMPT, "parallelism": f"pp{world}",
@@ -382,7 +417,7 @@ def run_ours(args):
                        "handoff": stage.handoff, "handoff_fallback_reason": stage.handoff_error},
             "p50_ms_per_token": round(lat[len(lat) // 2] / n_mb, 4),
             "prefill_tokens_per_sec": round(n_mb * BATCH * PROMPT / (prefill_ms.item() * 1e-3), 1),
-            "prefill_note": "first call, includes one-time descriptor/workspace set-up",
+            "prefill_note": "first call, includes one-time descriptor/workspace set-up", "prefill": prefill,
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roofline,
@@ -429,13 +464,17 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--batch", type=int, default=None, help="override the batch (experiments; the default is the config's 16)")
+    ap.add_argument("--model", default=None, choices=["7b", "13b", "70b", "tiny"], help="shape (default: configs[1], 7b)")
+    ap.add_argument("--layers", type=int, default=None, help="total layers over all stages (default: the model's)")
     ap.add_argument("--micro-batches", type=int, default=None, help="micro-batches in flight (default: number of stages)")
     ap.add_argument("--nccl-handoff", action="store_true", help="hand off by NCCL isend/irecv instead of peer stores")
     ap.add_argument("--no-graph", action="store_true", help="decode with eager launches instead of the CUDA graph")
     args = ap.parse_args()
+    global BATCH, MODEL
     if args.batch:
-        global BATCH
         BATCH = args.batch
+    if args.model:
+        MODEL = args.model
     if args.impl == "reference":
         run_reference(args)
     else:
