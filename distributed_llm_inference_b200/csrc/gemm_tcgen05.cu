@@ -110,6 +110,85 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int bn) {
 
 __device__ __forceinline__ float silu(float x) { return x / (1.0f + __expf(-x)); }
 
+// Token-major epilogue of one accumulator tile: lane = token (row arow), columns = features b_row0 ..
+template <int BN, int EPI>
+__device__ __forceinline__ void epilogue_token_major(uint32_t taddr, int arow, int b_row0, const GemmParams& p) {
+  uint32_t v[16];
+  if (EPI == DLI_EPI_SILU_MUL_BF16) {
+  // lane = token; columns [0, BN/2) = gate, [BN/2, BN) = up of features b_row0 ..
+  const bool t_ok = arow < p.m_tokens;
+  uint32_t u[16];
+#pragma unroll 1
+  for (int c0 = 0; c0 < BN / 2; c0 += 16) {
+    tmem_ld16(taddr + c0, v);
+    tmem_ld16(taddr + BN / 2 + c0, u);
+    tmem_ld_wait();
+    const int f0 = b_row0 + c0;
+    if (t_ok && f0 < p.n_features) {
+      __nv_bfloat16* o = (__nv_bfloat16*)p.out + (long long)arow * p.ldo + f0;
+      if (f0 + 16 <= p.n_features) {
+        uint32_t w[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          w[j] = pack_bf16(silu(__uint_as_float(v[2 * j])) * __uint_as_float(u[2 * j]),
+                           silu(__uint_as_float(v[2 * j + 1])) * __uint_as_float(u[2 * j + 1]));
+        *reinterpret_cast<uint4*>(o) = make_uint4(w[0], w[1], w[2], w[3]);
+        *reinterpret_cast<uint4*>(o + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+      } else {
+        for (int j = 0; j < 16 && f0 + j < p.n_features; ++j)
+          o[j] = __float2bfloat16_rn(silu(__uint_as_float(v[j])) * __uint_as_float(u[j]));
+      }
+    }
+  }
+} else {
+  // lane = token, column = feature
+  const bool t_ok = arow < p.m_tokens;
+#pragma unroll 1
+  for (int c0 = 0; c0 < BN; c0 += 16) {
+    tmem_ld16(taddr + c0, v);
+    tmem_ld_wait();
+    const int f0 = b_row0 + c0;
+    if (t_ok && f0 < p.n_features) {
+      const bool full = f0 + 16 <= p.n_features;
+      if (EPI == DLI_EPI_STORE_BF16) {
+        __nv_bfloat16* o = (__nv_bfloat16*)p.out + (long long)arow * p.ldo + f0;
+        if (full) {
+          uint32_t w[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) w[j] = pack_bf16(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+          *reinterpret_cast<uint4*>(o) = make_uint4(w[0], w[1], w[2], w[3]);
+          *reinterpret_cast<uint4*>(o + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+        } else {
+          for (int j = 0; j < 16 && f0 + j < p.n_features; ++j) o[j] = __float2bfloat16_rn(__uint_as_float(v[j]));
+        }
+      } else {
+        float* o = (float*)p.out + (long long)arow * p.ldo + f0;
+        if (full) {
+#pragma unroll
+          for (int j = 0; j < 16; j += 4) {
+            if (EPI == DLI_EPI_ADD_F32) {
+              asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o + j), "f"(__uint_as_float(v[j])),
+                           "f"(__uint_as_float(v[j + 1])), "f"(__uint_as_float(v[j + 2])),
+                           "f"(__uint_as_float(v[j + 3]))
+                           : "memory");
+            } else {
+              *reinterpret_cast<float4*>(o + j) =
+                  make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                              __uint_as_float(v[j + 3]));
+            }
+          }
+        } else {
+          for (int j = 0; j < 16 && f0 + j < p.n_features; ++j) {
+            if (EPI == DLI_EPI_ADD_F32) atomicAdd(o + j, __uint_as_float(v[j]));
+            else o[j] = __uint_as_float(v[j]);
+          }
+        }
+      }
+    }
+  }
+}
+}
+
 // ---- kernel -------------------------------------------------------------------------------------------
 template <int BN, int EPI, bool SWAP>
 __global__ void __launch_bounds__(GEMM_THREADS, SWAP ? 2 : 1)
@@ -292,78 +371,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
             }
           }
         }
-      } else if (EPI == DLI_EPI_SILU_MUL_BF16) {
-        // lane = token; columns [0, BN/2) = gate, [BN/2, BN) = up of features b_row0 ..
-        const bool t_ok = arow < p.m_tokens;
-        uint32_t u[16];
-#pragma unroll 1
-        for (int c0 = 0; c0 < BN / 2; c0 += 16) {
-          tmem_ld16(taddr + c0, v);
-          tmem_ld16(taddr + BN / 2 + c0, u);
-          tmem_ld_wait();
-          const int f0 = b_row0 + c0;
-          if (t_ok && f0 < p.n_features) {
-            __nv_bfloat16* o = (__nv_bfloat16*)p.out + (long long)arow * p.ldo + f0;
-            if (f0 + 16 <= p.n_features) {
-              uint32_t w[8];
-#pragma unroll
-              for (int j = 0; j < 8; ++j)
-                w[j] = pack_bf16(silu(__uint_as_float(v[2 * j])) * __uint_as_float(u[2 * j]),
-                                 silu(__uint_as_float(v[2 * j + 1])) * __uint_as_float(u[2 * j + 1]));
-              *reinterpret_cast<uint4*>(o) = make_uint4(w[0], w[1], w[2], w[3]);
-              *reinterpret_cast<uint4*>(o + 8) = make_uint4(w[4], w[5], w[6], w[7]);
-            } else {
-              for (int j = 0; j < 16 && f0 + j < p.n_features; ++j)
-                o[j] = __float2bfloat16_rn(silu(__uint_as_float(v[j])) * __uint_as_float(u[j]));
-            }
-          }
-        }
       } else {
-        // lane = token, column = feature
-        const bool t_ok = arow < p.m_tokens;
-#pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 16) {
-          tmem_ld16(taddr + c0, v);
-          tmem_ld_wait();
-          const int f0 = b_row0 + c0;
-          if (t_ok && f0 < p.n_features) {
-            const bool full = f0 + 16 <= p.n_features;
-            if (EPI == DLI_EPI_STORE_BF16) {
-              __nv_bfloat16* o = (__nv_bfloat16*)p.out + (long long)arow * p.ldo + f0;
-              if (full) {
-                uint32_t w[8];
-#pragma unroll
-                for (int j = 0; j < 8; ++j) w[j] = pack_bf16(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
-                *reinterpret_cast<uint4*>(o) = make_uint4(w[0], w[1], w[2], w[3]);
-                *reinterpret_cast<uint4*>(o + 8) = make_uint4(w[4], w[5], w[6], w[7]);
-              } else {
-                for (int j = 0; j < 16 && f0 + j < p.n_features; ++j) o[j] = __float2bfloat16_rn(__uint_as_float(v[j]));
-              }
-            } else {
-              float* o = (float*)p.out + (long long)arow * p.ldo + f0;
-              if (full) {
-#pragma unroll
-                for (int j = 0; j < 16; j += 4) {
-                  if (EPI == DLI_EPI_ADD_F32) {
-                    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o + j), "f"(__uint_as_float(v[j])),
-                                 "f"(__uint_as_float(v[j + 1])), "f"(__uint_as_float(v[j + 2])),
-                                 "f"(__uint_as_float(v[j + 3]))
-                                 : "memory");
-                  } else {
-                    *reinterpret_cast<float4*>(o + j) =
-                        make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
-                                    __uint_as_float(v[j + 3]));
-                  }
-                }
-              } else {
-                for (int j = 0; j < 16 && f0 + j < p.n_features; ++j) {
-                  if (EPI == DLI_EPI_ADD_F32) atomicAdd(o + j, __uint_as_float(v[j]));
-                  else o[j] = __uint_as_float(v[j]);
-                }
-              }
-            }
-          }
-        }
+        epilogue_token_major<BN, EPI>(taddr, arow, b_row0, p);
       }
     }
   }
@@ -374,6 +383,130 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TMEM_COLS) : "memory");
   }
 }
+
+// ---- persistent token-major kernel (prefill) -------------------------------------------------------------
+// One CTA per SM loops over output tiles (static round-robin, token tiles fastest so that concurrently running
+// CTAs share weight tiles in L2).  The accumulator is double-buffered in TMEM (2 x BN columns), so the epilogue of
+// tile i (tcgen05.ld -> global) overlaps the TMA/MMA main loop of tile i+1; the smem operand ring runs straight
+// through tile boundaries.  Barriers: smem full/empty per stage, tmem_full/tmem_empty per accumulator.
+template <int BN, int EPI>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                               const GemmParams p, const int tiles_m, const int n_tiles) {
+  constexpr int B_TILE_BYTES = BN * BK * 2;
+  constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
+  constexpr int TMEM_COLS = 2 * BN;  // 256 or 512
+  constexpr int N_PER_TILE = EPI == DLI_EPI_SILU_MUL_BF16 ? BN / 2 : BN;  // output features per tile
+
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t bars[2 * MAX_STAGES + 4];
+  __shared__ uint32_t tmem_base_slot;
+
+  const uint32_t tiles = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int stages = p.stages;
+  const uint32_t full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[MAX_STAGES]);
+  const uint32_t tfull0 = smem_u32(&bars[2 * MAX_STAGES]), tempty0 = smem_u32(&bars[2 * MAX_STAGES + 2]);
+  const int n_kb = p.k_blocks;
+
+  pdl_trigger();
+  if (threadIdx.x == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull0 + 8 * a, 1);
+      mbar_init(tempty0 + 8 * a, 4);  // one arrival per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)),
+                 "r"((uint32_t)TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_d = tmem_base_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ===== TMA producer =====
+      int s = 0;
+      uint32_t ph = 0;
+      bool waited = false;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const int a_row0 = (t % tiles_m) * BM, b_row0 = (t / tiles_m) * N_PER_TILE;
+        for (int kb = 0; kb < n_kb; ++kb) {
+          mbar_wait(empty0 + 8 * s, ph ^ 1);
+          const uint32_t a_dst = tiles + s * STAGE_BYTES, b_dst = a_dst + A_TILE_BYTES;
+          mbar_expect_tx(full0 + 8 * s, STAGE_BYTES);
+          if (EPI == DLI_EPI_SILU_MUL_BF16) {  // gate rows then up rows of the same features
+            tma_load_2d(b_dst, &tma_b, full0 + 8 * s, kb * BK, b_row0);
+            tma_load_2d(b_dst + B_TILE_BYTES / 2, &tma_b, full0 + 8 * s, kb * BK, p.up_row_offset + b_row0);
+          } else {
+            tma_load_2d(b_dst, &tma_b, full0 + 8 * s, kb * BK, b_row0);
+          }
+          if (!waited) {  // weights do not depend on the previous kernel; activations do
+            pdl_wait();
+            waited = true;
+          }
+          tma_load_2d(a_dst, &tma_a, full0 + 8 * s, kb * BK, a_row0);
+          if (++s == stages) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {  // ===== MMA issuer =====
+      constexpr uint32_t idesc = umma_idesc_bf16(BN);
+      int s = 0, it = 0;
+      uint32_t ph = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+        const int acc = it & 1;
+        mbar_wait(tempty0 + 8 * acc, (((uint32_t)it >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
+        tcgen05_fence_after();
+        const uint32_t d = tmem_d + (uint32_t)(acc * BN);
+        for (int kb = 0; kb < n_kb; ++kb) {
+          mbar_wait(full0 + 8 * s, ph);
+          tcgen05_fence_after();
+          const uint32_t a_src = tiles + s * STAGE_BYTES;
+          const uint64_t adesc = umma_desc_sw128(a_src), bdesc = umma_desc_sw128(a_src + A_TILE_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) umma_bf16(d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          umma_commit(empty0 + 8 * s);
+          if (++s == stages) { s = 0; ph ^= 1; }
+        }
+        umma_commit(tfull0 + 8 * acc);
+      }
+    }
+  } else {  // ===== epilogue warps =====
+    pdl_wait();
+    const int q = warp & 3;
+    int it = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const int a_row0 = (t % tiles_m) * BM, b_row0 = (t / tiles_m) * N_PER_TILE;
+      mbar_wait(tfull0 + 8 * acc, ((uint32_t)it >> 1) & 1);
+      tcgen05_fence_after();
+      const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+      epilogue_token_major<BN, EPI>(taddr, a_row0 + q * 32 + lane, b_row0, p);
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8 * acc) : "memory");
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TMEM_COLS) : "memory");
+  }
+}
+
 
 // ---- host side ----------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -421,6 +554,43 @@ static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const Ge
     configured = true;
   }
   return launch_kernel("gemm_tcgen05_kernel", kern, grid, dim3(GEMM_THREADS), smem, st, ta, tb, p);
+}
+
+template <int BN, int EPI>
+static int launch_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int tiles_m, int tiles_n,
+                             cudaStream_t st) {
+  constexpr int STAGE_BYTES = A_TILE_BYTES + BN * BK * 2;
+  const size_t smem = (size_t)p.stages * STAGE_BYTES + 1024;
+  static bool configured = false;
+  auto kern = gemm_tcgen05_persistent_kernel<BN, EPI>;
+  if (!configured) {
+    DLI_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+    configured = true;
+  }
+  const int n_tiles = tiles_m * tiles_n;
+  const int grid = n_tiles < sm_count() ? n_tiles : sm_count();
+  return launch_kernel("gemm_tcgen05_persistent_kernel", kern, dim3(grid), dim3(GEMM_THREADS), smem, st, ta, tb, p, tiles_m,
+                       n_tiles);
+}
+
+template <int BN>
+static int launch_persistent_epi(int epi, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int tiles_m,
+                                 int tiles_n, cudaStream_t st) {
+  switch (epi) {
+    case DLI_EPI_STORE_F32: return launch_persistent<BN, DLI_EPI_STORE_F32>(ta, tb, p, tiles_m, tiles_n, st);
+    case DLI_EPI_ADD_F32: return launch_persistent<BN, DLI_EPI_ADD_F32>(ta, tb, p, tiles_m, tiles_n, st);
+    case DLI_EPI_STORE_BF16: return launch_persistent<BN, DLI_EPI_STORE_BF16>(ta, tb, p, tiles_m, tiles_n, st);
+    default: return fail(DLI_ERR_ARG, "unknown epilogue %d", epi);
+  }
+}
+
+static bool persistent_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DLI_NO_PERSISTENT");
+    v = (e && e[0] == '1') ? 0 : 1;
+  }
+  return v == 1;
 }
 
 template <int BN, bool SWAP>
@@ -517,6 +687,12 @@ int launch_gemm_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const CUte
       case 64: return launch_epi<64, true>(epilogue, tmap_w, tmap_x, p, grid, st);
       default: return launch_epi<128, true>(epilogue, tmap_w, tmap_x, p, grid, st);
     }
+  }
+  if (persistent_enabled()) {  // prefill: persistent CTAs, double-buffered TMEM accumulators
+    if (epilogue == DLI_EPI_SILU_MUL_BF16)
+      return launch_persistent<256, DLI_EPI_SILU_MUL_BF16>(tmap_x, tmap_w, p, g.grid_x, g.grid_y, st);
+    if (g.bn == 256) return launch_persistent_epi<256>(epilogue, tmap_x, tmap_w, p, g.grid_x, g.grid_y, st);
+    return launch_persistent_epi<128>(epilogue, tmap_x, tmap_w, p, g.grid_x, g.grid_y, st);
   }
   if (epilogue == DLI_EPI_SILU_MUL_BF16) return launch_variant<256, DLI_EPI_SILU_MUL_BF16, false>(tmap_x, tmap_w, p, grid, st);
   if (g.bn == 256) return launch_epi<256, false>(epilogue, tmap_x, tmap_w, p, grid, st);
