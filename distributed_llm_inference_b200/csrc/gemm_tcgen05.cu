@@ -389,10 +389,23 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
 // CTAs share weight tiles in L2).  The accumulator is double-buffered in TMEM (2 x BN columns), so the epilogue of
 // tile i (tcgen05.ld -> global) overlaps the TMA/MMA main loop of tile i+1; the smem operand ring runs straight
 // through tile boundaries.  Barriers: smem full/empty per stage, tmem_full/tmem_empty per accumulator.
+// Tile rasterisation of the persistent kernel: bands of `group_m` token tiles; inside a band feature tiles advance
+// slowest-but-one, so the CTAs running at any moment cover (group_m token tiles) x (a few feature tiles): the band's
+// activations stay in L2 for the whole sweep and every weight tile is fetched from HBM once per band (ncu on the
+// naive order showed 8x the algorithmic DRAM traffic: the full activation matrix did not survive in L2).
+__device__ __forceinline__ void tile_coords(int t, int tiles_m, int tiles_n, int group_m, int& mt, int& nt) {
+  const int band_sz = group_m * tiles_n;
+  const int band = t / band_sz, r = t - band * band_sz;
+  const int gsize = min(group_m, tiles_m - band * group_m);
+  nt = r / gsize;
+  mt = band * group_m + (r - nt * gsize);
+}
+
 template <int BN, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-                               const GemmParams p, const int tiles_m, const int n_tiles) {
+                               const GemmParams p, const int tiles_m, const int tiles_n, const int group_m) {
+  const int n_tiles = tiles_m * tiles_n;
   constexpr int B_TILE_BYTES = BN * BK * 2;
   constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
   constexpr int TMEM_COLS = 2 * BN;  // 256 or 512
@@ -440,7 +453,9 @@ gemm_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const 
       uint32_t ph = 0;
       bool waited = false;
       for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        const int a_row0 = (t % tiles_m) * BM, b_row0 = (t / tiles_m) * N_PER_TILE;
+        int mt, nt;
+        tile_coords(t, tiles_m, tiles_n, group_m, mt, nt);
+        const int a_row0 = mt * BM, b_row0 = nt * N_PER_TILE;
         for (int kb = 0; kb < n_kb; ++kb) {
           mbar_wait(empty0 + 8 * s, ph ^ 1);
           const uint32_t a_dst = tiles + s * STAGE_BYTES, b_dst = a_dst + A_TILE_BYTES;
@@ -489,7 +504,9 @@ gemm_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const 
     int it = 0;
     for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
       const int acc = it & 1;
-      const int a_row0 = (t % tiles_m) * BM, b_row0 = (t / tiles_m) * N_PER_TILE;
+      int mt, nt;
+      tile_coords(t, tiles_m, tiles_n, group_m, mt, nt);
+      const int a_row0 = mt * BM, b_row0 = nt * N_PER_TILE;
       mbar_wait(tfull0 + 8 * acc, ((uint32_t)it >> 1) & 1);
       tcgen05_fence_after();
       const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
@@ -569,8 +586,16 @@ static int launch_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const
   }
   const int n_tiles = tiles_m * tiles_n;
   const int grid = n_tiles < sm_count() ? n_tiles : sm_count();
+  static int group_env = -1;
+  if (group_env < 0) {
+    const char* e = getenv("DLI_GROUP_M");
+    group_env = e ? atoi(e) : 0;
+  }
+  // band height: activations of a band (group_m x 128 tokens x K) should fit comfortably in one die's share of L2
+  int group_m = group_env > 0 ? group_env : 16;
+  if (group_m > tiles_m) group_m = tiles_m;
   return launch_kernel("gemm_tcgen05_persistent_kernel", kern, dim3(grid), dim3(GEMM_THREADS), smem, st, ta, tb, p, tiles_m,
-                       n_tiles);
+                       tiles_n, group_m);
 }
 
 template <int BN>
