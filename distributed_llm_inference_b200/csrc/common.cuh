@@ -73,6 +73,17 @@ struct KvView {
 };
 int kv_view(const dli_kv_desc* kv, int layer, KvView* out);
 
+// Arguments of the fused q|k|v projection epilogue (prefill): RoPE + paged KV append straight from the accumulator.
+struct RopeArgs {
+  const float* cos;  // [q_len, hd]
+  const float* sin;
+  __nv_bfloat16* q_out;  // [tokens, H * hd]
+  KvView kv;
+  int q_len, H, KV, hd;
+};
+constexpr int DLI_EPI_QKV_ROPE_INTERNAL = 4;  // not part of the public enum: only the span runner uses it
+bool gemm_persistent_enabled();
+
 // ---- GEMM planning / launch (gemm_tcgen05.cu) --------------------------------------------------------
 struct GemmPlan {
   bool swap;          // weights are the 128-row MMA operand (decode); else tokens are
@@ -84,7 +95,7 @@ struct GemmPlan {
 GemmPlan plan_gemm(int m, int n, int k, int epilogue);
 int make_tmap_bf16(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld, int box_rows);
 int launch_gemm_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const CUtensorMap& tmap_w, void* out,
-                        long long ldo, int m, int n, int epilogue, cudaStream_t st);
+                        long long ldo, int m, int n, int epilogue, cudaStream_t st, const RopeArgs* rope = nullptr);
 int launch_gemm(const void* x, long long ldx, const void* w, void* out, long long ldo, int m, int n, int k,
                 int epilogue, cudaStream_t st);
 

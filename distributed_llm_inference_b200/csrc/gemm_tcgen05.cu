@@ -37,6 +37,7 @@ struct GemmParams {
   int k_blocks, kb_per_split;
   int stages;
   int up_row_offset;  // SILU epilogue: row of w where up_proj starts (= n_features)
+  RopeArgs rope;      // QKV_ROPE epilogue only
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------------
@@ -187,6 +188,83 @@ __device__ __forceinline__ void epilogue_token_major(uint32_t taddr, int arow, i
     }
   }
 }
+}
+
+// Fused epilogue of the q|k|v projection at prefill (token-major tile of 256 features = whole heads): rotates q and
+// k with the token's cos/sin rows (modules.py:17-20), writes q densely and k / v into the sequence's page slot
+// (cache.py:103-109) — the fp32 projection never goes to HBM and no separate RoPE kernel runs.
+template <int BN>
+__device__ __forceinline__ void epilogue_qkv_rope(uint32_t taddr, int token, int b_row0, const GemmParams& p) {
+  const RopeArgs& r = p.rope;
+  const int hd = r.hd, half = hd >> 1;
+  const bool t_ok = token < p.m_tokens;
+  int l = 0;
+  long long slot_off = 0;  // element offset of (page, kv head 0, slot, 0) for this token
+  if (t_ok) {
+    const int b = token / r.q_len;
+    l = token - b * r.q_len;
+    const int pos = r.kv.seq_lens[b] + l;
+    const int page = r.kv.block_table[(long long)b * r.kv.max_pages + pos / r.kv.page_tokens];
+    slot_off = ((long long)page * r.KV * r.kv.page_tokens + pos % r.kv.page_tokens) * hd;
+  }
+  const long long head_stride = (long long)r.kv.page_tokens * hd;  // between kv heads inside a page
+  const float* cs = r.cos + (long long)l * hd;
+  const float* sn = r.sin + (long long)l * hd;
+  uint32_t lo[16], hi[16];
+#pragma unroll 1
+  for (int h0 = 0; h0 < BN; h0 += hd) {
+    const int f_head = b_row0 + h0;
+    if (f_head >= p.n_features) break;  // warp-uniform
+    const int head = f_head / hd;
+    if (head >= r.H + r.KV) {  // value head: plain conversion
+      __nv_bfloat16* dst = r.kv.v + slot_off + (long long)(head - r.H - r.KV) * head_stride;
+#pragma unroll 1
+      for (int c0 = 0; c0 < hd; c0 += 16) {
+        tmem_ld16(taddr + h0 + c0, lo);
+        tmem_ld_wait();
+        if (t_ok) {
+          uint32_t w[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) w[j] = pack_bf16(__uint_as_float(lo[2 * j]), __uint_as_float(lo[2 * j + 1]));
+          *reinterpret_cast<uint4*>(dst + c0) = make_uint4(w[0], w[1], w[2], w[3]);
+          *reinterpret_cast<uint4*>(dst + c0 + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+        }
+      }
+    } else {
+      __nv_bfloat16* dst = head < r.H ? r.q_out + ((long long)token * r.H + head) * hd
+                                      : r.kv.k + slot_off + (long long)(head - r.H) * head_stride;
+#pragma unroll 1
+      for (int c0 = 0; c0 < half; c0 += 16) {
+        tmem_ld16(taddr + h0 + c0, lo);
+        tmem_ld16(taddr + h0 + half + c0, hi);
+        tmem_ld_wait();
+        if (t_ok) {
+          uint32_t wl[8], wh[8];
+#pragma unroll
+          for (int j = 0; j < 16; j += 4) {
+            const float4 c1 = *reinterpret_cast<const float4*>(cs + c0 + j), c2 = *reinterpret_cast<const float4*>(cs + half + c0 + j);
+            const float4 s1 = *reinterpret_cast<const float4*>(sn + c0 + j), s2 = *reinterpret_cast<const float4*>(sn + half + c0 + j);
+            const float x1[4] = {__uint_as_float(lo[j]), __uint_as_float(lo[j + 1]), __uint_as_float(lo[j + 2]), __uint_as_float(lo[j + 3])};
+            const float x2[4] = {__uint_as_float(hi[j]), __uint_as_float(hi[j + 1]), __uint_as_float(hi[j + 2]), __uint_as_float(hi[j + 3])};
+            const float cc1[4] = {c1.x, c1.y, c1.z, c1.w}, cc2[4] = {c2.x, c2.y, c2.z, c2.w};
+            const float ss1[4] = {s1.x, s1.y, s1.z, s1.w}, ss2[4] = {s2.x, s2.y, s2.z, s2.w};
+            float o1[4], o2[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              o1[e] = x1[e] * cc1[e] - x2[e] * ss1[e];  // rotate_half: first half pairs with -x2
+              o2[e] = x2[e] * cc2[e] + x1[e] * ss2[e];
+            }
+            wl[j / 2] = pack_bf16(o1[0], o1[1]); wl[j / 2 + 1] = pack_bf16(o1[2], o1[3]);
+            wh[j / 2] = pack_bf16(o2[0], o2[1]); wh[j / 2 + 1] = pack_bf16(o2[2], o2[3]);
+          }
+          *reinterpret_cast<uint4*>(dst + c0) = make_uint4(wl[0], wl[1], wl[2], wl[3]);
+          *reinterpret_cast<uint4*>(dst + c0 + 8) = make_uint4(wl[4], wl[5], wl[6], wl[7]);
+          *reinterpret_cast<uint4*>(dst + half + c0) = make_uint4(wh[0], wh[1], wh[2], wh[3]);
+          *reinterpret_cast<uint4*>(dst + half + c0 + 8) = make_uint4(wh[4], wh[5], wh[6], wh[7]);
+        }
+      }
+    }
+  }
 }
 
 // ---- kernel -------------------------------------------------------------------------------------------
@@ -510,7 +588,8 @@ gemm_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const 
       mbar_wait(tfull0 + 8 * acc, ((uint32_t)it >> 1) & 1);
       tcgen05_fence_after();
       const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
-      epilogue_token_major<BN, EPI>(taddr, a_row0 + q * 32 + lane, b_row0, p);
+      if constexpr (EPI == DLI_EPI_QKV_ROPE_INTERNAL) epilogue_qkv_rope<BN>(taddr, a_row0 + q * 32 + lane, b_row0, p);
+      else epilogue_token_major<BN, EPI>(taddr, a_row0 + q * 32 + lane, b_row0, p);
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8 * acc) : "memory");
@@ -618,6 +697,8 @@ static bool persistent_enabled() {
   return v == 1;
 }
 
+bool gemm_persistent_enabled() { return persistent_enabled(); }
+
 template <int BN, bool SWAP>
 static int launch_epi(int epi, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid, cudaStream_t st) {
   switch (epi) {
@@ -632,7 +713,7 @@ GemmPlan plan_gemm(int m, int n, int k, int epilogue) {
   GemmPlan g{};
   g.k_blocks = (k + BK - 1) / BK;
   const int sms = sm_count();
-  if (m <= 128) {
+  if (m <= 128 && epilogue != DLI_EPI_QKV_ROPE_INTERNAL) {
     const bool fused_silu = epilogue == DLI_EPI_SILU_MUL_BF16;  // 64 gate + 64 up rows per CTA, never split
     g.swap = true;
     g.bn = m <= 16 ? 16 : m <= 32 ? 32 : m <= 64 ? 64 : 128;
@@ -670,6 +751,7 @@ GemmPlan plan_gemm(int m, int n, int k, int epilogue) {
     } else {
       auto waves = [&](int bn) { return (double)(((long long)tm * ((n + bn - 1) / bn) + sms - 1) / sms) * bn; };
       g.bn = (n % 256 == 0 && waves(256) * 0.95 <= waves(128)) ? 256 : 128;
+      if (epilogue == DLI_EPI_QKV_ROPE_INTERNAL) g.bn = 256;  // whole heads per tile
       g.b_box_rows = g.bn;
       g.grid_y = (n + g.bn - 1) / g.bn;
     }
@@ -685,8 +767,13 @@ GemmPlan plan_gemm(int m, int n, int k, int epilogue) {
 }
 
 int launch_gemm_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const CUtensorMap& tmap_w, void* out, long long ldo,
-                        int m, int n, int epilogue, cudaStream_t st) {
+                        int m, int n, int epilogue, cudaStream_t st, const RopeArgs* rope) {
   GemmParams p{};
+  if (epilogue == DLI_EPI_QKV_ROPE_INTERNAL) {
+    if (!rope || g.swap || g.bn != 256 || n % 256 != 0 || 256 % rope->hd != 0 || !persistent_enabled())
+      return fail(DLI_ERR_ARG, "fused qkv+rope epilogue needs the persistent 256-column path");
+    p.rope = *rope;
+  }
   p.out = out;
   p.ldo = ldo;
   p.m_tokens = m;
@@ -714,6 +801,8 @@ int launch_gemm_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const CUte
     }
   }
   if (persistent_enabled()) {  // prefill: persistent CTAs, double-buffered TMEM accumulators
+    if (epilogue == DLI_EPI_QKV_ROPE_INTERNAL)
+      return launch_persistent<256, DLI_EPI_QKV_ROPE_INTERNAL>(tmap_x, tmap_w, p, g.grid_x, g.grid_y, st);
     if (epilogue == DLI_EPI_SILU_MUL_BF16)
       return launch_persistent<256, DLI_EPI_SILU_MUL_BF16>(tmap_x, tmap_w, p, g.grid_x, g.grid_y, st);
     if (g.bn == 256) return launch_persistent_epi<256>(epilogue, tmap_x, tmap_w, p, g.grid_x, g.grid_y, st);

@@ -173,7 +173,7 @@ static int prof_mark(dli_span* s, int cls, cudaStream_t st) {
 
 // one linear layer of the span: out (+)= x[m, k] . w[n, k]^T through the planned tcgen05 kernel
 static int span_gemm(dli_span* s, const void* x, const WeightMaps& wm, void* out, long long ldo, int m, int n, int k,
-                     int epilogue, cudaStream_t st) {
+                     int epilogue, cudaStream_t st, const RopeArgs* rope = nullptr) {
   const GemmPlan g = plan_gemm(m, n, k, epilogue);
   const int x_box = g.swap ? g.b_box_rows : g.a_box_rows;
   const int w_box = g.swap ? g.a_box_rows : g.b_box_rows;
@@ -181,7 +181,7 @@ static int span_gemm(dli_span* s, const void* x, const WeightMaps& wm, void* out
   int rc = act_map(s, x, m, k, x_box, &tx);
   if (rc) return rc;
   const CUtensorMap& tw = w_box == 256 ? wm.box256 : w_box == 64 ? wm.box64 : wm.box128;
-  return launch_gemm_planned(g, *tx, tw, out, ldo, m, n, epilogue, st);
+  return launch_gemm_planned(g, *tx, tw, out, ldo, m, n, epilogue, st, rope);
 }
 
 }  // namespace dli
@@ -363,14 +363,22 @@ int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, i
                         j == 0 ? w.resid : nullptr, hs ? hs + (size_t)j * M * h : nullptr, M, h, d.eps_input, 1.0f, st);
     if (rc) return rc;
     // q|k|v projection (modules.py:61-63)
-    float* qkv = skinny ? w.qkv_acc : w.qkv;
+    // prefill: RoPE + KV append are the epilogue of the projection GEMM (whole heads per 256-column tile)
+    const bool fused_rope = !skinny && s->n_qkv % 256 == 0 && gemm_persistent_enabled();
     DLI_MARK(DLI_PROF_GEMM_QKV);
-    rc = span_gemm(s, w.xn, L.qkv, qkv, s->n_qkv, M, s->n_qkv, h, skinny ? DLI_EPI_ADD_F32 : DLI_EPI_STORE_F32, st);
-    if (rc) return rc;
-    // RoPE + cache append (modules.py:73-85, cache.py:103-109); re-zeroes the split-K accumulation buffer behind itself
-    DLI_MARK(DLI_PROF_ROPE_APPEND);
-    rc = launch_rope_kv_append(qkv, skinny, cos, sin, w.qbuf, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim, st);
-    if (rc) return rc;
+    if (fused_rope) {
+      RopeArgs ra{cos, sin, w.qbuf, view, q_len, d.n_heads, d.n_kv_heads, d.head_dim};
+      rc = span_gemm(s, w.xn, L.qkv, nullptr, 0, M, s->n_qkv, h, DLI_EPI_QKV_ROPE_INTERNAL, st, &ra);
+      if (rc) return rc;
+    } else {
+      float* qkv = skinny ? w.qkv_acc : w.qkv;
+      rc = span_gemm(s, w.xn, L.qkv, qkv, s->n_qkv, M, s->n_qkv, h, skinny ? DLI_EPI_ADD_F32 : DLI_EPI_STORE_F32, st);
+      if (rc) return rc;
+      // RoPE + cache append (modules.py:73-85, cache.py:103-109); re-zeroes the split-K accumulation buffer behind itself
+      DLI_MARK(DLI_PROF_ROPE_APPEND);
+      rc = launch_rope_kv_append(qkv, skinny, cos, sin, w.qbuf, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim, st);
+      if (rc) return rc;
+    }
     // attention core (modules.py:87-105)
     DLI_MARK(DLI_PROF_ATTENTION);
     if (q_len == 1)

@@ -85,6 +85,26 @@ def test_span_matches_oracle_live_two_generations_and_hidden_states():
         assert gc.get_seq_length(0, gid) == oc.get_seq_length(0, gid) == lens[gid]
 
 
+@pytest.mark.parametrize("shape_name,B,L1,L2,rope", [("test_gqa", 2, 150, 140, "float"), ("test_hd128", 1, 300, 129, "float"),
+                                                       ("test_gqa", 1, 257, 130, "literal")])
+def test_chunked_prefill_matches_oracle(shape_name, B, L1, L2, rope):
+    """Chunks of more than 128 tokens take the token-major tcgen05 path whose q|k|v epilogue applies RoPE and
+    appends to the pages (hd 64: four heads per tile, hd 128: two); the second chunk attends to a cached past."""
+    shp = syn.SHAPES[shape_name]
+    W = syn.make_span_weights(shp, [0, 1], norm_jitter=0.1)
+    blk = gpu_make_span(shp, W, "eager", rope)
+    osp = oracle_make_span(shp, W, "eager", rope)
+    gc, oc = gpu_make_cache(4096, 4), so.SinkCacheOracle(4096, 4)
+    pos = 0
+    for step, L in enumerate([L1, L2, 1]):
+        x = syn.make_hidden(shp, B, L, seed=20 + step)
+        cp = torch.arange(pos, pos + L)
+        ref = osp.forward("g", x.float(), past_key_value=oc, cache_position=cp)[0]
+        got = blk("g", x.to(DEV), past_key_value=gc, cache_position=cp.to(DEV))[0]
+        _check(f"chunk{step}", got.float().cpu().numpy(), ref.numpy())
+        pos += L
+
+
 def test_graphed_decode_matches_oracle():
     """Whole-step CUDA graph (the B200 counterpart of utils/cuda.py:6-77): replayed steps against the oracle."""
     shp = syn.SHAPES["test_hd128"]
