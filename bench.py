@@ -118,11 +118,11 @@ def decode_step_bytes(shape: syn.LlamaShape, n_layers: int, batch: int, ctx: int
             "per_gemm_per_layer": per_gemm}
 
 
-def build_span(shape: syn.LlamaShape, layer_ids, device, rope="float"):
+def build_span(shape: syn.LlamaShape, layer_ids, device, rope="float", max_positions: int = 8192):
     from distributed_llm_inference_b200.models.llama import LlamaBlock
 
     with torch.device(device):
-        blk = LlamaBlock(shape.to_hf_config("eager"), list(layer_ids), rope=rope)
+        blk = LlamaBlock(shape.to_hf_config("eager", max_positions), list(layer_ids), rope=rope)
     for j, g in enumerate(layer_ids):   # random-init of the architecture, generated on the device
         w = syn.make_layer_weights(shape, g, device=device)
         blk.load_state_dict({f"layers.{j}.{n}.weight": t for n, t in w.items()}, strict=False)
@@ -237,7 +237,7 @@ def run_ours(args):
     n_mb = args.micro_batches or world   # micro-batches in flight (default: the pipeline depth)
     total_ctx = PROMPT + W + K + 8 + 32 + 8
 
-    blk = build_span(shape, layer_ids, dev)
+    blk = build_span(shape, layer_ids, dev, max_positions=max(8192, total_ctx + 64))
     cache = PartialLlamaSinkCache(1 << 20, 4, page_tokens=16,
                                   capacity_tokens=n_mb * BATCH * (total_ctx + 16) + BATCH * 64 + BATCH * (PROMPT + 16))
     stage = PipelineStage(blk, cache, rank, world, dev)
@@ -465,12 +465,15 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--batch", type=int, default=None, help="override the batch (experiments; the default is the config's 16)")
     ap.add_argument("--model", default=None, choices=["7b", "13b", "70b", "tiny"], help="shape (default: configs[1], 7b)")
+    ap.add_argument("--prompt", type=int, default=None, help="prompt length (default 512, the config's)")
     ap.add_argument("--layers", type=int, default=None, help="total layers over all stages (default: the model's)")
     ap.add_argument("--micro-batches", type=int, default=None, help="micro-batches in flight (default: number of stages)")
     ap.add_argument("--nccl-handoff", action="store_true", help="hand off by NCCL isend/irecv instead of peer stores")
     ap.add_argument("--no-graph", action="store_true", help="decode with eager launches instead of the CUDA graph")
     args = ap.parse_args()
-    global BATCH, MODEL
+    global BATCH, MODEL, PROMPT
+    if args.prompt:
+        PROMPT = args.prompt
     if args.batch:
         BATCH = args.batch
     if args.model:

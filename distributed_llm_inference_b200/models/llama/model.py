@@ -229,6 +229,9 @@ class LlamaBlock(nn.Module):
             cache.evict(gid, L, self._table[0, p0:p0 + W], self._table[1, p0:p0 + W])
             past = gen.length
         gen = cache.reserve(gid, B, past + L)
+        if gen.first_pos + gen.seen_tokens + L > self.max_positions and (gen.length or gen.seen_tokens):
+            raise ValueError(f"position {gen.first_pos + gen.seen_tokens + L} exceeds max_position_embeddings="
+                             f"{self.max_positions} (the rotary table)")
         if gen.length == 0 and gen.seen_tokens == 0:
             gen.first_pos = int(position_ids[0, 0].item()) if (cache_position_given or position_ids_given) else 0
         max_ctx = past + L

@@ -41,14 +41,14 @@ class LlamaShape:
     def layer_weight_bytes(self, elt: int = 2) -> int:
         return elt * (sum(a * b for a, b in self.linear_shapes().values()) + 2 * self.hidden_size)
 
-    def to_hf_config(self, attn_implementation: str = "eager"):
+    def to_hf_config(self, attn_implementation: str = "eager", max_position_embeddings: int = 8192):
         from transformers import LlamaConfig
 
         cfg = LlamaConfig(
             hidden_size=self.hidden_size, intermediate_size=self.intermediate_size,
             num_attention_heads=self.num_attention_heads, num_key_value_heads=self.num_key_value_heads,
             num_hidden_layers=self.num_hidden_layers, vocab_size=self.vocab_size,
-            max_position_embeddings=8192,
+            max_position_embeddings=max_position_embeddings,
             rope_parameters={"rope_type": "default", "rope_theta": self.rope_theta},
             attention_bias=False, mlp_bias=False, pretraining_tp=1, head_dim=self.head_dim,
         )
