@@ -8,17 +8,16 @@
 // (model.py:94-101 + modules.py:92-94); `causal` == 1 the eager mask of model.py:103-127.
 //
 // Round-1 implementation: warp-level mma.sync (m16n8k16, bf16 -> fp32) with ldmatrix-fed fragments; one
-// CTA = 64 queries of one head (4 warps x 16 rows), K/V tiles of 64 keys gathered from pages with
-// cp.async into XOR-swizzled shared memory.  Attention is <= 7 % of prefill FLOPs at 8k context
+// CTA = 64 or 128 queries of one head (4 or 8 warps x 16 rows), K/V tiles of 64 keys gathered from pages with
+// cp.async into XOR-swizzled, double-buffered shared memory (the next tile loads while this one is consumed).  Attention is <= 7 % of prefill FLOPs at 8k context
 // (SURVEY 8d); the tcgen05 version is later work.
 #include "common.cuh"
 
 #include <math.h>
+#include <stdlib.h>
 
 namespace dli {
 
-constexpr int PF_THREADS = 128;
-constexpr int PF_BM = 64;
 constexpr int PF_BN = 64;
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int src_bytes) {
@@ -48,17 +47,20 @@ __device__ __forceinline__ uint32_t swz(int r, int c) {
   return (uint32_t)(r * HD * 2 + ((c ^ (r & 7)) << 4));
 }
 
-template <int HD>
-__global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const __nv_bfloat16* __restrict__ q,
-                                                                  __nv_bfloat16* __restrict__ out, KvView kv, int q_len,
-                                                                  int H, int KV, int causal, float scale_log2) {
-  constexpr int CPR = HD / 8;  // 16-byte chunks per row
+template <int HD, int NWARPS, int NBUF>
+__global__ void __launch_bounds__(NWARPS * 32) prefill_attn_kernel(const __nv_bfloat16* __restrict__ q,
+                                                                   __nv_bfloat16* __restrict__ out, KvView kv, int q_len,
+                                                                   int H, int KV, int causal, float scale_log2) {
+  constexpr int CPR = HD / 8;          // 16-byte chunks per row
+  constexpr int BM = NWARPS * 16;      // queries per CTA
+  constexpr int NT = NWARPS * 32;
+  constexpr int KV_TILE_BYTES = PF_BN * HD * 2;
   extern __shared__ __align__(128) uint8_t pf_smem[];
-  const uint32_t sQ = smem_u32(pf_smem), sK = sQ + PF_BM * HD * 2, sV = sK + PF_BN * HD * 2;
+  const uint32_t sQ = smem_u32(pf_smem), sK0 = sQ + BM * HD * 2, sV0 = sK0 + NBUF * KV_TILE_BYTES;  // K[NBUF], V[NBUF]
 
   pdl_trigger();
   pdl_wait();
-  const int m0 = blockIdx.x * PF_BM, h = blockIdx.y, b = blockIdx.z;
+  const int m0 = blockIdx.x * BM, h = blockIdx.y, b = blockIdx.z;
   const int kvh = h / (H / KV);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, t4 = lane & 3;
@@ -66,40 +68,14 @@ __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const __nv_bfl
   const int T = past + q_len;
   const int32_t* bt = kv.block_table + (long long)b * kv.max_pages;
 
-  // ---- Q tile -> smem (rows beyond q_len are zero) ----
-  for (int i = threadIdx.x; i < PF_BM * CPR; i += PF_THREADS) {
-    const int r = i / CPR, c = i - r * CPR;
-    const int qi = m0 + r;
-    const bool ok = qi < q_len;
-    const __nv_bfloat16* src = q + (((long long)b * q_len + (ok ? qi : 0)) * H + h) * HD + c * 8;
-    cp_async16(sQ + swz<HD>(r, c), src, ok ? 16 : 0);
-  }
-  cp_async_wait_all();
-  __syncthreads();
-
-  // Q fragments of this warp's 16 rows, all k-slices
-  uint32_t qa[HD / 16][4];
-#pragma unroll
-  for (int ks = 0; ks < HD / 16; ++ks) {
-    const int r = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
-    const int c = ks * 2 + (lane >> 4);
-    ldsm_x4(sQ + swz<HD>(r, c), qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3]);
-  }
-
-  float o[HD / 8][4];
-#pragma unroll
-  for (int n = 0; n < HD / 8; ++n) o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f;
-  float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
-
-  const int pos0 = past + m0 + warp * 16 + g;  // absolute position of this thread's first row (second: +8)
   int kv_end = T;
-  if (causal) kv_end = min(T, past + m0 + PF_BM);
+  if (causal) kv_end = min(T, past + m0 + BM);
   const int n_tiles = (kv_end + PF_BN - 1) / PF_BN;
 
-  for (int tile = 0; tile < n_tiles; ++tile) {
+  auto load_kv = [&](int tile) {  // K/V rows of keys [tile*64, +64) -> buffer tile&1 (zeros past T)
     const int j0 = tile * PF_BN;
-    __syncthreads();  // previous tile's K/V fully consumed
-    for (int i = threadIdx.x; i < PF_BN * CPR; i += PF_THREADS) {
+    const uint32_t sK = sK0 + (tile % NBUF) * KV_TILE_BYTES, sV = sV0 + (tile % NBUF) * KV_TILE_BYTES;
+    for (int i = threadIdx.x; i < PF_BN * CPR; i += NT) {
       const int r = i / CPR, c = i - r * CPR;
       const int j = j0 + r;
       const bool ok = j < T;
@@ -111,80 +87,129 @@ __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const __nv_bfl
       cp_async16(sK + swz<HD>(r, c), kv.k + off, ok ? 16 : 0);
       cp_async16(sV + swz<HD>(r, c), kv.v + off, ok ? 16 : 0);
     }
-    cp_async_wait_all();
+  };
+
+  // ---- Q tile (rows beyond q_len are zero) + first K/V tile ----
+  for (int i = threadIdx.x; i < BM * CPR; i += NT) {
+    const int r = i / CPR, c = i - r * CPR;
+    const int qi = m0 + r;
+    const bool ok = qi < q_len;
+    const __nv_bfloat16* src = q + (((long long)b * q_len + (ok ? qi : 0)) * H + h) * HD + c * 8;
+    cp_async16(sQ + swz<HD>(r, c), src, ok ? 16 : 0);
+  }
+  load_kv(0);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+
+  uint32_t qa[HD / 16][4];
+  float o[HD / 8][4];
+#pragma unroll
+  for (int n = 0; n < HD / 8; ++n) o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f;
+  float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
+  const int pos0 = past + m0 + warp * 16 + g;        // absolute position of this thread's first row (second: +8)
+  const int warp_last_pos = past + m0 + warp * 16 + 15;
+
+  for (int tile = 0; tile < n_tiles; ++tile) {
+    const int j0 = tile * PF_BN;
+    if (NBUF == 1 && tile > 0) {  // single buffer (more CTAs per SM hide the load instead)
+      load_kv(tile);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    if (NBUF == 2 && tile + 1 < n_tiles) {  // prefetch the next tile into the other buffer while this one is consumed
+      load_kv(tile + 1);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
     __syncthreads();
-
-    // ---- S = Q K^T (16 x 64 per warp) ----
-    float s[PF_BN / 8][4];
+    if (tile == 0) {  // Q fragments of this warp's 16 rows, all k-slices
 #pragma unroll
-    for (int n = 0; n < PF_BN / 8; ++n) s[n][0] = s[n][1] = s[n][2] = s[n][3] = 0.f;
-#pragma unroll
-    for (int ks = 0; ks < HD / 16; ++ks) {
-#pragma unroll
-      for (int np = 0; np < PF_BN / 16; ++np) {
-        uint32_t b0, b1, b2, b3;
-        const int r = np * 16 + (lane & 7) + (lane >> 4) * 8;
-        const int c = ks * 2 + ((lane >> 3) & 1);
-        ldsm_x4(sK + swz<HD>(r, c), b0, b1, b2, b3);
-        mma_bf16_16816(s[2 * np], qa[ks], b0, b1);
-        mma_bf16_16816(s[2 * np + 1], qa[ks], b2, b3);
+      for (int ks = 0; ks < HD / 16; ++ks) {
+        const int r = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+        const int c = ks * 2 + (lane >> 4);
+        ldsm_x4(sQ + swz<HD>(r, c), qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3]);
       }
     }
+    const uint32_t sK = sK0 + (tile % NBUF) * KV_TILE_BYTES, sV = sV0 + (tile % NBUF) * KV_TILE_BYTES;
 
-    // ---- mask + online softmax ----
-    float mx[2] = {-INFINITY, -INFINITY};
+    if (!causal || j0 <= warp_last_pos) {  // warp-uniform: tiles entirely above this warp's diagonal are skipped
+      // ---- S = Q K^T (16 x 64 per warp) ----
+      float s[PF_BN / 8][4];
 #pragma unroll
-    for (int n = 0; n < PF_BN / 8; ++n) {
+      for (int n = 0; n < PF_BN / 8; ++n) s[n][0] = s[n][1] = s[n][2] = s[n][3] = 0.f;
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const int j = j0 + n * 8 + 2 * t4 + (e & 1);
-        const int pos = pos0 + (e >> 1) * 8;
-        const bool ok = j < T && (!causal || j <= pos);
-        s[n][e] = ok ? s[n][e] * scale_log2 : -INFINITY;
-        mx[e >> 1] = fmaxf(mx[e >> 1], s[n][e]);
+      for (int ks = 0; ks < HD / 16; ++ks) {
+#pragma unroll
+        for (int np = 0; np < PF_BN / 16; ++np) {
+          uint32_t b0, b1, b2, b3;
+          const int r = np * 16 + (lane & 7) + (lane >> 4) * 8;
+          const int c = ks * 2 + ((lane >> 3) & 1);
+          ldsm_x4(sK + swz<HD>(r, c), b0, b1, b2, b3);
+          mma_bf16_16816(s[2 * np], qa[ks], b0, b1);
+          mma_bf16_16816(s[2 * np + 1], qa[ks], b2, b3);
+        }
+      }
+
+      // ---- mask (only on tiles that touch the diagonal or the end of the context) + online softmax ----
+      const bool need_mask = (j0 + PF_BN > T) || (causal && j0 + PF_BN - 1 > past + m0 + warp * 16);
+      float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+      for (int n = 0; n < PF_BN / 8; ++n) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          float v = s[n][e] * scale_log2;
+          if (need_mask) {
+            const int j = j0 + n * 8 + 2 * t4 + (e & 1);
+            const int pos = pos0 + (e >> 1) * 8;
+            if (!(j < T && (!causal || j <= pos))) v = -INFINITY;
+          }
+          s[n][e] = v;
+          mx[e >> 1] = fmaxf(mx[e >> 1], v);
+        }
+      }
+      float corr[2], mref[2];
+#pragma unroll
+      for (int r2 = 0; r2 < 2; ++r2) {
+        mx[r2] = fmaxf(mx[r2], __shfl_xor_sync(0xffffffffu, mx[r2], 1));
+        mx[r2] = fmaxf(mx[r2], __shfl_xor_sync(0xffffffffu, mx[r2], 2));
+        const float mn = fmaxf(mrow[r2], mx[r2]);
+        mref[r2] = mn == -INFINITY ? 0.f : mn;
+        corr[r2] = exp2f(mrow[r2] - mref[r2]);
+        mrow[r2] = mn;
+        lrow[r2] *= corr[r2];
+      }
+#pragma unroll
+      for (int n = 0; n < HD / 8; ++n) {
+        o[n][0] *= corr[0]; o[n][1] *= corr[0];
+        o[n][2] *= corr[1]; o[n][3] *= corr[1];
+      }
+      uint32_t pa[PF_BN / 16][4];
+#pragma unroll
+      for (int n = 0; n < PF_BN / 8; ++n) {
+        const float p0 = exp2f(s[n][0] - mref[0]), p1 = exp2f(s[n][1] - mref[0]);
+        const float p2 = exp2f(s[n][2] - mref[1]), p3 = exp2f(s[n][3] - mref[1]);
+        lrow[0] += p0 + p1;
+        lrow[1] += p2 + p3;
+        // C layout of two adjacent 8-key tiles == A layout of one 16-key slice
+        pa[n >> 1][(n & 1) * 2 + 0] = pack_bf16(p0, p1);
+        pa[n >> 1][(n & 1) * 2 + 1] = pack_bf16(p2, p3);
+      }
+
+      // ---- O += P V ----
+#pragma unroll
+      for (int ks = 0; ks < PF_BN / 16; ++ks) {
+#pragma unroll
+        for (int np = 0; np < HD / 16; ++np) {
+          uint32_t b0, b1, b2, b3;
+          const int r = ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+          const int c = np * 2 + (lane >> 4);
+          ldsm_x4_trans(sV + swz<HD>(r, c), b0, b1, b2, b3);
+          mma_bf16_16816(o[2 * np], pa[ks], b0, b1);
+          mma_bf16_16816(o[2 * np + 1], pa[ks], b2, b3);
+        }
       }
     }
-    float corr[2], mref[2];
-#pragma unroll
-    for (int r2 = 0; r2 < 2; ++r2) {
-      mx[r2] = fmaxf(mx[r2], __shfl_xor_sync(0xffffffffu, mx[r2], 1));
-      mx[r2] = fmaxf(mx[r2], __shfl_xor_sync(0xffffffffu, mx[r2], 2));
-      const float mn = fmaxf(mrow[r2], mx[r2]);
-      mref[r2] = mn == -INFINITY ? 0.f : mn;
-      corr[r2] = exp2f(mrow[r2] - mref[r2]);
-      mrow[r2] = mn;
-      lrow[r2] *= corr[r2];
-    }
-#pragma unroll
-    for (int n = 0; n < HD / 8; ++n) {
-      o[n][0] *= corr[0]; o[n][1] *= corr[0];
-      o[n][2] *= corr[1]; o[n][3] *= corr[1];
-    }
-    uint32_t pa[PF_BN / 16][4];
-#pragma unroll
-    for (int n = 0; n < PF_BN / 8; ++n) {
-      const float p0 = exp2f(s[n][0] - mref[0]), p1 = exp2f(s[n][1] - mref[0]);
-      const float p2 = exp2f(s[n][2] - mref[1]), p3 = exp2f(s[n][3] - mref[1]);
-      lrow[0] += p0 + p1;
-      lrow[1] += p2 + p3;
-      // C layout of two adjacent 8-key tiles == A layout of one 16-key slice
-      pa[n >> 1][(n & 1) * 2 + 0] = pack_bf16(p0, p1);
-      pa[n >> 1][(n & 1) * 2 + 1] = pack_bf16(p2, p3);
-    }
-
-    // ---- O += P V ----
-#pragma unroll
-    for (int ks = 0; ks < PF_BN / 16; ++ks) {
-#pragma unroll
-      for (int np = 0; np < HD / 16; ++np) {
-        uint32_t b0, b1, b2, b3;
-        const int r = ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
-        const int c = np * 2 + (lane >> 4);
-        ldsm_x4_trans(sV + swz<HD>(r, c), b0, b1, b2, b3);
-        mma_bf16_16816(o[2 * np], pa[ks], b0, b1);
-        mma_bf16_16816(o[2 * np + 1], pa[ks], b2, b3);
-      }
-    }
+    __syncthreads();  // every warp is done with this buffer before the load of tile + 2 overwrites it
   }
 
   // ---- finalize: row sums across the quad, normalise, store ----
@@ -206,19 +231,20 @@ __global__ void __launch_bounds__(PF_THREADS) prefill_attn_kernel(const __nv_bfl
   }
 }
 
-template <int HD>
+template <int HD, int NWARPS, int NBUF>
 static int launch_pf(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H, int KV,
                      bool causal, cudaStream_t st) {
-  const size_t smem = (size_t)(PF_BM + 2 * PF_BN) * HD * 2;
+  constexpr int BM = NWARPS * 16;
+  const size_t smem = (size_t)(BM + 2 * NBUF * PF_BN) * HD * 2;
   static bool configured = false;
   if (!configured) {
-    DLI_CUDA_OK(cudaFuncSetAttribute(prefill_attn_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DLI_CUDA_OK(cudaFuncSetAttribute(prefill_attn_kernel<HD, NWARPS, NBUF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
-  dim3 grid((q_len + PF_BM - 1) / PF_BM, H, batch);
-  return launch_kernel("prefill_attn_kernel", prefill_attn_kernel<HD>, grid, dim3(PF_THREADS), smem, st, q, out, kv, q_len, H,
-                       KV, causal ? 1 : 0, scale_log2);
+  dim3 grid((q_len + BM - 1) / BM, H, batch);
+  return launch_kernel("prefill_attn_kernel", prefill_attn_kernel<HD, NWARPS, NBUF>, grid, dim3(NWARPS * 32), smem, st, q, out, kv,
+                       q_len, H, KV, causal ? 1 : 0, scale_log2);
 }
 
 int launch_prefill_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H,
@@ -226,8 +252,21 @@ int launch_prefill_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const K
   DLI_REQUIRE(q && out, "dli_prefill_attention: null pointer");
   DLI_REQUIRE(batch > 0 && q_len > 0 && H > 0 && KV > 0 && H % KV == 0, "dli_prefill_attention: batch=%d q_len=%d H=%d KV=%d",
               batch, q_len, H, KV);
-  if (hd == 128) return launch_pf<128>(q, out, kv, batch, q_len, H, KV, causal, st);
-  if (hd == 64) return launch_pf<64>(q, out, kv, batch, q_len, H, KV, causal, st);
+    // head_dim 128: both contractions on tcgen05 (attn_prefill_tc.cu); q_len >= 16 keeps tiny chunks on the light kernel
+  if (q_len >= 16 && prefill_attn_tc_supported(kv, hd)) return launch_prefill_attention_tc(q, out, kv, batch, q_len, H, KV, causal, st);
+  static int force = -1;
+  if (force < 0) {
+    const char* e = getenv("DLI_PF_WARPS");
+    force = e ? atoi(e) : 0;
+  }
+  // measured on B200 (70B shape, 8k tokens): 4 warps + single K/V buffer (48 KB, 3 CTAs/SM) 68.7 ms per 10 layers,
+  // 4 warps double-buffered 77.2 ms, 8 warps double-buffered 75.7 ms: occupancy beats intra-CTA pipelining here
+  if (force == 8) {
+    if (hd == 128) return launch_pf<128, 8, 2>(q, out, kv, batch, q_len, H, KV, causal, st);
+    if (hd == 64) return launch_pf<64, 8, 2>(q, out, kv, batch, q_len, H, KV, causal, st);
+  }
+  if (hd == 128) return launch_pf<128, 4, 1>(q, out, kv, batch, q_len, H, KV, causal, st);
+  if (hd == 64) return launch_pf<64, 4, 1>(q, out, kv, batch, q_len, H, KV, causal, st);
   return fail(DLI_ERR_UNSUPPORTED, "dli_prefill_attention: head_dim %d is not instantiated (64, 128)", hd);
 }
 

@@ -1,0 +1,312 @@
+// tcgen05 flash attention for prefill (head_dim 128) over the paged KV cache.
+//
+// Replaces modules.py:87-105 for multi-token chunks, like attn_prefill.cu, but with both contractions on the
+// 5th-generation tensor cores:
+//   S = Q K^T   : tcgen05.mma, A = Q tile [128 queries x 128] (K-major, TMA), B = K tile [64 keys x 128] (K-major,
+//                 TMA straight from the pages: one box per page and head-dim half), D = S in TMEM (64 fp32 columns)
+//   O += P V    : tcgen05.mma, A = P [128 x 64 keys] bf16 written by the softmax warps into 128B-swizzled smem,
+//                 B = V tile [64 keys x 128] in its natural [key][head_dim] layout (MN-major descriptor), D = O in TMEM
+// Softmax runs on 4 warps, one query row per thread (tcgen05.ld of its S row), fp32 statistics in the exp2 domain.
+// O stays in TMEM for the whole key loop; it is rescaled only when a row's running maximum has grown by more than
+// 2^8 since its reference maximum was fixed (lazy rescaling), so the TMEM round trip is rare.
+// One CTA = 128 queries of one head; 80 KB of shared memory and 256 TMEM columns, so two CTAs share an SM and one
+// runs its MMAs while the other is in softmax.  Warp 0 lane 0 issues TMA, warp 1 lane 0 issues MMAs, warps 2-5 softmax.
+#include "common.cuh"
+#include "tc_ptx.cuh"
+
+#include <math.h>
+#include <stdlib.h>
+
+namespace dli {
+
+constexpr int FA_BM = 128;      // queries per CTA
+constexpr int FA_BN = 64;       // keys per tile
+constexpr int FA_HD = 128;
+constexpr int FA_THREADS = 192;
+constexpr int FA_Q_BYTES = FA_BM * FA_HD * 2;        // 32 KB: two 64-column halves of [128 rows x 128 B]
+constexpr int FA_KV_BYTES = FA_BN * FA_HD * 2;       // 16 KB: two halves of [64 rows x 128 B]
+constexpr int FA_P_BYTES = FA_BM * FA_BN * 2;        // 16 KB: [128 rows x 128 B]
+constexpr int FA_SMEM = FA_Q_BYTES + 2 * FA_KV_BYTES + FA_P_BYTES + 1024;
+constexpr uint32_t FA_TMEM_COLS = 256;               // S: columns [0, 64), O: columns [64, 192)
+constexpr float FA_RESCALE_THRESHOLD = 8.0f;         // log2 units
+
+// MN-major (here: head_dim-contiguous) 128B-swizzled operand: 64-element rows of 128 bytes, 8 rows (keys) per
+// 1024-byte swizzle atom; SBO = distance between 8-key groups, LBO = distance between 64-element column blocks.
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// kind::f16 instruction descriptor, D fp32, A/B bf16, A K-major, B K-major or MN-major, M = 128
+__host__ __device__ constexpr uint32_t fa_idesc(int n, bool b_mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((b_mn_major ? 1u : 0u) << 16) | ((uint32_t)(n >> 3) << 17) |
+         ((uint32_t)(128 >> 4) << 24);
+}
+
+struct FaParams {
+  __nv_bfloat16* out;
+  const int32_t* block_table;
+  const int32_t* seq_lens;
+  int max_pages, page_tokens, q_len, H, KV, causal;
+  float scale_log2;
+};
+
+__global__ void __launch_bounds__(FA_THREADS, 2)
+prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
+                       const __grid_constant__ CUtensorMap tma_v, const FaParams p) {
+  extern __shared__ uint8_t fa_smem_raw[];
+  // barriers: 0 q_full, 1 k_full, 2 k_empty, 3 v_full, 4 s_full, 5 s_empty, 6 p_full, 7 pv_done
+  __shared__ uint64_t bars[8];
+  __shared__ uint32_t tmem_base_slot;
+
+  const uint32_t base = (smem_u32(fa_smem_raw) + 1023u) & ~1023u;
+  const uint32_t sQ = base, sK = sQ + FA_Q_BYTES, sV = sK + FA_KV_BYTES, sP = sV + FA_KV_BYTES;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t q_full = smem_u32(&bars[0]), k_full = smem_u32(&bars[1]), k_empty = smem_u32(&bars[2]),
+                 v_full = smem_u32(&bars[3]), s_full = smem_u32(&bars[4]), s_empty = smem_u32(&bars[5]),
+                 p_full = smem_u32(&bars[6]), pv_done = smem_u32(&bars[7]);
+
+  pdl_trigger();
+  if (threadIdx.x == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_q) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_k) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_v) : "memory");
+    mbar_init(q_full, 1);
+    mbar_init(k_full, 1);
+    mbar_init(k_empty, 1);
+    mbar_init(v_full, 1);
+    mbar_init(s_full, 1);
+    mbar_init(s_empty, 128);
+    mbar_init(p_full, 128);
+    mbar_init(pv_done, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)),
+                 "r"(FA_TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem = tmem_base_slot;
+  const uint32_t tS = tmem, tO = tmem + FA_BN;
+
+  pdl_wait();  // q, the pages and seq_lens are produced by the preceding kernels of the stream
+  const int m0 = blockIdx.x * FA_BM, h = blockIdx.y, b = blockIdx.z;
+  const int kvh = h / (p.H / p.KV);
+  const int past = p.seq_lens[b];
+  const int T = past + p.q_len;
+  int kv_end = T;
+  if (p.causal) kv_end = min(T, past + m0 + FA_BM);
+  const int n_tiles = (kv_end + FA_BN - 1) / FA_BN;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ===== TMA producer =====
+      const int32_t* bt = p.block_table + (long long)b * p.max_pages;
+      const int pages_per_tile = FA_BN / p.page_tokens;
+      const uint32_t page_bytes = (uint32_t)p.page_tokens * 128u;  // one head-dim half of one page
+      mbar_expect_tx(q_full, FA_Q_BYTES);
+      tma_load_2d(sQ, &tma_q, q_full, h * FA_HD, b * p.q_len + m0);
+      tma_load_2d(sQ + FA_Q_BYTES / 2, &tma_q, q_full, h * FA_HD + 64, b * p.q_len + m0);
+      for (int j = 0; j < n_tiles; ++j) {
+        const int page0 = j * pages_per_tile;
+        if (j > 0) mbar_wait(k_empty, (j - 1) & 1);  // QK^T of the previous tile has read K
+        mbar_expect_tx(k_full, FA_KV_BYTES);
+        for (int pg = 0; pg < pages_per_tile; ++pg) {
+          const int tok0 = (page0 + pg) * p.page_tokens;
+          const int page = tok0 < T ? bt[page0 + pg] : bt[0];  // past the end: any valid page (masked later)
+          const int row = (page * p.KV + kvh) * p.page_tokens;
+          tma_load_2d(sK + pg * page_bytes, &tma_k, k_full, 0, row);
+          tma_load_2d(sK + FA_KV_BYTES / 2 + pg * page_bytes, &tma_k, k_full, 64, row);
+        }
+        if (j > 0) mbar_wait(pv_done, (j - 1) & 1);  // P V of the previous tile has read V
+        mbar_expect_tx(v_full, FA_KV_BYTES);
+        for (int pg = 0; pg < pages_per_tile; ++pg) {
+          const int tok0 = (page0 + pg) * p.page_tokens;
+          const int page = tok0 < T ? bt[page0 + pg] : bt[0];
+          const int row = (page * p.KV + kvh) * p.page_tokens;
+          tma_load_2d(sV + pg * page_bytes, &tma_v, v_full, 0, row);
+          tma_load_2d(sV + FA_KV_BYTES / 2 + pg * page_bytes, &tma_v, v_full, 64, row);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {  // ===== MMA issuer =====
+      constexpr uint32_t idesc_qk = fa_idesc(FA_BN, false);
+      constexpr uint32_t idesc_pv = fa_idesc(FA_HD, true);
+      auto issue_qk = [&](int j) {
+        mbar_wait(k_full, j & 1);
+        if (j > 0) mbar_wait(s_empty, (j - 1) & 1);  // softmax has copied S of the previous tile to registers
+        tcgen05_fence_after();
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb) {
+          const uint64_t a = umma_desc_sw128(sQ + kb * (FA_Q_BYTES / 2)), bd = umma_desc_sw128(sK + kb * (FA_KV_BYTES / 2));
+#pragma unroll
+          for (int k = 0; k < 4; ++k) umma_bf16(tS, a + 2 * k, bd + 2 * k, idesc_qk, (kb | k) ? 1u : 0u);
+        }
+        umma_commit(s_full);
+        umma_commit(k_empty);
+      };
+      mbar_wait(q_full, 0);
+      issue_qk(0);
+      for (int j = 0; j < n_tiles; ++j) {
+        if (j + 1 < n_tiles) issue_qk(j + 1);  // overlaps the softmax of tile j
+        mbar_wait(v_full, j & 1);
+        mbar_wait(p_full, j & 1);
+        tcgen05_fence_after();
+        const uint64_t a = umma_desc_sw128(sP);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {  // 16 keys per instruction: two 8-key swizzle atoms of V
+          const uint64_t bd = umma_desc_mn_sw128(sV + k * 2048, FA_KV_BYTES / 2, 1024);
+          umma_bf16(tO, a + 2 * k, bd, idesc_pv, (j | k) ? 1u : 0u);
+        }
+        umma_commit(pv_done);
+      }
+    }
+  } else {
+    // ===== softmax warps: one query row per thread =====
+    const int q4 = warp & 3;
+    const int row = q4 * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
+    const int qi = m0 + row;
+    const int pos = past + qi;  // absolute position of this query
+    float m_ref = -INFINITY, l = 0.f;
+    uint32_t v[16];
+    for (int j = 0; j < n_tiles; ++j) {
+      const int j0 = j * FA_BN;
+      float s[FA_BN];
+      mbar_wait(s_full, j & 1);
+      tcgen05_fence_after();
+#pragma unroll
+      for (int c0 = 0; c0 < FA_BN; c0 += 16) {
+        tmem_ld16(tS + lane_addr + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) s[c0 + i] = __uint_as_float(v[i]) * p.scale_log2;
+      }
+      tcgen05_fence_before();
+      mbar_arrive(s_empty);
+
+      const bool need_mask = (j0 + FA_BN > T) || (p.causal && j0 + FA_BN - 1 > past + m0);
+      float mx = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < FA_BN; ++i) {
+        if (need_mask) {
+          const int key = j0 + i;
+          if (!(key < T && (!p.causal || key <= pos))) s[i] = -INFINITY;
+        }
+        mx = fmaxf(mx, s[i]);
+      }
+      float corr = 1.f;
+      if (mx > m_ref + FA_RESCALE_THRESHOLD || m_ref == -INFINITY) {  // move the reference maximum
+        const float m_new = fmaxf(mx, m_ref);
+        if (m_new > -INFINITY) {
+          corr = m_ref == -INFINITY ? 1.f : exp2f(m_ref - m_new);
+          l *= corr;
+          m_ref = m_new;
+        }
+      }
+      const float mref = m_ref == -INFINITY ? 0.f : m_ref;
+      uint32_t pk[FA_BN / 2];
+#pragma unroll
+      for (int i = 0; i < FA_BN; i += 2) {
+        const float p0 = exp2f(s[i] - mref), p1 = exp2f(s[i + 1] - mref);
+        l += p0 + p1;
+        pk[i / 2] = pack_bf16(p0, p1);
+      }
+
+      if (j > 0) {
+        mbar_wait(pv_done, (j - 1) & 1);  // P buffer free, O holds tiles 0..j-1
+        tcgen05_fence_after();
+        if (__any_sync(0xffffffffu, corr != 1.f)) {  // rare: rescale this warp's 32 rows of O in TMEM
+#pragma unroll 1
+          for (int c0 = 0; c0 < FA_HD; c0 += 16) {
+            tmem_ld16(tO + lane_addr + c0, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * corr);
+            tmem_st16(tO + lane_addr + c0, v);
+          }
+          tmem_st_wait();
+        }
+      }
+      // P row -> smem, K-major 128B-swizzled: 16-byte chunk c of row r lives at chunk (c ^ (r & 7))
+      uint8_t* prow = fa_smem_raw + (sP - smem_u32(fa_smem_raw)) + row * 128;
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+      fence_proxy_async_smem();
+      tcgen05_fence_before();
+      mbar_arrive(p_full);
+    }
+
+    // ---- finalize: O / l -> bf16 ----
+    mbar_wait(pv_done, (n_tiles - 1) & 1);
+    tcgen05_fence_after();
+    const float inv = l > 0.f ? 1.f / l : 0.f;
+    __nv_bfloat16* dst = p.out + (((long long)b * p.q_len + qi) * p.H + h) * FA_HD;
+#pragma unroll 1
+    for (int c0 = 0; c0 < FA_HD; c0 += 16) {
+      tmem_ld16(tO + lane_addr + c0, v);
+      tmem_ld_wait();
+      if (qi < p.q_len) {
+        uint32_t w[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) w[i] = pack_bf16(__uint_as_float(v[2 * i]) * inv, __uint_as_float(v[2 * i + 1]) * inv);
+        *reinterpret_cast<uint4*>(dst + c0) = make_uint4(w[0], w[1], w[2], w[3]);
+        *reinterpret_cast<uint4*>(dst + c0 + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+      }
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(FA_TMEM_COLS) : "memory");
+  }
+}
+
+bool prefill_attn_tc_supported(const KvView& kv, int hd) {
+  static int legacy = -1;
+  if (legacy < 0) {
+    const char* e = getenv("DLI_ATTN_LEGACY");
+    legacy = (e && e[0] == '1') ? 1 : 0;
+  }
+  return !legacy && hd == FA_HD && kv.page_tokens >= 8 && kv.page_tokens % 8 == 0 && FA_BN % kv.page_tokens == 0;
+}
+
+int launch_prefill_attention_tc(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H,
+                                int KV, bool causal, cudaStream_t st) {
+  CUtensorMap tq, tk, tv;
+  int rc = make_tmap_bf16(&tq, q, (long long)batch * q_len, (long long)H * FA_HD, (long long)H * FA_HD, FA_BM);
+  if (rc) return rc;
+  const long long pool_rows = (long long)kv.n_pages * KV * kv.page_tokens;
+  if ((rc = make_tmap_bf16(&tk, kv.k, pool_rows, FA_HD, FA_HD, kv.page_tokens))) return rc;
+  if ((rc = make_tmap_bf16(&tv, kv.v, pool_rows, FA_HD, FA_HD, kv.page_tokens))) return rc;
+  static bool configured = false;
+  if (!configured) {
+    DLI_CUDA_OK(cudaFuncSetAttribute(prefill_attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM));
+    configured = true;
+  }
+  FaParams p{};
+  p.out = out;
+  p.block_table = kv.block_table;
+  p.seq_lens = kv.seq_lens;
+  p.max_pages = kv.max_pages;
+  p.page_tokens = kv.page_tokens;
+  p.q_len = q_len;
+  p.H = H;
+  p.KV = KV;
+  p.causal = causal ? 1 : 0;
+  p.scale_log2 = 1.4426950408889634f / sqrtf((float)FA_HD);
+  dim3 grid((q_len + FA_BM - 1) / FA_BM, H, batch);
+  return launch_kernel("prefill_attn_tc_kernel", prefill_attn_tc_kernel, grid, dim3(FA_THREADS), (size_t)FA_SMEM, st, tq, tk, tv, p);
+}
+
+}  // namespace dli

@@ -111,6 +111,9 @@ int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t s
 size_t decode_attn_scratch_bytes(int batch, int H, int hd, int max_ctx);
 int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV,
                             int hd, float* scratch, size_t scratch_bytes, cudaStream_t st);
+bool prefill_attn_tc_supported(const KvView& kv, int hd);
+int launch_prefill_attention_tc(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H,
+                                int KV, bool causal, cudaStream_t st);
 int launch_prefill_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len,
                              int H, int KV, int hd, bool causal, cudaStream_t st);
 

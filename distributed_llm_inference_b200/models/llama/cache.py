@@ -70,8 +70,10 @@ class PartialLlamaSinkCache:
             return
         cap = self.capacity_tokens if self.capacity_tokens is not None else min(self.window_length, 4096) * 4
         n_pages = max(1, -(-cap // self.page_tokens))
-        self._k = torch.empty(n_layers, n_pages, n_kv_heads, self.page_tokens, head_dim, dtype=dtype, device=device)
-        self._v = torch.empty_like(self._k)
+        # zero-filled: the tensor-core attention loads whole pages, and never-written slots must hold finite values
+        # (their probabilities are exactly 0, but 0 * NaN would poison the P.V product)
+        self._k = torch.zeros(n_layers, n_pages, n_kv_heads, self.page_tokens, head_dim, dtype=dtype, device=device)
+        self._v = torch.zeros_like(self._k)
         self._free = list(range(n_pages - 1, -1, -1))
         self._shape = shape
 

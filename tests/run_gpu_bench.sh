@@ -3,17 +3,17 @@ mkdir -p gpurun_out
 run() { name=$1; shift; timeout 900 "$@" > gpurun_out/$name.log 2>&1; echo "$name exit $?"; tail -n ${TAILN:-12} gpurun_out/$name.log | cut -c1-${CUTC:-400}; }
 run ops python -m pytest tests/test_ops_gpu.py -q -m gpu --no-header -p no:cacheprovider --maxfail=10
 run span python -m pytest tests/test_span_gpu.py tests/test_zz_no_alloc.py -q -m gpu --no-header -p no:cacheprovider -s --maxfail=10
-for cfg in "7b 16 0" "70b 32 10"; do
+for cfg in "7b 16 0 512" "70b 32 10 512" "70b 1 10 8192"; do
   set -- $cfg
   extra=""; [ "$3" != "0" ] && extra="--layers $3"
-  timeout 600 python bench.py --steps 32 --warmup 4 --cpu-budget 0 --model $1 --batch $2 $extra > gpurun_out/bench_$1.json 2> gpurun_out/bench_$1.err || tail -5 gpurun_out/bench_$1.err
+  timeout 600 python bench.py --steps 16 --warmup 4 --cpu-budget 0 --model $1 --batch $2 --prompt $4 $extra > gpurun_out/bench_$1_$4.json 2> gpurun_out/bench_$1_$4.err || tail -5 gpurun_out/bench_$1_$4.err
   python - <<PY
 import json
 try:
-    d=json.load(open("gpurun_out/bench_$1.json"))
-    print("$1 B=$2 value",d["value"],"ms/step",d["ms_per_step"],"stage",d["stage_roofline"]["frac"],"gemm",d["roofline"]["frac"],"e2e",d["e2e"]["value"])
+    d=json.load(open("gpurun_out/bench_$1_$4.json"))
+    print("$1 B=$2 T=$4 value",d["value"],"ms/step",d["ms_per_step"],"stage",d["stage_roofline"]["frac"],"gemm",d["roofline"]["frac"],"e2e",d["e2e"]["value"])
     print("   decode",d["kernel_ms_per_step"])
-    print("   prefill",d["prefill"])
+    print("   prefill",{k:v for k,v in d["prefill"].items() if k in ("ms","tflops","frac","kernel_ms")})
 except Exception as e: print("bench $1 failed",e)
 PY
 done
