@@ -238,7 +238,7 @@ def run_ours(args):
     total_ctx = PROMPT + W + K + 8 + 32 + 8
 
     blk = build_span(shape, layer_ids, dev, max_positions=max(8192, total_ctx + 64))
-    cache = PartialLlamaSinkCache(1 << 20, 4, page_tokens=16,
+    cache = PartialLlamaSinkCache(1 << 20, 4, page_tokens=args.page_tokens,
                                   capacity_tokens=n_mb * BATCH * (total_ctx + 16) + BATCH * 64 + BATCH * (PROMPT + 16))
     stage = PipelineStage(blk, cache, rank, world, dev)
     gids = [f"mb{m}" for m in range(n_mb)]
@@ -412,7 +412,7 @@ def run_ours(args):
                                    f"{n_mb} micro-batch(es) in flight, {PROMPT}-token prompt, context "
                                    f"{PROMPT + W}..{PROMPT + W + K}; random-init weights, synthetic hidden states",
                        "global_batch": tokens_per_step, "seq_len": PROMPT, "parallelism": f"pp{world}",
-                       "l2": "inputs larger than L2 (12.9 GB of weights streamed per step)", "page_tokens": 16,
+                       "l2": "inputs larger than L2 (12.9 GB of weights streamed per step)", "page_tokens": args.page_tokens,
                        "launch": "cuda_graph" if graph is not None else "eager",
                        "handoff": stage.handoff, "handoff_fallback_reason": stage.handoff_error},
             "p50_ms_per_token": round(lat[len(lat) // 2] / n_mb, 4),
@@ -465,6 +465,7 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--batch", type=int, default=None, help="override the batch (experiments; the default is the config's 16)")
     ap.add_argument("--model", default=None, choices=["7b", "13b", "70b", "tiny"], help="shape (default: configs[1], 7b)")
+    ap.add_argument("--page-tokens", type=int, default=16, help="tokens per KV page")
     ap.add_argument("--prompt", type=int, default=None, help="prompt length (default 512, the config's)")
     ap.add_argument("--layers", type=int, default=None, help="total layers over all stages (default: the model's)")
     ap.add_argument("--micro-batches", type=int, default=None, help="micro-batches in flight (default: number of stages)")

@@ -9,7 +9,8 @@
 // Softmax runs on 4 warps, one query row per thread (tcgen05.ld of its S row), fp32 statistics in the exp2 domain.
 // O stays in TMEM for the whole key loop; it is rescaled only when a row's running maximum has grown by more than
 // 2^8 since its reference maximum was fixed (lazy rescaling), so the TMEM round trip is rare.
-// One CTA = 128 queries of one head; 80 KB of shared memory and 256 TMEM columns, so two CTAs share an SM and one
+// V is double-buffered (its load would otherwise sit on the critical path between two P.V products).
+// One CTA = 128 queries of one head; 96 KB of shared memory and 256 TMEM columns, so two CTAs share an SM and one
 // runs its MMAs while the other is in softmax.  Warp 0 lane 0 issues TMA, warp 1 lane 0 issues MMAs, warps 2-5 softmax.
 #include "common.cuh"
 #include "tc_ptx.cuh"
@@ -26,7 +27,7 @@ constexpr int FA_THREADS = 192;
 constexpr int FA_Q_BYTES = FA_BM * FA_HD * 2;        // 32 KB: two 64-column halves of [128 rows x 128 B]
 constexpr int FA_KV_BYTES = FA_BN * FA_HD * 2;       // 16 KB: two halves of [64 rows x 128 B]
 constexpr int FA_P_BYTES = FA_BM * FA_BN * 2;        // 16 KB: [128 rows x 128 B]
-constexpr int FA_SMEM = FA_Q_BYTES + 2 * FA_KV_BYTES + FA_P_BYTES + 1024;
+constexpr int FA_SMEM = FA_Q_BYTES + 3 * FA_KV_BYTES + FA_P_BYTES + 1024;  // Q, K, V[2], P
 constexpr uint32_t FA_TMEM_COLS = 256;               // S: columns [0, 64), O: columns [64, 192)
 constexpr float FA_RESCALE_THRESHOLD = 8.0f;         // log2 units
 
@@ -59,16 +60,16 @@ __global__ void __launch_bounds__(FA_THREADS, 2)
 prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
                        const __grid_constant__ CUtensorMap tma_v, const FaParams p) {
   extern __shared__ uint8_t fa_smem_raw[];
-  // barriers: 0 q_full, 1 k_full, 2 k_empty, 3 v_full, 4 s_full, 5 s_empty, 6 p_full, 7 pv_done
-  __shared__ uint64_t bars[8];
+  // barriers: 0 q_full, 1 k_full, 2 k_empty, 3 s_full, 4 s_empty, 5 p_full, 6 pv_done, 7-8 v_full[2], 9-10 v_empty[2]
+  __shared__ uint64_t bars[11];
   __shared__ uint32_t tmem_base_slot;
 
   const uint32_t base = (smem_u32(fa_smem_raw) + 1023u) & ~1023u;
-  const uint32_t sQ = base, sK = sQ + FA_Q_BYTES, sV = sK + FA_KV_BYTES, sP = sV + FA_KV_BYTES;
+  const uint32_t sQ = base, sK = sQ + FA_Q_BYTES, sV = sK + FA_KV_BYTES, sP = sV + 2 * FA_KV_BYTES;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t q_full = smem_u32(&bars[0]), k_full = smem_u32(&bars[1]), k_empty = smem_u32(&bars[2]),
-                 v_full = smem_u32(&bars[3]), s_full = smem_u32(&bars[4]), s_empty = smem_u32(&bars[5]),
-                 p_full = smem_u32(&bars[6]), pv_done = smem_u32(&bars[7]);
+                 s_full = smem_u32(&bars[3]), s_empty = smem_u32(&bars[4]), p_full = smem_u32(&bars[5]),
+                 pv_done = smem_u32(&bars[6]), v_full = smem_u32(&bars[7]), v_empty = smem_u32(&bars[9]);
 
   pdl_trigger();
   if (threadIdx.x == 0) {
@@ -79,6 +80,9 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
     mbar_init(k_full, 1);
     mbar_init(k_empty, 1);
     mbar_init(v_full, 1);
+    mbar_init(v_full + 8, 1);
+    mbar_init(v_empty, 1);
+    mbar_init(v_empty + 8, 1);
     mbar_init(s_full, 1);
     mbar_init(s_empty, 128);
     mbar_init(p_full, 128);
@@ -125,14 +129,15 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
           tma_load_2d(sK + pg * page_bytes, &tma_k, k_full, 0, row);
           tma_load_2d(sK + FA_KV_BYTES / 2 + pg * page_bytes, &tma_k, k_full, 64, row);
         }
-        if (j > 0) mbar_wait(pv_done, (j - 1) & 1);  // P V of the previous tile has read V
-        mbar_expect_tx(v_full, FA_KV_BYTES);
+        const int vb = j & 1;  // V buffer of this tile; free once P V of tile j - 2 has read it
+        if (j >= 2) mbar_wait(v_empty + 8 * vb, ((j >> 1) - 1) & 1);
+        mbar_expect_tx(v_full + 8 * vb, FA_KV_BYTES);
         for (int pg = 0; pg < pages_per_tile; ++pg) {
           const int tok0 = (page0 + pg) * p.page_tokens;
           const int page = tok0 < T ? bt[page0 + pg] : bt[0];
           const int row = (page * p.KV + kvh) * p.page_tokens;
-          tma_load_2d(sV + pg * page_bytes, &tma_v, v_full, 0, row);
-          tma_load_2d(sV + FA_KV_BYTES / 2 + pg * page_bytes, &tma_v, v_full, 64, row);
+          tma_load_2d(sV + vb * FA_KV_BYTES + pg * page_bytes, &tma_v, v_full + 8 * vb, 0, row);
+          tma_load_2d(sV + vb * FA_KV_BYTES + FA_KV_BYTES / 2 + pg * page_bytes, &tma_v, v_full + 8 * vb, 64, row);
         }
       }
     }
@@ -157,16 +162,18 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       issue_qk(0);
       for (int j = 0; j < n_tiles; ++j) {
         if (j + 1 < n_tiles) issue_qk(j + 1);  // overlaps the softmax of tile j
-        mbar_wait(v_full, j & 1);
+        const int vb = j & 1;
+        mbar_wait(v_full + 8 * vb, (j >> 1) & 1);
         mbar_wait(p_full, j & 1);
         tcgen05_fence_after();
         const uint64_t a = umma_desc_sw128(sP);
 #pragma unroll
         for (int k = 0; k < 4; ++k) {  // 16 keys per instruction: two 8-key swizzle atoms of V
-          const uint64_t bd = umma_desc_mn_sw128(sV + k * 2048, FA_KV_BYTES / 2, 1024);
+          const uint64_t bd = umma_desc_mn_sw128(sV + vb * FA_KV_BYTES + k * 2048, FA_KV_BYTES / 2, 1024);
           umma_bf16(tO, a + 2 * k, bd, idesc_pv, (j | k) ? 1u : 0u);
         }
         umma_commit(pv_done);
+        umma_commit(v_empty + 8 * vb);
       }
     }
   } else {
@@ -180,7 +187,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
     uint32_t v[16];
     for (int j = 0; j < n_tiles; ++j) {
       const int j0 = j * FA_BN;
-      float s[FA_BN];
+      float s[FA_BN];  // raw scores (unscaled): the 1/sqrt(hd)*log2(e) factor is folded into the exp2 argument
       mbar_wait(s_full, j & 1);
       tcgen05_fence_after();
 #pragma unroll
@@ -188,21 +195,24 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
         tmem_ld16(tS + lane_addr + c0, v);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 16; ++i) s[c0 + i] = __uint_as_float(v[i]) * p.scale_log2;
+        for (int i = 0; i < 16; ++i) s[c0 + i] = __uint_as_float(v[i]);
       }
       tcgen05_fence_before();
       mbar_arrive(s_empty);
 
-      const bool need_mask = (j0 + FA_BN > T) || (p.causal && j0 + FA_BN - 1 > past + m0);
-      float mx = -INFINITY;
+      if ((j0 + FA_BN > T) || (p.causal && j0 + FA_BN - 1 > past + m0)) {  // tile touches the diagonal / context end
 #pragma unroll
-      for (int i = 0; i < FA_BN; ++i) {
-        if (need_mask) {
+        for (int i = 0; i < FA_BN; ++i) {
           const int key = j0 + i;
           if (!(key < T && (!p.causal || key <= pos))) s[i] = -INFINITY;
         }
-        mx = fmaxf(mx, s[i]);
       }
+      float mx0 = s[0], mx1 = s[1], mx2 = s[2], mx3 = s[3];
+#pragma unroll
+      for (int i = 4; i < FA_BN; i += 4) {
+        mx0 = fmaxf(mx0, s[i]); mx1 = fmaxf(mx1, s[i + 1]); mx2 = fmaxf(mx2, s[i + 2]); mx3 = fmaxf(mx3, s[i + 3]);
+      }
+      const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * p.scale_log2;  // scale > 0: max commutes with it
       float corr = 1.f;
       if (mx > m_ref + FA_RESCALE_THRESHOLD || m_ref == -INFINITY) {  // move the reference maximum
         const float m_new = fmaxf(mx, m_ref);
@@ -212,14 +222,19 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
           m_ref = m_new;
         }
       }
-      const float mref = m_ref == -INFINITY ? 0.f : m_ref;
+      const float neg_mref = m_ref == -INFINITY ? 0.f : -m_ref;
       uint32_t pk[FA_BN / 2];
+      float l0 = 0.f, l1 = 0.f;
 #pragma unroll
-      for (int i = 0; i < FA_BN; i += 2) {
-        const float p0 = exp2f(s[i] - mref), p1 = exp2f(s[i + 1] - mref);
-        l += p0 + p1;
+      for (int i = 0; i < FA_BN; i += 2) {  // one FFMA + one MUFU.EX2 per score
+        float p0, p1;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p0) : "f"(fmaf(s[i], p.scale_log2, neg_mref)));
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p1) : "f"(fmaf(s[i + 1], p.scale_log2, neg_mref)));
+        l0 += p0;
+        l1 += p1;
         pk[i / 2] = pack_bf16(p0, p1);
       }
+      l += l0 + l1;
 
       if (j > 0) {
         mbar_wait(pv_done, (j - 1) & 1);  // P buffer free, O holds tiles 0..j-1
