@@ -120,7 +120,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       tma_load_2d(sQ + FA_Q_BYTES / 2, &tma_q, q_full, h * FA_HD + 64, b * p.q_len + m0);
       for (int j = 0; j < n_tiles; ++j) {
         const int page0 = j * pages_per_tile;
-        if (j > 0) mbar_wait(k_empty, (j - 1) & 1);  // QK^T of the previous tile has read K
+        if (j > 0) mbar_wait(k_empty, (j - 1) & 1, 64);  // QK^T of the previous tile has read K
         mbar_expect_tx(k_full, FA_KV_BYTES);
         for (int pg = 0; pg < pages_per_tile; ++pg) {
           const int tok0 = (page0 + pg) * p.page_tokens;
@@ -130,7 +130,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
           tma_load_2d(sK + FA_KV_BYTES / 2 + pg * page_bytes, &tma_k, k_full, 64, row);
         }
         const int vb = j & 1;  // V buffer of this tile; free once P V of tile j - 2 has read it
-        if (j >= 2) mbar_wait(v_empty + 8 * vb, ((j >> 1) - 1) & 1);
+        if (j >= 2) mbar_wait(v_empty + 8 * vb, ((j >> 1) - 1) & 1, 64);
         mbar_expect_tx(v_full + 8 * vb, FA_KV_BYTES);
         for (int pg = 0; pg < pages_per_tile; ++pg) {
           const int tok0 = (page0 + pg) * p.page_tokens;
@@ -146,8 +146,8 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       constexpr uint32_t idesc_qk = fa_idesc(FA_BN, false);
       constexpr uint32_t idesc_pv = fa_idesc(FA_HD, true);
       auto issue_qk = [&](int j) {
-        mbar_wait(k_full, j & 1);
-        if (j > 0) mbar_wait(s_empty, (j - 1) & 1);  // softmax has copied S of the previous tile to registers
+        mbar_wait(k_full, j & 1, 32);
+        if (j > 0) mbar_wait(s_empty, (j - 1) & 1, 32);  // softmax has copied S of the previous tile to registers
         tcgen05_fence_after();
 #pragma unroll
         for (int kb = 0; kb < 2; ++kb) {
@@ -163,8 +163,8 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       for (int j = 0; j < n_tiles; ++j) {
         if (j + 1 < n_tiles) issue_qk(j + 1);  // overlaps the softmax of tile j
         const int vb = j & 1;
-        mbar_wait(v_full + 8 * vb, (j >> 1) & 1);
-        mbar_wait(p_full, j & 1);
+        mbar_wait(v_full + 8 * vb, (j >> 1) & 1, 32);
+        mbar_wait(p_full, j & 1, 32);
         tcgen05_fence_after();
         const uint64_t a = umma_desc_sw128(sP);
 #pragma unroll
@@ -188,7 +188,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
     for (int j = 0; j < n_tiles; ++j) {
       const int j0 = j * FA_BN;
       float s[FA_BN];  // raw scores (unscaled): the 1/sqrt(hd)*log2(e) factor is folded into the exp2 argument
-      mbar_wait(s_full, j & 1);
+      mbar_wait(s_full, j & 1, 20);
       tcgen05_fence_after();
 #pragma unroll
       for (int c0 = 0; c0 < FA_BN; c0 += 16) {
@@ -237,7 +237,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       l += l0 + l1;
 
       if (j > 0) {
-        mbar_wait(pv_done, (j - 1) & 1);  // P buffer free, O holds tiles 0..j-1
+        mbar_wait(pv_done, (j - 1) & 1, 20);  // P buffer free, O holds tiles 0..j-1
         tcgen05_fence_after();
         if (__any_sync(0xffffffffu, corr != 1.f)) {  // rare: rescale this warp's 32 rows of O in TMEM
 #pragma unroll 1

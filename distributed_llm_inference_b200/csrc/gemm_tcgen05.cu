@@ -306,7 +306,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       }
     } else {  // ===== epilogue: TMEM -> registers -> global =====
       pdl_wait();  // the output buffers belong to the predecessor until it has completed
-      mbar_wait(tmem_full, 0);
+      mbar_wait(tmem_full, 0, 200);  // 128 threads wait out the whole main loop: poll rarely
       tcgen05_fence_after();
       const int q = warp & 3;  // TMEM lane quarter this warp may read
       const int arow = a_row0 + q * 32 + lane;
@@ -514,7 +514,7 @@ gemm_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const 
       int mt, nt;
       tile_coords(t, tiles_m, tiles_n, group_m, mt, nt);
       const int a_row0 = mt * BM, b_row0 = nt * N_PER_TILE;
-      mbar_wait(tfull0 + 8 * acc, ((uint32_t)it >> 1) & 1);
+      mbar_wait(tfull0 + 8 * acc, ((uint32_t)it >> 1) & 1, 100);
       tcgen05_fence_after();
       const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
       if constexpr (EPI == DLI_EPI_QKV_ROPE_INTERNAL) epilogue_qkv_rope<BN>(taddr, a_row0 + q * 32 + lane, b_row0, p);

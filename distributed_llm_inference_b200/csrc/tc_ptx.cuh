@@ -16,7 +16,8 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+// backoff_ns > 0: sleep between polls, so that a waiting role does not take issue slots from the warps that compute
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, uint32_t backoff_ns = 0) {
   uint32_t done = 0;
   uint32_t spins = 0;
   while (true) {
@@ -28,6 +29,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "r"(bar), "r"(parity)
         : "memory");
     if (done) break;
+    if (backoff_ns) __nanosleep(backoff_ns);
     if (++spins > 4000000u) {  // a lost arrival must surface as a launch failure, never as a hung GPU
       printf("dli gemm: mbarrier wait timed out (block %d,%d,%d thread %d)\n", blockIdx.x, blockIdx.y,
              blockIdx.z, threadIdx.x);
