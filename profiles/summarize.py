@@ -17,8 +17,8 @@ METRICS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.
            "launch__occupancy_limit_shared_mem", "lts__t_sector_hit_rate.pct", "smsp__cycles_active.avg"]
 
 
-def launches(tag):
-    with open("gpurun_out/launches.csv") as f:
+def launches(tag, src="launches", suffix="launches_summary"):
+    with open(f"gpurun_out/{src}.csv") as f:
         lines = [l for l in f if not l.startswith("==")]
     agg, n = collections.OrderedDict(), 0
     for row in csv.DictReader(lines):
@@ -32,12 +32,12 @@ def launches(tag):
         a[1] += v
         n += 1
     tot = sum(a[1] for a in agg.values())
-    with open(f"profiles/{tag}_launches_summary.txt", "w") as out:
+    with open(f"profiles/{tag}_{suffix}.txt", "w") as out:
         out.write(f"# ncu --metrics gpu__time_duration.sum --clock-control none (cold-cache, serialised): {n} launches, "
                   f"{tot:.1f} us total\n# share   launches   avg_us   kernel\n")
         for k, (c, t) in sorted(agg.items(), key=lambda x: -x[1][1]):
             out.write(f"{t / tot * 100:6.2f}%  {c:5d}  {t / c:8.2f}  {k}\n")
-    print(open(f"profiles/{tag}_launches_summary.txt").read())
+    print(open(f"profiles/{tag}_{suffix}.txt").read())
 
 
 def full(tag, rep):
@@ -58,5 +58,8 @@ def full(tag, rep):
 if __name__ == "__main__":
     tag = sys.argv[1]
     launches(tag)
+    import os
+    if os.path.exists("gpurun_out/launches_prefill.csv"):
+        launches(tag, "launches_prefill", "launches_prefill_summary")
     for rep in sys.argv[2:] or ["prof_gemm_decode", "prof_attn_decode"]:
         full(tag, rep)

@@ -4,14 +4,18 @@ mkdir -p gpurun_out
 KN='regex:gemm_tcgen05|rmsnorm_kernel|rope_kv|decode_attn|decode_combine|prefill_attn|silu_mul|cast_kernel|kv_evict'
 CMD="python bench.py --steps 2 --warmup 3 --cpu-budget 0"
 $CMD > gpurun_out/plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/plain.log; exit 1; }
-ncu --metrics gpu__time_duration.sum --clock-control none -k "$KN" -s 2313 -c 514 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
+# launch list: two decode steps (257 launches each) after prefill (225), 4 warm prefills, graph warm-up and 3 warm-up steps
+ncu --metrics gpu__time_duration.sum --clock-control none -k "$KN" -s 2153 -c 514 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
 echo "ncu list exit $?"
-ncu --set full --clock-control none --import-source on -k regex:gemm_tcgen05_kernel -s 640 -c 4 -o gpurun_out/prof_gemm_decode $CMD > gpurun_out/ncu_full1.log 2>&1
+# launch list of one warm prefill (225 launches)
+ncu --metrics gpu__time_duration.sum --clock-control none -k "$KN" -s 225 -c 225 --csv --log-file gpurun_out/launches_prefill.csv $CMD > gpurun_out/ncu_list2.log 2>&1
+echo "ncu list prefill exit $?"
+ncu --set full --clock-control none --import-source on -k regex:gemm_tcgen05_kernel -s 512 -c 4 -o gpurun_out/prof_gemm_decode $CMD > gpurun_out/ncu_full1.log 2>&1
 echo "ncu gemm decode exit $?"
 ncu --set full --clock-control none --import-source on -k regex:persistent -s 128 -c 4 -o gpurun_out/prof_gemm_prefill $CMD > gpurun_out/ncu_full2.log 2>&1
 echo "ncu gemm prefill exit $?"
 ncu --set full --clock-control none --import-source on -k regex:decode_attn_kernel -s 40 -c 1 -o gpurun_out/prof_attn_decode $CMD > gpurun_out/ncu_full3.log 2>&1
 echo "ncu attn decode exit $?"
-ncu --set full --clock-control none --import-source on -k regex:prefill_attn -s 32 -c 1 -o gpurun_out/prof_attn_prefill $CMD > gpurun_out/ncu_full4.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:prefill_attn_tc -s 33 -c 1 -o gpurun_out/prof_attn_prefill_tc $CMD > gpurun_out/ncu_full4.log 2>&1
 echo "ncu attn prefill exit $?"
-ls -la gpurun_out | tail -12
+ls -la gpurun_out | tail -14
