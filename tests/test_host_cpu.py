@@ -143,3 +143,44 @@ def test_inference_backend_contract():
         be.on_backward(3)
     with pytest.raises(AssertionError):
         InferenceBackend("x", Echo())
+
+
+def test_load_block_from_local_sharded_checkpoint(tmp_path):
+    """utils/model.py:16-90 contract, offline: only the shards holding the span's layers are read, parameters keep
+    the reference's names, floating tensors are cast to the span dtype."""
+    import json
+
+    import safetensors.torch
+
+    from distributed_llm_inference_b200.utils.model import get_block_state_dict, load_block
+
+    shp = syn.SHAPES["test_gqa"]
+    shp.to_hf_config().save_pretrained(tmp_path)
+    weight_map, shards = {}, {0: {}, 1: {}}
+    per_layer = {}
+    for idx in range(shp.num_hidden_layers):
+        w = syn.make_layer_weights(shp, idx, dtype=torch.float16, norm_jitter=0.1)     # checkpoints are often fp16
+        per_layer[idx] = w
+        for name, t in w.items():
+            key = f"model.layers.{idx}.{name}.weight"
+            shard = idx % 2 if "mlp" in name else (idx + 1) % 2                       # a layer spans two shards
+            shards[shard][key] = t
+            weight_map[key] = f"model-{shard:05d}-of-00002.safetensors"
+    shards[0]["model.embed_tokens.weight"] = torch.zeros(4, 4)
+    weight_map["model.embed_tokens.weight"] = "model-00000-of-00002.safetensors"
+    for s, tensors in shards.items():
+        safetensors.torch.save_file(tensors, str(tmp_path / f"model-{s:05d}-of-00002.safetensors"))
+    (tmp_path / "model.safetensors.index.json").write_text(json.dumps({"metadata": {}, "weight_map": weight_map}))
+
+    state = get_block_state_dict(str(tmp_path), 2)
+    assert set(state) == {f"{n}.weight" for n in syn.LINEARS + syn.NORMS}
+    blk = load_block(str(tmp_path), [1, 3], rope="float", attn_implementation="eager")
+    assert [layer.layer_idx for layer in blk.layers] == [1, 3]
+    for j, idx in enumerate([1, 3]):
+        for name, t in per_layer[idx].items():
+            got = blk.state_dict()[f"layers.{j}.{name}.weight"]
+            assert got.dtype == torch.bfloat16 and torch.equal(got, t.to(torch.bfloat16))
+    with pytest.raises(FileNotFoundError):
+        get_block_state_dict(str(tmp_path / "nowhere"), 0)
+    with pytest.raises(NotImplementedError):
+        load_block(str(tmp_path), [0], use_quantized=True)
