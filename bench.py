@@ -8,8 +8,10 @@
 Workload (config.workload): BASELINE.json configs[1] — Llama-2-7B-shaped bf16, one span of 32 layers on one B200,
 batch 16, 512-token prompt, then KV-cached decode; one STEP = one decode step of the whole span for the batch
 (16 tokens).  Weights are random-init of that architecture, prompts synthetic (no network).  For N > 1 the same
-32 layers are cut into N pipeline stages (one process per GPU) with N micro-batches of 16 sequences in flight and
-hidden states handed from stage to stage by NCCL P2P send/recv ("strong" scaling: the model is fixed).
+32 layers are cut into N pipeline stages (one process per GPU) with N micro-batches of 16 sequences in flight; each
+stage's last kernel stores the hand-off tensor straight into the next stage's inbox over NVLink (NCCL send/recv is
+the fallback).  Per-GPU work per step is the same at every N (N micro-batches x 32/N layers), the number of
+sequences served grows with N: "weak" scaling.
 
 Timing: W >= 3 warm-up steps; K timed steps bracketed by barrier + synchronize, CUDA events on the launching
 stream, max over ranks.  Every step streams the span's 12.9 GB of weights (>> the 126 MB L2), so no explicit L2
@@ -407,7 +409,7 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": f"{shape.name}-shaped span ({n_total} layers) KV-cached decode, batch {BATCH} x "
                                    f"{n_mb} micro-batch(es) in flight, {PROMPT}-token prompt, context "
                                    f"{PROMPT + W}..{PROMPT + W + K}; random-init weights, synthetic hidden states",
@@ -447,7 +449,7 @@ def run_reference(args):
     cpu = cpu_reference_decode(shape, shape.num_hidden_layers, BATCH, PROMPT, budget_s=budget)
     line = {"impl": "reference", "metric": METRIC, "value": round(cpu["value"], 3), "unit": UNIT, "n_gpus": world,
             "steps": K, "warmup": W, "ms_per_step": round(BATCH / cpu["value"] * 1e3, 2), "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"Llama-2-7B-shaped span (32 layers) KV-cached decode, batch {BATCH}, "
                                    f"{PROMPT}-token context, CPU", "global_batch": BATCH, "seq_len": PROMPT,
                        "parallelism": "cpu"},
