@@ -9,9 +9,13 @@
 // Softmax runs on 4 warps, one query row per thread (tcgen05.ld of its S row), fp32 statistics in the exp2 domain.
 // O stays in TMEM for the whole key loop; it is rescaled only when a row's running maximum has grown by more than
 // 2^8 since its reference maximum was fixed (lazy rescaling), so the TMEM round trip is rare.
-// V is double-buffered (its load would otherwise sit on the critical path between two P.V products).
-// One CTA = 128 queries of one head; 96 KB of shared memory and 256 TMEM columns, so two CTAs share an SM and one
-// runs its MMAs while the other is in softmax.  Warp 0 lane 0 issues TMA, warp 1 lane 0 issues MMAs, warps 2-5 softmax.
+// K and V are double-buffered and K runs one tile ahead of V (the order in which their buffers become free).
+// Single-thread instructions (TMA, tcgen05.mma, tcgen05.commit) are issued by one ELECTED lane of a CONVERGED warp:
+// behind `if (lane == 0)` ptxas wraps each of them in an ELECT/BRA.U.ANY loop that costs ~145 cycles per issue
+// (tests/exp/mma_chain.cu), which made the issuing lanes the bottleneck (cycle counters: the Q.K^T issuer waited
+// 1459 of 2386 cycles per tile for K; tensor pipe 20 % busy).
+// One CTA = 128 queries of one head; 112 KB of shared memory and 256 TMEM columns, so two CTAs share an SM and one
+// runs its MMAs while the other is in softmax.  Warp 0 issues TMA, warp 1 issues MMAs, warps 2-5 are the softmax.
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
@@ -27,7 +31,8 @@ constexpr int FA_THREADS = 192;
 constexpr int FA_Q_BYTES = FA_BM * FA_HD * 2;        // 32 KB: two 64-column halves of [128 rows x 128 B]
 constexpr int FA_KV_BYTES = FA_BN * FA_HD * 2;       // 16 KB: two halves of [64 rows x 128 B]
 constexpr int FA_P_BYTES = FA_BM * FA_BN * 2;        // 16 KB: [128 rows x 128 B]
-constexpr int FA_SMEM = FA_Q_BYTES + 3 * FA_KV_BYTES + FA_P_BYTES + 1024;  // Q, K, V[2], P
+constexpr int FA_TILE_SMEM = FA_Q_BYTES + 4 * FA_KV_BYTES + FA_P_BYTES;  // Q, K[2], V[2], P = 112 KB
+constexpr int FA_SMEM = FA_TILE_SMEM + 128;                               // + mbarriers and the TMEM slot
 constexpr uint32_t FA_TMEM_COLS = 256;               // S: columns [0, 64), O: columns [64, 192)
 constexpr float FA_RESCALE_THRESHOLD = 8.0f;         // log2 units
 
@@ -54,22 +59,26 @@ struct FaParams {
   const int32_t* seq_lens;
   int max_pages, page_tokens, q_len, H, KV, causal;
   float scale_log2;
+  unsigned long long* dbg;  // optional cycle counters of one CTA (experiments only; nullptr in production)
 };
 
 __global__ void __launch_bounds__(FA_THREADS, 2)
 prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
                        const __grid_constant__ CUtensorMap tma_v, const FaParams p) {
-  extern __shared__ uint8_t fa_smem_raw[];
-  // barriers: 0 q_full, 1 k_full, 2 k_empty, 3 s_full, 4 s_empty, 5 p_full, 6 pv_done, 7-8 v_full[2], 9-10 v_empty[2]
-  __shared__ uint64_t bars[11];
-  __shared__ uint32_t tmem_base_slot;
+  // No static shared memory: the dynamic window then starts at the CTA's (1024-byte aligned) shared base, and two
+  // CTAs of 112 KB + 128 B fit one SM.  Layout: Q | K[2] | V[2] | P | mbarriers | TMEM slot.
+  extern __shared__ __align__(1024) uint8_t fa_smem_raw[];
+  // barriers: 0 q_full, 1 s_full, 2 s_empty, 3 p_full, 4 pv_done, 5-6 k_full[2], 7-8 k_empty[2], 9-10 v_full[2], 11-12 v_empty[2]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(fa_smem_raw + FA_TILE_SMEM);
+  uint32_t& tmem_base_slot = *reinterpret_cast<uint32_t*>(fa_smem_raw + FA_TILE_SMEM + 13 * 8);
 
-  const uint32_t base = (smem_u32(fa_smem_raw) + 1023u) & ~1023u;
-  const uint32_t sQ = base, sK = sQ + FA_Q_BYTES, sV = sK + FA_KV_BYTES, sP = sV + 2 * FA_KV_BYTES;
+  const uint32_t base = smem_u32(fa_smem_raw);
+  if (base & 1023u) __trap();  // the 128B swizzle needs 1024-byte aligned tiles
+  const uint32_t sQ = base, sK = sQ + FA_Q_BYTES, sV = sK + 2 * FA_KV_BYTES, sP = sV + 2 * FA_KV_BYTES;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t q_full = smem_u32(&bars[0]), k_full = smem_u32(&bars[1]), k_empty = smem_u32(&bars[2]),
-                 s_full = smem_u32(&bars[3]), s_empty = smem_u32(&bars[4]), p_full = smem_u32(&bars[5]),
-                 pv_done = smem_u32(&bars[6]), v_full = smem_u32(&bars[7]), v_empty = smem_u32(&bars[9]);
+  const uint32_t q_full = smem_u32(&bars[0]), s_full = smem_u32(&bars[1]), s_empty = smem_u32(&bars[2]),
+                 p_full = smem_u32(&bars[3]), pv_done = smem_u32(&bars[4]), k_full = smem_u32(&bars[5]),
+                 k_empty = smem_u32(&bars[7]), v_full = smem_u32(&bars[9]), v_empty = smem_u32(&bars[11]);
 
   pdl_trigger();
   if (threadIdx.x == 0) {
@@ -78,7 +87,9 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_v) : "memory");
     mbar_init(q_full, 1);
     mbar_init(k_full, 1);
+    mbar_init(k_full + 8, 1);
     mbar_init(k_empty, 1);
+    mbar_init(k_empty + 8, 1);
     mbar_init(v_full, 1);
     mbar_init(v_full + 8, 1);
     mbar_init(v_empty, 1);
@@ -111,61 +122,82 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
   const int n_tiles = (kv_end + FA_BN - 1) / FA_BN;
 
   if (warp == 0) {
-    if (lane == 0) {  // ===== TMA producer =====
-      const int32_t* bt = p.block_table + (long long)b * p.max_pages;
-      const int pages_per_tile = FA_BN / p.page_tokens;
-      const uint32_t page_bytes = (uint32_t)p.page_tokens * 128u;  // one head-dim half of one page
+    // ===== TMA producer: Q, then K(j+1) and V(j) alternately — the order in which their buffers become free =====
+    const int32_t* bt = p.block_table + (long long)b * p.max_pages;
+    const int pages_per_tile = FA_BN / p.page_tokens;
+    const uint32_t page_bytes = (uint32_t)p.page_tokens * 128u;  // one head-dim half of one page
+    auto lookup = [&](int j) {  // lane pg: first pool row of page pg of tile j (past the end: any valid page, masked later)
+      int my_row = 0;
+      if (lane < pages_per_tile && j < n_tiles) {
+        const int tok0 = (j * pages_per_tile + lane) * p.page_tokens;
+        const int page = tok0 < T ? bt[j * pages_per_tile + lane] : bt[0];
+        my_row = (page * p.KV + kvh) * p.page_tokens;
+      }
+      return my_row;
+    };
+    auto load_tile = [&](int j, int my_row, const CUtensorMap* map, uint32_t smem_base, uint32_t full_bar) {
+      const uint32_t dst = smem_base + (j & 1) * FA_KV_BYTES, bar = full_bar + 8 * (j & 1);
+      if (elect_one()) mbar_expect_tx(bar, FA_KV_BYTES);
+      __syncwarp();
+      for (int pg = 0; pg < pages_per_tile; ++pg) {
+        const int row = __shfl_sync(0xffffffffu, my_row, pg);
+        if (elect_one()) {
+          tma_load_2d(dst + pg * page_bytes, map, bar, 0, row);
+          tma_load_2d(dst + FA_KV_BYTES / 2 + pg * page_bytes, map, bar, 64, row);
+        }
+        __syncwarp();
+      }
+    };
+    if (elect_one()) {
       mbar_expect_tx(q_full, FA_Q_BYTES);
       tma_load_2d(sQ, &tma_q, q_full, h * FA_HD, b * p.q_len + m0);
       tma_load_2d(sQ + FA_Q_BYTES / 2, &tma_q, q_full, h * FA_HD + 64, b * p.q_len + m0);
-      for (int j = 0; j < n_tiles; ++j) {
-        const int page0 = j * pages_per_tile;
-        if (j > 0) mbar_wait(k_empty, (j - 1) & 1, 64);  // QK^T of the previous tile has read K
-        mbar_expect_tx(k_full, FA_KV_BYTES);
-        for (int pg = 0; pg < pages_per_tile; ++pg) {
-          const int tok0 = (page0 + pg) * p.page_tokens;
-          const int page = tok0 < T ? bt[page0 + pg] : bt[0];  // past the end: any valid page (masked later)
-          const int row = (page * p.KV + kvh) * p.page_tokens;
-          tma_load_2d(sK + pg * page_bytes, &tma_k, k_full, 0, row);
-          tma_load_2d(sK + FA_KV_BYTES / 2 + pg * page_bytes, &tma_k, k_full, 64, row);
-        }
-        const int vb = j & 1;  // V buffer of this tile; free once P V of tile j - 2 has read it
-        if (j >= 2) mbar_wait(v_empty + 8 * vb, ((j >> 1) - 1) & 1, 64);
-        mbar_expect_tx(v_full + 8 * vb, FA_KV_BYTES);
-        for (int pg = 0; pg < pages_per_tile; ++pg) {
-          const int tok0 = (page0 + pg) * p.page_tokens;
-          const int page = tok0 < T ? bt[page0 + pg] : bt[0];
-          const int row = (page * p.KV + kvh) * p.page_tokens;
-          tma_load_2d(sV + vb * FA_KV_BYTES + pg * page_bytes, &tma_v, v_full + 8 * vb, 0, row);
-          tma_load_2d(sV + vb * FA_KV_BYTES + FA_KV_BYTES / 2 + pg * page_bytes, &tma_v, v_full + 8 * vb, 64, row);
-        }
+    }
+    __syncwarp();
+    int row_cur = lookup(0), row_next = lookup(1);
+    load_tile(0, row_cur, &tma_k, sK, k_full);
+    for (int j = 0; j < n_tiles; ++j) {
+      const int row_next2 = lookup(j + 2);  // page-table reads stay two tiles ahead of their use
+      if (j + 1 < n_tiles) {                // K(j+1): its buffer is free once Q.K^T(j-1) has completed
+        if (j >= 1) mbar_wait(k_empty + 8 * ((j + 1) & 1), (((j + 1) >> 1) - 1) & 1, 64);
+        load_tile(j + 1, row_next, &tma_k, sK, k_full);
       }
+      if (j >= 2) mbar_wait(v_empty + 8 * (j & 1), ((j >> 1) - 1) & 1, 64);  // V(j): free once P.V(j-2) has completed
+      load_tile(j, row_cur, &tma_v, sV, v_full);
+      row_cur = row_next;
+      row_next = row_next2;
     }
   } else if (warp == 1) {
-    if (lane == 0) {  // ===== MMA issuer =====
-      constexpr uint32_t idesc_qk = fa_idesc(FA_BN, false);
-      constexpr uint32_t idesc_pv = fa_idesc(FA_HD, true);
-      auto issue_qk = [&](int j) {
-        mbar_wait(k_full, j & 1, 32);
-        if (j > 0) mbar_wait(s_empty, (j - 1) & 1, 32);  // softmax has copied S of the previous tile to registers
-        tcgen05_fence_after();
+    // ===== MMA issuer (converged warp, elected lane): Q.K^T runs one tile ahead of P.V =====
+    constexpr uint32_t idesc_qk = fa_idesc(FA_BN, false);
+    constexpr uint32_t idesc_pv = fa_idesc(FA_HD, true);
+    auto issue_qk = [&](int j) {
+      const int kbuf = j & 1;
+      mbar_wait(k_full + 8 * kbuf, (j >> 1) & 1, 32);
+      if (j > 0) mbar_wait(s_empty, (j - 1) & 1, 32);  // softmax has copied S of the previous tile to registers
+      tcgen05_fence_after();
+      if (elect_one()) {
 #pragma unroll
         for (int kb = 0; kb < 2; ++kb) {
-          const uint64_t a = umma_desc_sw128(sQ + kb * (FA_Q_BYTES / 2)), bd = umma_desc_sw128(sK + kb * (FA_KV_BYTES / 2));
+          const uint64_t a = umma_desc_sw128(sQ + kb * (FA_Q_BYTES / 2)),
+                         bd = umma_desc_sw128(sK + kbuf * FA_KV_BYTES + kb * (FA_KV_BYTES / 2));
 #pragma unroll
           for (int k = 0; k < 4; ++k) umma_bf16(tS, a + 2 * k, bd + 2 * k, idesc_qk, (kb | k) ? 1u : 0u);
         }
         umma_commit(s_full);
-        umma_commit(k_empty);
-      };
-      mbar_wait(q_full, 0);
-      issue_qk(0);
-      for (int j = 0; j < n_tiles; ++j) {
-        if (j + 1 < n_tiles) issue_qk(j + 1);  // overlaps the softmax of tile j
-        const int vb = j & 1;
-        mbar_wait(v_full + 8 * vb, (j >> 1) & 1, 32);
-        mbar_wait(p_full, j & 1, 32);
-        tcgen05_fence_after();
+        umma_commit(k_empty + 8 * kbuf);
+      }
+      __syncwarp();
+    };
+    mbar_wait(q_full, 0, 32);
+    issue_qk(0);
+    for (int j = 0; j < n_tiles; ++j) {
+      if (j + 1 < n_tiles) issue_qk(j + 1);  // overlaps the softmax of tile j
+      const int vb = j & 1;
+      mbar_wait(v_full + 8 * vb, (j >> 1) & 1, 32);
+      mbar_wait(p_full, j & 1, 32);
+      tcgen05_fence_after();
+      if (elect_one()) {
         const uint64_t a = umma_desc_sw128(sP);
 #pragma unroll
         for (int k = 0; k < 4; ++k) {  // 16 keys per instruction: two 8-key swizzle atoms of V
@@ -175,6 +207,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
         umma_commit(pv_done);
         umma_commit(v_empty + 8 * vb);
       }
+      __syncwarp();
     }
   } else {
     // ===== softmax warps: one query row per thread =====
@@ -185,10 +218,15 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
     const int pos = past + qi;  // absolute position of this query
     float m_ref = -INFINITY, l = 0.f;
     uint32_t v[16];
+    const bool dbg_on = p.dbg != nullptr && blockIdx.x == gridDim.x - 1 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 64;
+    unsigned long long tc[5] = {0, 0, 0, 0, 0}, t0 = 0, t1;
+#define FA_TICK(i) do { if (dbg_on) { t1 = clock64(); tc[i] += t1 - t0; t0 = t1; } } while (0)
+    if (dbg_on) t0 = clock64();
     for (int j = 0; j < n_tiles; ++j) {
       const int j0 = j * FA_BN;
       float s[FA_BN];  // raw scores (unscaled): the 1/sqrt(hd)*log2(e) factor is folded into the exp2 argument
       mbar_wait(s_full, j & 1, 20);
+      FA_TICK(0);
       tcgen05_fence_after();
 #pragma unroll
       for (int c0 = 0; c0 < FA_BN; c0 += 16) {
@@ -199,6 +237,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       }
       tcgen05_fence_before();
       mbar_arrive(s_empty);
+      FA_TICK(1);
 
       if ((j0 + FA_BN > T) || (p.causal && j0 + FA_BN - 1 > past + m0)) {  // tile touches the diagonal / context end
 #pragma unroll
@@ -235,6 +274,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
         pk[i / 2] = pack_bf16(p0, p1);
       }
       l += l0 + l1;
+      FA_TICK(2);
 
       if (j > 0) {
         mbar_wait(pv_done, (j - 1) & 1, 20);  // P buffer free, O holds tiles 0..j-1
@@ -251,6 +291,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
           tmem_st_wait();
         }
       }
+      FA_TICK(3);
       // P row -> smem, K-major 128B-swizzled: 16-byte chunk c of row r lives at chunk (c ^ (r & 7))
       uint8_t* prow = fa_smem_raw + (sP - smem_u32(fa_smem_raw)) + row * 128;
 #pragma unroll
@@ -259,6 +300,11 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       fence_proxy_async_smem();
       tcgen05_fence_before();
       mbar_arrive(p_full);
+      FA_TICK(4);
+    }
+    if (dbg_on) {
+      for (int i = 0; i < 5; ++i) p.dbg[i] = tc[i];
+      p.dbg[5] = n_tiles;
     }
 
     // ---- finalize: O / l -> bf16 ----
@@ -320,6 +366,10 @@ int launch_prefill_attention_tc(const __nv_bfloat16* q, __nv_bfloat16* out, cons
   p.KV = KV;
   p.causal = causal ? 1 : 0;
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)FA_HD);
+  {
+    const char* e = getenv("DLI_FA_DBG_PTR");  // experiments: device pointer (hex) receiving cycle counters
+    p.dbg = e ? reinterpret_cast<unsigned long long*>(strtoull(e, nullptr, 16)) : nullptr;
+  }
   dim3 grid((q_len + FA_BM - 1) / FA_BM, H, batch);
   return launch_kernel("prefill_attn_tc_kernel", prefill_attn_tc_kernel, grid, dim3(FA_THREADS), (size_t)FA_SMEM, st, tq, tk, tv, p);
 }

@@ -244,7 +244,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
 
   if (kb1 > kb0) {
     if (warp == 0) {
-      if (lane == 0) {  // ===== TMA producer =====
+      {  // ===== TMA producer (converged warp; one elected lane issues: see elect_one) =====
         // The weight operand does not depend on the previous kernel of the stream: under programmatic dependent
         // launch its first `stages` tiles are requested BEFORE griddepcontrol.wait, so weights keep streaming from
         // HBM while the predecessor drains; the activation operand is requested after the wait.
@@ -268,41 +268,53 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
           else tma_load_2d(a_dst, &tma_a, full0 + 8 * s, kb * BK, a_row0);
         };
         const int n_pre = min(stages, kb1 - kb0);
-        for (int i = 0; i < n_pre; ++i) {  // fresh barriers: every slot is free
-          mbar_expect_tx(full0 + 8 * i, STAGE_BYTES);
-          load_weights(i, kb0 + i);
+        if (elect_one()) {
+          for (int i = 0; i < n_pre; ++i) {  // fresh barriers: every slot is free
+            mbar_expect_tx(full0 + 8 * i, STAGE_BYTES);
+            load_weights(i, kb0 + i);
+          }
         }
+        __syncwarp();
         pdl_wait();
-        for (int i = 0; i < n_pre; ++i) load_acts(i, kb0 + i);
+        if (elect_one()) {
+          for (int i = 0; i < n_pre; ++i) load_acts(i, kb0 + i);
+        }
+        __syncwarp();
         int s = n_pre == stages ? 0 : n_pre;
         uint32_t ph = n_pre == stages ? 1 : 0;
         for (int kb = kb0 + n_pre; kb < kb1; ++kb) {
           mbar_wait(empty0 + 8 * s, ph ^ 1);
-          mbar_expect_tx(full0 + 8 * s, STAGE_BYTES);
-          load_weights(s, kb);
-          load_acts(s, kb);
+          if (elect_one()) {
+            mbar_expect_tx(full0 + 8 * s, STAGE_BYTES);
+            load_weights(s, kb);
+            load_acts(s, kb);
+          }
+          __syncwarp();
           if (++s == stages) { s = 0; ph ^= 1; }
         }
       }
     } else if (warp == 1) {
-      if (lane == 0) {  // ===== MMA issuer =====
+      {  // ===== MMA issuer (converged warp; one elected lane issues) =====
         constexpr uint32_t idesc = umma_idesc_bf16(BN);
         int s = 0;
         uint32_t ph = 0;
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(full0 + 8 * s, ph);
           tcgen05_fence_after();
-          const uint32_t a_src = tiles + s * STAGE_BYTES;
-          const uint64_t adesc = umma_desc_sw128(a_src), bdesc = umma_desc_sw128(a_src + A_TILE_BYTES);
+          if (elect_one()) {
+            const uint32_t a_src = tiles + s * STAGE_BYTES;
+            const uint64_t adesc = umma_desc_sw128(a_src), bdesc = umma_desc_sw128(a_src + A_TILE_BYTES);
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            // advancing 16 bf16 (32 bytes) along K inside the swizzle atom: +2 in the (addr >> 4) field
-            umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < BK / UMMA_K; ++k) {
+              // advancing 16 bf16 (32 bytes) along K inside the swizzle atom: +2 in the (addr >> 4) field
+              umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            }
+            umma_commit(empty0 + 8 * s);  // frees the smem slot once these MMAs have read it
+            if (kb + 1 == kb1) umma_commit(tmem_full);  // accumulator complete
           }
-          umma_commit(empty0 + 8 * s);  // frees the smem slot once these MMAs have read it
+          __syncwarp();
           if (++s == stages) { s = 0; ph ^= 1; }
         }
-        umma_commit(tmem_full);  // accumulator complete
       }
     } else {  // ===== epilogue: TMEM -> registers -> global =====
       pdl_wait();  // the output buffers belong to the predecessor until it has completed
@@ -455,7 +467,7 @@ gemm_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const 
   const uint32_t tmem_d = tmem_base_slot;
 
   if (warp == 0) {
-    if (lane == 0) {  // ===== TMA producer =====
+    {  // ===== TMA producer (converged warp; one elected lane issues) =====
       int s = 0;
       uint32_t ph = 0;
       bool waited = false;
@@ -466,24 +478,28 @@ gemm_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const 
         for (int kb = 0; kb < n_kb; ++kb) {
           mbar_wait(empty0 + 8 * s, ph ^ 1);
           const uint32_t a_dst = tiles + s * STAGE_BYTES, b_dst = a_dst + A_TILE_BYTES;
-          mbar_expect_tx(full0 + 8 * s, STAGE_BYTES);
-          if (EPI == DLI_EPI_SILU_MUL_BF16) {  // gate rows then up rows of the same features
-            tma_load_2d(b_dst, &tma_b, full0 + 8 * s, kb * BK, b_row0);
-            tma_load_2d(b_dst + B_TILE_BYTES / 2, &tma_b, full0 + 8 * s, kb * BK, p.up_row_offset + b_row0);
-          } else {
-            tma_load_2d(b_dst, &tma_b, full0 + 8 * s, kb * BK, b_row0);
+          if (elect_one()) {
+            mbar_expect_tx(full0 + 8 * s, STAGE_BYTES);
+            if (EPI == DLI_EPI_SILU_MUL_BF16) {  // gate rows then up rows of the same features
+              tma_load_2d(b_dst, &tma_b, full0 + 8 * s, kb * BK, b_row0);
+              tma_load_2d(b_dst + B_TILE_BYTES / 2, &tma_b, full0 + 8 * s, kb * BK, p.up_row_offset + b_row0);
+            } else {
+              tma_load_2d(b_dst, &tma_b, full0 + 8 * s, kb * BK, b_row0);
+            }
           }
+          __syncwarp();
           if (!waited) {  // weights do not depend on the previous kernel; activations do
             pdl_wait();
             waited = true;
           }
-          tma_load_2d(a_dst, &tma_a, full0 + 8 * s, kb * BK, a_row0);
+          if (elect_one()) tma_load_2d(a_dst, &tma_a, full0 + 8 * s, kb * BK, a_row0);
+          __syncwarp();
           if (++s == stages) { s = 0; ph ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {  // ===== MMA issuer =====
+    {  // ===== MMA issuer (converged warp; one elected lane issues) =====
       constexpr uint32_t idesc = umma_idesc_bf16(BN);
       int s = 0, it = 0;
       uint32_t ph = 0;
@@ -495,14 +511,17 @@ gemm_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const 
         for (int kb = 0; kb < n_kb; ++kb) {
           mbar_wait(full0 + 8 * s, ph);
           tcgen05_fence_after();
-          const uint32_t a_src = tiles + s * STAGE_BYTES;
-          const uint64_t adesc = umma_desc_sw128(a_src), bdesc = umma_desc_sw128(a_src + A_TILE_BYTES);
+          if (elect_one()) {
+            const uint32_t a_src = tiles + s * STAGE_BYTES;
+            const uint64_t adesc = umma_desc_sw128(a_src), bdesc = umma_desc_sw128(a_src + A_TILE_BYTES);
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) umma_bf16(d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
-          umma_commit(empty0 + 8 * s);
+            for (int k = 0; k < BK / UMMA_K; ++k) umma_bf16(d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            umma_commit(empty0 + 8 * s);
+            if (kb + 1 == n_kb) umma_commit(tfull0 + 8 * acc);
+          }
+          __syncwarp();
           if (++s == stages) { s = 0; ph ^= 1; }
         }
-        umma_commit(tfull0 + 8 * acc);
       }
     }
   } else {  // ===== epilogue warps =====

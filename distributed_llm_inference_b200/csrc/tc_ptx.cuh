@@ -81,6 +81,15 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int bn) {
 }
 
 
+// One lane of a CONVERGED warp.  Single-thread instructions (tcgen05.mma, tcgen05.commit, TMA) must be issued from
+// warp-uniform control flow under this predicate: behind a plain `if (lane == 0)` ptxas wraps every UTCHMMA / UTMALDG
+// in an ELECT + BRA.U.ANY loop, which measured ~145 cycles per MMA issue (tests/exp/mma_chain.cu) and capped the
+// tensor pipe at 20 % (attention, N = 64) to 83 % (GEMM, N = 256).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
