@@ -13,6 +13,9 @@
 #include "common.cuh"
 
 #include <math.h>
+#include <stdlib.h>
+
+#include "tc_ptx.cuh"
 
 namespace dli {
 
@@ -35,7 +38,7 @@ size_t decode_attn_scratch_bytes(int batch, int H, int hd, int max_ctx) {
 }
 
 template <int HD, int G>
-__global__ void __launch_bounds__(DEC_THREADS) decode_attn_kernel(const __nv_bfloat16* __restrict__ q, KvView kv,
+__global__ void __launch_bounds__(DEC_THREADS) decode_attn_direct_kernel(const __nv_bfloat16* __restrict__ q, KvView kv,
                                                                   float* __restrict__ scratch,
                                                                   __nv_bfloat16* __restrict__ out, int H, int KV,
                                                                   float scale_log2) {
@@ -171,6 +174,225 @@ __global__ void __launch_bounds__(DEC_THREADS) decode_attn_kernel(const __nv_bfl
   }
 }
 
+
+// -------------------------------------------------------------------------------------------------------
+// Staged variant (the default).  The direct kernel above keeps at most one 16 KB fetch per CTA in flight
+// and every fetch waits on a block-table lookup first, which left HBM half idle (ncu: 50 % DRAM
+// throughput, 21 % warps active at B=16, ctx 512).  Here a fifth warp is a pure producer: it walks the
+// block table and streams K and V into a ring of DEC_STAGES x 32-token stages with 1-D bulk copies
+// (cp.async.bulk, one per page piece, completion counted on the stage's mbarrier), so that 48 KB per CTA
+// -- about 24 MB over a full grid -- is in flight whatever the consumer warps are doing.  The four
+// consumer warps use the direct kernel's lane mapping and arithmetic; they copy a stage from shared
+// memory to registers, hand the slot back at once and only then do the math.
+// -------------------------------------------------------------------------------------------------------
+constexpr int DEC_STAGES = 3;
+constexpr int DEC_STAGE_TOK = 32;
+constexpr int DEC_THREADS_STAGED = DEC_THREADS + 32;
+
+template <int HD>
+__host__ __device__ constexpr int dec_stage_bytes() { return DEC_STAGE_TOK * HD * 2 * 2; }  // K then V, bf16
+// the ring and its barriers, or the end-of-kernel merge buffer that overlays them, whichever is larger
+template <int HD, int G>
+__host__ __device__ constexpr int dec_smem_bytes() {
+  constexpr int ring = DEC_STAGES * dec_stage_bytes<HD>() + 2 * DEC_STAGES * 8;
+  constexpr int merge = (DEC_THREADS / 32) * (32 / (HD / 8)) * G * (HD + 2) * 4;
+  return ring > merge ? ring : merge;
+}
+
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+
+template <int HD, int G>
+__global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const __nv_bfloat16* __restrict__ q, KvView kv,
+                                                                         float* __restrict__ scratch,
+                                                                         __nv_bfloat16* __restrict__ out, int H, int KV,
+                                                                         float scale_log2) {
+  constexpr int LPT = HD / 8;                   // lanes per token
+  constexpr int GPW = 32 / LPT;                 // token groups per warp
+  constexpr int NG = (DEC_THREADS / 32) * GPW;  // token groups per CTA
+  constexpr int UNROLL = DEC_STAGE_TOK / NG;    // tokens of a stage per group
+  constexpr int UH = G <= 2 ? UNROLL : (UNROLL >= 2 ? 2 : 1);  // tokens held in registers at a time
+  constexpr int ROW = HD * 2;                   // bytes of one token's K (or V) row
+  constexpr int KPART = DEC_STAGE_TOK * ROW;
+  constexpr int STAGE = dec_stage_bytes<HD>();
+  static_assert(UNROLL % UH == 0, "stage must split evenly");
+  static_assert(NG * G * (HD + 2) * 4 <= dec_smem_bytes<HD, G>(), "merge buffer must fit");
+
+  extern __shared__ __align__(128) unsigned char dsm[];
+  const uint32_t ring = smem_u32(dsm);
+  const uint32_t full0 = ring + DEC_STAGES * STAGE, empty0 = full0 + 8 * DEC_STAGES;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < DEC_STAGES; ++i) {
+      mbar_init(full0 + 8 * i, 1);
+      mbar_init(empty0 + 8 * i, DEC_THREADS / 32);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  pdl_trigger();
+  pdl_wait();
+
+  const int split = blockIdx.x, n_splits = gridDim.x, kvh = blockIdx.y, b = blockIdx.z;
+  const int T = kv.seq_lens[b] + 1;  // the step's own token is already appended
+  int chunk = (T + n_splits - 1) / n_splits;
+  chunk = (chunk + DEC_STAGE_TOK - 1) & ~(DEC_STAGE_TOK - 1);
+  const int t_begin = split * chunk;
+  const int t_end = min(T, t_begin + chunk);
+  const int n_stages = t_end > t_begin ? (t_end - t_begin + DEC_STAGE_TOK - 1) / DEC_STAGE_TOK : 0;
+
+  float o[G][8], m[G], l[G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    m[g] = -INFINITY;
+    l[g] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[g][j] = 0.f;
+  }
+  const int grp = warp * GPW + lane / LPT;  // token group of this lane (consumer warps)
+  const int dl = (lane % LPT) * 8;          // head_dim slice [dl, dl + 8)
+
+  if (warp == DEC_THREADS / 32) {
+    // ===== producer warp: lane i copies the i-th page piece of the stage =====
+    const int32_t* bt = kv.block_table + (long long)b * kv.max_pages;
+    const int pt = kv.page_tokens;
+    for (int i = 0; i < n_stages; ++i) {
+      const int slot = i % DEC_STAGES;
+      const int s0 = t_begin + i * DEC_STAGE_TOK, s1 = min(t_end, s0 + DEC_STAGE_TOK);
+      const int p0 = s0 / pt, p1 = (s1 - 1) / pt;
+      // pieces beyond the 32nd (page_tokens == 1 is the only way to get there) are taken in a second pass
+      int page = -1;
+      if (p0 + lane <= p1) page = bt[p0 + lane];
+      if (i >= DEC_STAGES) mbar_wait(empty0 + 8 * slot, ((uint32_t)(i / DEC_STAGES) - 1) & 1);
+      if (lane == 0) mbar_expect_tx(full0 + 8 * slot, (uint32_t)(s1 - s0) * ROW * 2);
+      __syncwarp();
+      if (page >= 0) {
+        const int ta = max(s0, (p0 + lane) * pt), tb = min(s1, (p0 + lane + 1) * pt);
+        const long long off = (((long long)page * KV + kvh) * pt + (ta - (p0 + lane) * pt)) * HD;
+        const uint32_t dst = ring + slot * STAGE + (uint32_t)(ta - s0) * ROW;
+        const uint32_t bytes = (uint32_t)(tb - ta) * ROW;
+        bulk_load_1d(dst, kv.k + off, bytes, full0 + 8 * slot);
+        bulk_load_1d(dst + KPART, kv.v + off, bytes, full0 + 8 * slot);
+      }
+    }
+  } else {
+    float qf[G][8];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const uint4 a = *reinterpret_cast<const uint4*>(q + ((long long)b * H + kvh * G + g) * HD + dl);
+      qf[g][0] = bf16_lo(a.x) * scale_log2; qf[g][1] = bf16_hi(a.x) * scale_log2;
+      qf[g][2] = bf16_lo(a.y) * scale_log2; qf[g][3] = bf16_hi(a.y) * scale_log2;
+      qf[g][4] = bf16_lo(a.z) * scale_log2; qf[g][5] = bf16_hi(a.z) * scale_log2;
+      qf[g][6] = bf16_lo(a.w) * scale_log2; qf[g][7] = bf16_hi(a.w) * scale_log2;
+    }
+    for (int i = 0; i < n_stages; ++i) {
+      const int slot = i % DEC_STAGES;
+      const int t0 = t_begin + i * DEC_STAGE_TOK;
+      const uint32_t kbase = ring + slot * STAGE + (uint32_t)grp * ROW + dl * 2;
+      mbar_wait(full0 + 8 * slot, (uint32_t)(i / DEC_STAGES) & 1);
+#pragma unroll
+      for (int h = 0; h < UNROLL / UH; ++h) {
+        uint4 kk[UH], vv[UH];
+        bool ok[UH];
+#pragma unroll
+        for (int u = 0; u < UH; ++u) {
+          const int tok = (h * UH + u) * NG;
+          ok[u] = t0 + grp + tok < t_end;  // rows past the end of the split were never copied
+          kk[u] = lds_v4(kbase + tok * ROW);
+          vv[u] = lds_v4(kbase + KPART + tok * ROW);
+          if (!ok[u]) vv[u] = make_uint4(0, 0, 0, 0);
+        }
+        if (h == UNROLL / UH - 1) {  // the stage is in registers: give the slot back before the arithmetic
+          __syncwarp();
+          if (lane == 0) mbar_arrive(empty0 + 8 * slot);
+        }
+        float s[UH][G];
+#pragma unroll
+        for (int u = 0; u < UH; ++u) {
+          const float kf[8] = {bf16_lo(kk[u].x), bf16_hi(kk[u].x), bf16_lo(kk[u].y), bf16_hi(kk[u].y),
+                               bf16_lo(kk[u].z), bf16_hi(kk[u].z), bf16_lo(kk[u].w), bf16_hi(kk[u].w)};
+#pragma unroll
+          for (int g = 0; g < G; ++g) {
+            float acc = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc = fmaf(qf[g][j], kf[j], acc);
+#pragma unroll
+            for (int off = LPT / 2; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+            s[u][g] = ok[u] ? acc : -INFINITY;
+          }
+        }
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          float mn = m[g];
+#pragma unroll
+          for (int u = 0; u < UH; ++u) mn = fmaxf(mn, s[u][g]);
+          const float mref = mn == -INFINITY ? 0.f : mn;  // group has seen no token yet: keep everything at zero
+          const float corr = exp2f(m[g] - mref);
+          m[g] = mn;
+          l[g] *= corr;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[g][j] *= corr;
+#pragma unroll
+          for (int u = 0; u < UH; ++u) {
+            const float pw = exp2f(s[u][g] - mref);
+            l[g] += pw;
+            const float vf[8] = {bf16_lo(vv[u].x), bf16_hi(vv[u].x), bf16_lo(vv[u].y), bf16_hi(vv[u].y),
+                                 bf16_lo(vv[u].z), bf16_hi(vv[u].z), bf16_lo(vv[u].w), bf16_hi(vv[u].w)};
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[g][j] = fmaf(pw, vf[j], o[g][j]);
+          }
+        }
+      }
+    }
+  }
+
+  // merge the NG token groups of the CTA through the (now idle) ring
+  __syncthreads();
+  float* sm_o = reinterpret_cast<float*>(dsm);            // [NG][G][HD]
+  float* sm_m = sm_o + NG * G * HD;                       // [NG][G]
+  float* sm_l = sm_m + NG * G;                            // [NG][G]
+  if (warp < DEC_THREADS / 32) {
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sm_o[(grp * G + g) * HD + dl + j] = o[g][j];
+      if ((lane % LPT) == 0) { sm_m[grp * G + g] = m[g]; sm_l[grp * G + g] = l[g]; }
+    }
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < G * HD; idx += DEC_THREADS_STAGED) {
+    const int g = idx / HD, d = idx - g * HD;
+    float M = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < NG; ++i) M = fmaxf(M, sm_m[i * G + g]);
+    float L = 0.f, O = 0.f;
+    if (M > -INFINITY) {
+#pragma unroll
+      for (int i = 0; i < NG; ++i) {
+        const float w = exp2f(sm_m[i * G + g] - M);  // groups that saw no token have m = -inf -> w = 0
+        L = fmaf(sm_l[i * G + g], w, L);
+        O = fmaf(sm_o[(i * G + g) * HD + d], w, O);
+      }
+    }
+    if (n_splits == 1) {  // the whole context in one CTA: normalise and store, no combine pass
+      out[((long long)b * H + kvh * G + g) * HD + d] = __float2bfloat16_rn(O / L);
+    } else {
+      float* dst = scratch + (((long long)b * H + kvh * G + g) * n_splits + split) * (HD + 2);
+      dst[d] = O;
+      if (d == 0) { dst[HD] = M; dst[HD + 1] = L; }
+    }
+  }
+}
+
 template <int HD>
 __global__ void __launch_bounds__(HD) decode_combine_kernel(const float* __restrict__ scratch, __nv_bfloat16* __restrict__ out,
                                                             int H, int n_splits) {
@@ -193,8 +415,21 @@ template <int HD, int G>
 static int launch_dec(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV, int splits,
                       float* scratch, cudaStream_t st) {
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
-  int rc = launch_kernel("decode_attn_kernel", decode_attn_kernel<HD, G>, dim3(splits, KV, batch), dim3(DEC_THREADS), 0, st, q,
-                         kv, scratch, out, H, KV, scale_log2);
+  static const bool direct = getenv("DLI_DEC_DIRECT") != nullptr;  // A/B switch for the register-staged kernel
+  int rc;
+  if (direct) {
+    rc = launch_kernel("decode_attn_direct_kernel", decode_attn_direct_kernel<HD, G>, dim3(splits, KV, batch),
+                       dim3(DEC_THREADS), 0, st, q, kv, scratch, out, H, KV, scale_log2);
+  } else {
+    static bool attr_set = false;  // > 48 KB of dynamic shared memory needs the opt-in once per instantiation
+    if (!attr_set) {
+      DLI_CUDA_OK(cudaFuncSetAttribute(decode_attn_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dec_smem_bytes<HD, G>()));
+      attr_set = true;
+    }
+    rc = launch_kernel("decode_attn_kernel", decode_attn_kernel<HD, G>, dim3(splits, KV, batch),
+                       dim3(DEC_THREADS_STAGED), dec_smem_bytes<HD, G>(), st, q, kv, scratch, out, H, KV, scale_log2);
+  }
   if (rc || splits == 1) return rc;
   return launch_kernel("decode_combine_kernel", decode_combine_kernel<HD>, dim3(H, batch), dim3(HD), 0, st,
                        (const float*)scratch, out, H, splits);
