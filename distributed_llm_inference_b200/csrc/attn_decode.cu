@@ -444,6 +444,15 @@ int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const Kv
   const size_t need = (size_t)batch * H * splits * (hd + 2) * sizeof(float);
   if (scratch_bytes < need)
     return fail(DLI_ERR_WORKSPACE, "dli_decode_attention: scratch %zu bytes < %zu needed", scratch_bytes, need);
+  if (decode_attn_gqa_supported(kv, G, hd)) {  // grouped-query models: tensor-core kernel (attn_decode_gqa.cu)
+    int rc = launch_decode_attention_gqa(q, out, kv, batch, H, KV, hd, splits, scratch, st);
+    if (rc || splits == 1) return rc;
+    if (hd == 128)
+      return launch_kernel("decode_combine_kernel", decode_combine_kernel<128>, dim3(H, batch), dim3(128), 0, st,
+                           (const float*)scratch, out, H, splits);
+    return launch_kernel("decode_combine_kernel", decode_combine_kernel<64>, dim3(H, batch), dim3(64), 0, st,
+                         (const float*)scratch, out, H, splits);
+  }
 #define DLI_DEC_CASE(HD_, G_) \
   if (hd == HD_ && G == G_) return launch_dec<HD_, G_>(q, out, kv, batch, H, KV, splits, scratch, st)
   DLI_DEC_CASE(128, 1); DLI_DEC_CASE(128, 2); DLI_DEC_CASE(128, 4); DLI_DEC_CASE(128, 8);

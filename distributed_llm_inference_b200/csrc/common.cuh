@@ -109,6 +109,9 @@ int launch_kv_evict(const dli_kv_desc* kv, int n_layers, int batch, int KV, int 
                     int n_new, const float* cos_hist, const float* sin_hist, cudaStream_t st);
 int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st);
 size_t decode_attn_scratch_bytes(int batch, int H, int hd, int max_ctx);
+bool decode_attn_gqa_supported(const KvView& kv, int G, int hd);
+int launch_decode_attention_gqa(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV,
+                                int hd, int splits, float* scratch, cudaStream_t st);
 int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV,
                             int hd, float* scratch, size_t scratch_bytes, cudaStream_t st);
 bool prefill_attn_tc_supported(const KvView& kv, int hd);

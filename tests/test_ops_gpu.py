@@ -155,6 +155,39 @@ def test_decode_attention(H, KV, hd, B, T):
     assert err <= 8e-3 * scale + 1e-3, msg                                         # bf16 output rounding
 
 
+@pytest.mark.parametrize("H,KV,hd", [(4, 4, 128), (8, 1, 128), (8, 4, 128), (16, 4, 64), (64, 8, 128)])
+@pytest.mark.parametrize("pt", [8, 16, 32, 64, 24])
+@pytest.mark.parametrize("B,T", [(3, 333), (1, 4500)])
+def test_decode_attention_ragged_pages(H, KV, hd, pt, B, T):
+    """Ragged contexts over several page sizes (24 does not tile a stage -> the generic kernel), enough context
+    for many splits, and NaN in every slot no sequence owns: nothing outside [0, T_b) may reach the output."""
+    kv = ops.PagedKV(1, B, KV, hd, T + 3, page_tokens=pt, seed=T + pt)
+    K, V = _randn(B, KV, T, hd, seed=20), _randn(B, KV, T, hd, seed=21)
+    kv.k.fill_(float("nan"))
+    kv.v.fill_(float("nan"))
+    kv.fill(0, K, V)
+    lens = [max(1, T - 97 * b - (b % 2)) for b in range(B)]                        # T_b per sequence
+    pos = torch.arange(T, device="cuda")
+    pg = kv.block_table.long()[:, pos // pt]
+    sl = (pos % pt)[None, :].expand(B, T)
+    dead = pos[None, :] >= torch.tensor(lens, device="cuda")[:, None]              # slots past each sequence's end
+    kk, vv = kv.k[0][pg, :, sl], kv.v[0][pg, :, sl]                                # [B, T, KV, hd]
+    kk[dead] = float("nan")
+    vv[dead] = float("nan")
+    kv.k[0][pg, :, sl] = kk
+    kv.v[0][pg, :, sl] = vv
+    kv.seq_lens.copy_(torch.tensor([n - 1 for n in lens], dtype=torch.int32))
+    q = _randn(B, H * hd, seed=22)
+    out = ops.decode_attention(q, kv, 0, B, H, KV, hd, max_ctx=T)
+    assert torch.isfinite(out.float()).all()
+    for b in range(B):
+        n = lens[b]
+        ref = _attn_ref(q[b:b + 1].view(1, H, 1, hd).float().cpu(), K[b:b + 1, :, :n].float().cpu(),
+                        V[b:b + 1, :, :n].float().cpu(), False, n - 1)[:, 0]
+        msg, err, scale = ops.err_report(f"decode_attn ragged H{H} KV{KV} hd{hd} pt{pt} b{b} T{n}", out[b:b + 1], ref)
+        assert err <= 8e-3 * scale + 1e-3, msg
+
+
 @pytest.mark.parametrize("H,KV,hd", [(8, 2, 64), (4, 4, 128), (8, 1, 128), (4, 2, 128)])
 @pytest.mark.parametrize("B,past,L", [(1, 0, 1), (2, 0, 9), (1, 0, 64), (2, 0, 200), (1, 37, 100), (3, 5, 65), (1, 0, 1000)])
 @pytest.mark.parametrize("causal", [True, False])
