@@ -13,7 +13,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libdli_b200.so")
+# DLI_LIB selects another build of the same sources (the DLI_TRACE=1 timeline build used by tests/exp_trace.py)
+LIB_PATH = os.environ.get("DLI_LIB") or os.path.join(_HERE, "csrc", "libdli_b200.so")
 
 DLI_OK = 0
 EPI_STORE_F32, EPI_ADD_F32, EPI_STORE_BF16, EPI_SILU_MUL_BF16 = 0, 1, 2, 3

@@ -214,7 +214,7 @@ template <int HD, int G>
 __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const __nv_bfloat16* __restrict__ q, KvView kv,
                                                                          float* __restrict__ scratch,
                                                                          __nv_bfloat16* __restrict__ out, int H, int KV,
-                                                                         float scale_log2) {
+                                                                         float scale_log2, int early_kv) {
   constexpr int LPT = HD / 8;                   // lanes per token
   constexpr int GPW = 32 / LPT;                 // token groups per warp
   constexpr int NG = (DEC_THREADS / 32) * GPW;  // token groups per CTA
@@ -240,10 +240,16 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
   }
   __syncthreads();
   pdl_trigger();
-  pdl_wait();
+  if (threadIdx.x == 0) DLI_TRACE_EV(TR_ATTN, 0);
+  // With early_kv the producer warp starts streaming before the dependency wait: sequence lengths, the block table
+  // and the pages of every token but this step's own (position T - 1, which the preceding RoPE/append kernel is
+  // writing) date from before the current chain of launches.  Everyone else waits here.
+  const bool producer = warp == DEC_THREADS / 32;
+  if (!(producer && early_kv)) pdl_wait();
+  if (threadIdx.x == 0) DLI_TRACE_EV(TR_ATTN, 1);
 
   const int split = blockIdx.x, n_splits = gridDim.x, kvh = blockIdx.y, b = blockIdx.z;
-  const int T = kv.seq_lens[b] + 1;  // the step's own token is already appended
+  const int T = kv.seq_lens[b] + 1;  // the step's own token is (being) appended at position T - 1
   int chunk = (T + n_splits - 1) / n_splits;
   chunk = (chunk + DEC_STAGE_TOK - 1) & ~(DEC_STAGE_TOK - 1);
   const int t_begin = split * chunk;
@@ -265,6 +271,7 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
     // ===== producer warp: lane i copies the i-th page piece of the stage =====
     const int32_t* bt = kv.block_table + (long long)b * kv.max_pages;
     const int pt = kv.page_tokens;
+    bool waited = !early_kv;
     for (int i = 0; i < n_stages; ++i) {
       const int slot = i % DEC_STAGES;
       const int s0 = t_begin + i * DEC_STAGE_TOK, s1 = min(t_end, s0 + DEC_STAGE_TOK);
@@ -272,6 +279,10 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
       // pieces beyond the 32nd (page_tokens == 1 is the only way to get there) are taken in a second pass
       int page = -1;
       if (p0 + lane <= p1) page = bt[p0 + lane];
+      if (!waited && s1 >= T) {  // this stage holds the step's own token: not before the append kernel is done
+        pdl_wait();
+        waited = true;
+      }
       if (i >= DEC_STAGES) mbar_wait(empty0 + 8 * slot, ((uint32_t)(i / DEC_STAGES) - 1) & 1);
       if (lane == 0) mbar_expect_tx(full0 + 8 * slot, (uint32_t)(s1 - s0) * ROW * 2);
       __syncwarp();
@@ -284,6 +295,7 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
         bulk_load_1d(dst + KPART, kv.v + off, bytes, full0 + 8 * slot);
       }
     }
+    if (!waited) pdl_wait();  // this warp also stores results below
   } else {
     float qf[G][8];
 #pragma unroll
@@ -391,6 +403,7 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
       if (d == 0) { dst[HD] = M; dst[HD + 1] = L; }
     }
   }
+  if (threadIdx.x == 0) DLI_TRACE_EV(TR_ATTN, 2);
 }
 
 template <int HD>
@@ -413,7 +426,7 @@ __global__ void __launch_bounds__(HD) decode_combine_kernel(const float* __restr
 
 template <int HD, int G>
 static int launch_dec(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV, int splits,
-                      float* scratch, cudaStream_t st) {
+                      float* scratch, bool early_kv, cudaStream_t st) {
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
   static const bool direct = getenv("DLI_DEC_DIRECT") != nullptr;  // A/B switch for the register-staged kernel
   int rc;
@@ -428,7 +441,8 @@ static int launch_dec(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& 
       attr_set = true;
     }
     rc = launch_kernel("decode_attn_kernel", decode_attn_kernel<HD, G>, dim3(splits, KV, batch),
-                       dim3(DEC_THREADS_STAGED), dec_smem_bytes<HD, G>(), st, q, kv, scratch, out, H, KV, scale_log2);
+                       dim3(DEC_THREADS_STAGED), dec_smem_bytes<HD, G>(), st, q, kv, scratch, out, H, KV, scale_log2,
+                       early_kv ? 1 : 0);
   }
   if (rc || splits == 1) return rc;
   return launch_kernel("decode_combine_kernel", decode_combine_kernel<HD>, dim3(H, batch), dim3(HD), 0, st,
@@ -436,7 +450,7 @@ static int launch_dec(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& 
 }
 
 int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV, int hd,
-                            float* scratch, size_t scratch_bytes, cudaStream_t st) {
+                            float* scratch, size_t scratch_bytes, cudaStream_t st, bool early_kv) {
   DLI_REQUIRE(q && out && scratch, "dli_decode_attention: null pointer");
   DLI_REQUIRE(batch > 0 && H > 0 && KV > 0 && H % KV == 0, "dli_decode_attention: batch=%d H=%d KV=%d", batch, H, KV);
   const int G = H / KV;
@@ -445,7 +459,7 @@ int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const Kv
   if (scratch_bytes < need)
     return fail(DLI_ERR_WORKSPACE, "dli_decode_attention: scratch %zu bytes < %zu needed", scratch_bytes, need);
   if (decode_attn_gqa_supported(kv, G, hd)) {  // grouped-query models: tensor-core kernel (attn_decode_gqa.cu)
-    int rc = launch_decode_attention_gqa(q, out, kv, batch, H, KV, hd, splits, scratch, st);
+    int rc = launch_decode_attention_gqa(q, out, kv, batch, H, KV, hd, splits, scratch, early_kv, st);
     if (rc || splits == 1) return rc;
     if (hd == 128)
       return launch_kernel("decode_combine_kernel", decode_combine_kernel<128>, dim3(H, batch), dim3(128), 0, st,
@@ -454,7 +468,7 @@ int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const Kv
                          (const float*)scratch, out, H, splits);
   }
 #define DLI_DEC_CASE(HD_, G_) \
-  if (hd == HD_ && G == G_) return launch_dec<HD_, G_>(q, out, kv, batch, H, KV, splits, scratch, st)
+  if (hd == HD_ && G == G_) return launch_dec<HD_, G_>(q, out, kv, batch, H, KV, splits, scratch, early_kv, st)
   DLI_DEC_CASE(128, 1); DLI_DEC_CASE(128, 2); DLI_DEC_CASE(128, 4); DLI_DEC_CASE(128, 8);
   DLI_DEC_CASE(64, 1); DLI_DEC_CASE(64, 2); DLI_DEC_CASE(64, 4); DLI_DEC_CASE(64, 8);
 #undef DLI_DEC_CASE
@@ -494,6 +508,8 @@ static int static_scratch_for_current_device(float** out) {
   *out = g_decode_scratch_addr[dev];
   return DLI_OK;
 }
+
+DLI_TRACE_SETTER(trace_set_attn)
 
 }  // namespace dli
 

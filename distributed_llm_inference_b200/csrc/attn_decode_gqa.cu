@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
                                                                      const __nv_bfloat16* __restrict__ q, KvView kv,
                                                                      float* __restrict__ scratch,
                                                                      __nv_bfloat16* __restrict__ out, int H, int KV,
-                                                                     float scale_log2) {
+                                                                     float scale_log2, int early_kv) {
   static_assert(G <= 8, "one m16 tile holds at most 8 real heads in its lower half");
   constexpr int HALVES = HD / 64;
   constexpr int HALF_BYTES = GQ_STAGE_TOK * 128;
@@ -75,10 +75,14 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
   }
   __syncthreads();
   pdl_trigger();
-  pdl_wait();
+  if (threadIdx.x == 0) DLI_TRACE_EV(TR_ATTN_GQA, 0);
+  // early_kv (see common.cuh): the producer warp streams the pages of past tokens before the dependency wait
+  const bool producer = warp == GQ_WARPS;
+  if (!(producer && early_kv)) pdl_wait();
+  if (threadIdx.x == 0) DLI_TRACE_EV(TR_ATTN_GQA, 1);
 
   const int split = blockIdx.x, n_splits = gridDim.x, kvh = blockIdx.y, b = blockIdx.z;
-  const int T = kv.seq_lens[b] + 1;  // the step's own token is already appended
+  const int T = kv.seq_lens[b] + 1;  // the step's own token is (being) appended at position T - 1
   int chunk = (T + n_splits - 1) / n_splits;
   chunk = (chunk + GQ_STAGE_TOK - 1) & ~(GQ_STAGE_TOK - 1);
   const int t_begin = split * chunk;
@@ -95,12 +99,17 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
     // ===== producer warp: lane i pulls the i-th page of the stage (K and V, hd / 64 boxes each) =====
     const int32_t* bt = kv.block_table + (long long)b * kv.max_pages;
     const int pt = kv.page_tokens;
+    bool waited = !early_kv;
     for (int i = 0; i < n_stages; ++i) {
       const int slot = i % GQ_STAGES;
       const int s0 = t_begin + i * GQ_STAGE_TOK, s1 = min(t_end, s0 + GQ_STAGE_TOK);
       const int n_pages = (s1 - s0 + pt - 1) / pt;  // only pages that hold a token of this split are touched
       int page = -1;
       if (lane < n_pages) page = bt[s0 / pt + lane];
+      if (!waited && s1 >= T) {  // this stage holds the step's own token: not before the append kernel is done
+        pdl_wait();
+        waited = true;
+      }
       if (i >= GQ_STAGES) mbar_wait(empty0 + 8 * slot, ((uint32_t)(i / GQ_STAGES) - 1) & 1);
       if (lane == 0) mbar_expect_tx(full0 + 8 * slot, (uint32_t)n_pages * pt * HD * 2 * 2);
       __syncwarp();
@@ -114,6 +123,7 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
         }
       }
     }
+    if (!waited) pdl_wait();  // this warp also stores results below
   } else {
     // Q fragments of the group: rows r < G are real heads, the rest of the m16 tile is zero
     uint32_t qa[KS][2];
@@ -239,6 +249,7 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
       if (d == 0) { dst[HD] = M; dst[HD + 1] = L; }
     }
   }
+  if (threadIdx.x == 0) DLI_TRACE_EV(TR_ATTN_GQA, 2);
 }
 
 bool decode_attn_gqa_supported(const KvView& kv, int G, int hd) {
@@ -251,7 +262,8 @@ bool decode_attn_gqa_supported(const KvView& kv, int G, int hd) {
 
 template <int HD, int G>
 static int launch_gqa(const CUtensorMap& tk, const CUtensorMap& tv, const __nv_bfloat16* q, __nv_bfloat16* out,
-                      const KvView& kv, int batch, int H, int KV, int splits, float* scratch, cudaStream_t st) {
+                      const KvView& kv, int batch, int H, int KV, int splits, float* scratch, bool early_kv,
+                      cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
     DLI_CUDA_OK(cudaFuncSetAttribute(decode_attn_gqa_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -260,12 +272,12 @@ static int launch_gqa(const CUtensorMap& tk, const CUtensorMap& tv, const __nv_b
   }
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
   return launch_kernel("decode_attn_gqa_kernel", decode_attn_gqa_kernel<HD, G>, dim3(splits, KV, batch), dim3(GQ_THREADS),
-                       (size_t)gq_smem_bytes<HD, G>(), st, tk, tv, q, kv, scratch, out, H, KV, scale_log2);
+                       (size_t)gq_smem_bytes<HD, G>(), st, tk, tv, q, kv, scratch, out, H, KV, scale_log2, early_kv ? 1 : 0);
 }
 
 // Launches the main kernel only; the caller runs the shared combine kernel when splits > 1.
 int launch_decode_attention_gqa(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV,
-                                int hd, int splits, float* scratch, cudaStream_t st) {
+                                int hd, int splits, float* scratch, bool early_kv, cudaStream_t st) {
   const int G = H / KV;
   CUtensorMap tk, tv;
   const long long pool_rows = (long long)kv.n_pages * KV * kv.page_tokens;
@@ -273,11 +285,13 @@ int launch_decode_attention_gqa(const __nv_bfloat16* q, __nv_bfloat16* out, cons
   if (rc) return rc;
   if ((rc = make_tmap_bf16(&tv, kv.v, pool_rows, hd, hd, kv.page_tokens))) return rc;
 #define DLI_GQA_CASE(HD_, G_) \
-  if (hd == HD_ && G == G_) return launch_gqa<HD_, G_>(tk, tv, q, out, kv, batch, H, KV, splits, scratch, st)
+  if (hd == HD_ && G == G_) return launch_gqa<HD_, G_>(tk, tv, q, out, kv, batch, H, KV, splits, scratch, early_kv, st)
   DLI_GQA_CASE(128, 2); DLI_GQA_CASE(128, 4); DLI_GQA_CASE(128, 8);
   DLI_GQA_CASE(64, 2); DLI_GQA_CASE(64, 4); DLI_GQA_CASE(64, 8);
 #undef DLI_GQA_CASE
   return fail(DLI_ERR_UNSUPPORTED, "dli_decode_attention: GQA kernel not instantiated for head_dim %d group %d", hd, G);
 }
+
+DLI_TRACE_SETTER(trace_set_attn_gqa)
 
 }  // namespace dli

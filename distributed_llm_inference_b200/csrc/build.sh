@@ -4,14 +4,21 @@ set -euo pipefail
 cd "$(dirname "$0")"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xptxas -v"
-mkdir -p build
+OUT=libdli_b200.so
+BUILD=build
+if [ "${DLI_TRACE:-0}" = "1" ]; then  # timeline build for tests/exp_trace.py; never the product library
+  FLAGS="$FLAGS -DDLI_TRACE"
+  OUT=libdli_b200_trace.so
+  BUILD=build_trace
+fi
+mkdir -p $BUILD
 pids=()
 for f in gemm_tcgen05 norm_rope attn_decode attn_decode_gqa attn_prefill attn_prefill_tc span; do
-  if [ ! -f build/$f.o ] || [ $f.cu -nt build/$f.o ] || [ common.cuh -nt build/$f.o ] || [ tc_ptx.cuh -nt build/$f.o ] || [ mma_sync.cuh -nt build/$f.o ] || [ ../../include/dli_b200.h -nt build/$f.o ]; then
-    ( $NVCC $FLAGS -c $f.cu -o build/$f.o > build/$f.log 2>&1 || { cat build/$f.log; exit 1; } ) &
+  if [ ! -f $BUILD/$f.o ] || [ $f.cu -nt $BUILD/$f.o ] || [ common.cuh -nt $BUILD/$f.o ] || [ tc_ptx.cuh -nt $BUILD/$f.o ] || [ mma_sync.cuh -nt $BUILD/$f.o ] || [ ../../include/dli_b200.h -nt $BUILD/$f.o ]; then
+    ( $NVCC $FLAGS -c $f.cu -o $BUILD/$f.o > $BUILD/$f.log 2>&1 || { cat $BUILD/$f.log; exit 1; } ) &
     pids+=($!)
   fi
 done
 for p in "${pids[@]:-}"; do [ -n "$p" ] && wait $p; done
-$NVCC -shared -gencode arch=compute_100a,code=sm_100a -o libdli_b200.so build/*.o
-echo "built $(pwd)/libdli_b200.so"
+$NVCC -shared -gencode arch=compute_100a,code=sm_100a -o $OUT $BUILD/*.o
+echo "built $(pwd)/$OUT"

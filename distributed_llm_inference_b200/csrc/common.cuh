@@ -40,6 +40,12 @@ void reset_launch_count();
 
 int sm_count();  // SMs of the current device (cached)
 bool pdl_enabled();  // programmatic dependent launch for the span's kernel chain (DLI_NO_PDL=1 turns it off)
+// The next launch_kernel() of this thread is launched WITHOUT the attribute, i.e. it starts only when everything
+// before it in the stream has completed.  dli_span_forward does this for its first kernel, which bounds how far
+// back a pre-wait prologue can overlap: nothing launched before the current forward call is still running when
+// any of the call's kernels executes, so prologues may read what earlier calls wrote (the KV pages of past tokens).
+void pdl_barrier_next_launch();
+bool pdl_take_barrier();
 
 // Launch with the programmatic-stream-serialization attribute: the kernel may begin (prologue, weight prefetch)
 // while its predecessor in the stream is still running; it must execute pdl_wait() before touching anything the
@@ -56,7 +62,7 @@ int launch_kernel(const char* name, void (*kern)(KArgs...), dim3 grid, dim3 bloc
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cfg.numAttrs = (pdl_enabled() && !pdl_take_barrier()) ? 1 : 0;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
   if (e != cudaSuccess) return fail(DLI_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(e));
   count_launch();
@@ -111,9 +117,12 @@ int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t s
 size_t decode_attn_scratch_bytes(int batch, int H, int hd, int max_ctx);
 bool decode_attn_gqa_supported(const KvView& kv, int G, int hd);
 int launch_decode_attention_gqa(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV,
-                                int hd, int splits, float* scratch, cudaStream_t st);
+                                int hd, int splits, float* scratch, bool early_kv, cudaStream_t st);
+// early_kv: the K/V pages of every token but the step's own were written before the current chain of launches began
+// (see pdl_barrier_next_launch), so the kernel may stream them before its dependency wait.  The span runner says yes;
+// the op-level ABI, which knows nothing about its caller's stream, says no.
 int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV,
-                            int hd, float* scratch, size_t scratch_bytes, cudaStream_t st);
+                            int hd, float* scratch, size_t scratch_bytes, cudaStream_t st, bool early_kv = false);
 bool prefill_attn_tc_supported(const KvView& kv, int hd);
 int launch_prefill_attention_tc(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H,
                                 int KV, bool causal, cudaStream_t st);
@@ -126,6 +135,36 @@ int launch_prefill_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const K
 // visible / let the next kernel of the stream start its prologue.  Both are no-ops without the launch attribute.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// ---- in-kernel timeline (only in builds made with DLI_TRACE=1 build.sh; see tests/exp_trace.py) ------------
+// Every CTA stamps %globaltimer at kernel entry (phase 0), when griddepcontrol.wait returns (1) and at exit (2)
+// into a host-provided buffer: word 0 = event counter, word 1 = capacity, then (tag, time) pairs.
+#ifdef DLI_TRACE
+static __device__ unsigned long long* g_trace_buf = nullptr;
+__device__ __forceinline__ void trace_ev(int kid, int phase) {
+  unsigned long long* t = g_trace_buf;
+  if (!t) return;
+  unsigned long long now;
+  unsigned smid;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+  asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+  const unsigned long long i = atomicAdd(t, 1ull);
+  if (i >= t[1]) return;
+  const unsigned cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+  t[2 + 2 * i] = ((unsigned long long)kid << 56) | ((unsigned long long)phase << 52) | ((unsigned long long)smid << 32) | cta;
+  t[3 + 2 * i] = now;
+}
+#define DLI_TRACE_EV(kid, phase) trace_ev(kid, phase)
+#define DLI_TRACE_SETTER(name)                                                       \
+  int name(void* buf) {                                                              \
+    unsigned long long* p = static_cast<unsigned long long*>(buf);                   \
+    return cudaMemcpyToSymbol(g_trace_buf, &p, sizeof(p)) == cudaSuccess ? 0 : 1;    \
+  }
+#else
+#define DLI_TRACE_EV(kid, phase) ((void)0)
+#define DLI_TRACE_SETTER(name)
+#endif
+enum { TR_GEMM = 1, TR_RMSNORM = 2, TR_ROPE = 3, TR_ATTN = 4, TR_COMBINE = 5, TR_CAST = 6, TR_ATTN_GQA = 7 };
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

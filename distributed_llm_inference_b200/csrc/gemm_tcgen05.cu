@@ -222,6 +222,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
 
   pdl_trigger();  // the next kernel of the stream may start its own prologue / weight prefetch
   if (threadIdx.x == 0) {
+    DLI_TRACE_EV(TR_GEMM + 16 * EPI, 0);
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
     for (int s = 0; s < stages; ++s) {
@@ -276,6 +277,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
         }
         __syncwarp();
         pdl_wait();
+        if (lane == 0) DLI_TRACE_EV(TR_GEMM + 16 * EPI, 1);
         if (elect_one()) {
           for (int i = 0; i < n_pre; ++i) load_acts(i, kb0 + i);
         }
@@ -398,6 +400,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
 
   tcgen05_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) DLI_TRACE_EV(TR_GEMM + 16 * EPI, 2);
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TMEM_COLS) : "memory");
   }
@@ -787,5 +790,7 @@ int launch_gemm(const void* x, long long ldx, const void* w, void* out, long lon
   if (rc) return rc;
   return launch_gemm_planned(g, tx, tw, out, ldo, m, n, epi, st);
 }
+
+DLI_TRACE_SETTER(trace_set_gemm)
 
 }  // namespace dli

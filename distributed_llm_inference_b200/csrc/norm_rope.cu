@@ -26,19 +26,83 @@ __device__ __forceinline__ void load8(const void* x, long long i, float (&v)[8])
   }
 }
 
+// One CTA per row.  Rows of up to NORM_THREADS * 8 * NORM_CHUNKS (8192) elements are read ONCE and kept in
+// registers; the norm weights do not depend on the previous kernel, so they are fetched before the dependency
+// wait and the chain after it is a single load, one block reduction and the store.  (At decode this kernel is
+// pure latency between two weight-streaming GEMMs: every microsecond here is one the next GEMM's prefetched
+// ring cannot cover.)  Wider rows take the two-pass path.
+constexpr int NORM_CHUNKS = 4;
+
 template <bool F32IN>
 __global__ void __launch_bounds__(NORM_THREADS) rmsnorm_kernel(const void* __restrict__ x, const __nv_bfloat16* __restrict__ w,
                                                                __nv_bfloat16* __restrict__ y, float* __restrict__ resid_out,
                                                                __nv_bfloat16* __restrict__ copy_out, int h, float eps,
                                                                float s) {
   __shared__ float red[NORM_THREADS / 32];
-  __shared__ float rinv;
   pdl_trigger();
-  pdl_wait();
+  if (threadIdx.x == 0) DLI_TRACE_EV(TR_RMSNORM, 0);
   const long long base = (long long)blockIdx.x * h;
+  const int i0 = threadIdx.x * 8;
+  if (h <= NORM_THREADS * 8 * NORM_CHUNKS) {
+    uint4 wv[NORM_CHUNKS];
+    float v[NORM_CHUNKS][8];
+#pragma unroll
+    for (int c = 0; c < NORM_CHUNKS; ++c) {
+      const int i = i0 + c * NORM_THREADS * 8;
+      if (i < h) wv[c] = *reinterpret_cast<const uint4*>(w + i);
+    }
+    pdl_wait();
+    if (threadIdx.x == 0) DLI_TRACE_EV(TR_RMSNORM, 1);
+    float ss = 0.f;
+#pragma unroll
+    for (int c = 0; c < NORM_CHUNKS; ++c) {
+      const int i = i0 + c * NORM_THREADS * 8;
+      if (i < h) load8<F32IN>(x, base + i, v[c]);
+    }
+#pragma unroll
+    for (int c = 0; c < NORM_CHUNKS; ++c) {
+      const int i = i0 + c * NORM_THREADS * 8;
+      if (i < h) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ss += v[c][j] * v[c][j];
+        if (resid_out) {
+          *reinterpret_cast<float4*>(resid_out + base + i) = make_float4(v[c][0], v[c][1], v[c][2], v[c][3]);
+          *reinterpret_cast<float4*>(resid_out + base + i + 4) = make_float4(v[c][4], v[c][5], v[c][6], v[c][7]);
+        }
+        if (copy_out) {
+          *reinterpret_cast<uint4*>(copy_out + base + i) = make_uint4(pack_bf16(v[c][0], v[c][1]), pack_bf16(v[c][2], v[c][3]),
+                                                                      pack_bf16(v[c][4], v[c][5]), pack_bf16(v[c][6], v[c][7]));
+        }
+      }
+    }
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < NORM_THREADS / 32; ++k) t += red[k];  // same order in every thread: one value per row
+    const float r = rsqrtf(t * s * s / (float)h + eps) * s;
+#pragma unroll
+    for (int c = 0; c < NORM_CHUNKS; ++c) {
+      const int i = i0 + c * NORM_THREADS * 8;
+      if (i < h) {
+        const float g[8] = {bf16_lo(wv[c].x), bf16_hi(wv[c].x), bf16_lo(wv[c].y), bf16_hi(wv[c].y),
+                            bf16_lo(wv[c].z), bf16_hi(wv[c].z), bf16_lo(wv[c].w), bf16_hi(wv[c].w)};
+        uint32_t o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) o[j] = pack_bf16(g[2 * j] * (v[c][2 * j] * r), g[2 * j + 1] * (v[c][2 * j + 1] * r));
+        *reinterpret_cast<uint4*>(y + base + i) = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+    }
+    if (threadIdx.x == 0) DLI_TRACE_EV(TR_RMSNORM, 2);
+    return;
+  }
+  // ---- wide rows: two passes (the second one hits L1/L2)
+  __shared__ float rinv;
+  pdl_wait();
   float ss = 0.f;
   float v[8];
-  for (int i = threadIdx.x * 8; i < h; i += NORM_THREADS * 8) {
+  for (int i = i0; i < h; i += NORM_THREADS * 8) {
     load8<F32IN>(x, base + i, v);
 #pragma unroll
     for (int j = 0; j < 8; ++j) ss += v[j] * v[j];
@@ -61,8 +125,8 @@ __global__ void __launch_bounds__(NORM_THREADS) rmsnorm_kernel(const void* __res
   }
   __syncthreads();
   const float r = rinv * s;
-  for (int i = threadIdx.x * 8; i < h; i += NORM_THREADS * 8) {
-    load8<F32IN>(x, base + i, v);  // second pass hits L1/L2
+  for (int i = i0; i < h; i += NORM_THREADS * 8) {
+    load8<F32IN>(x, base + i, v);
     const uint4 wv = *reinterpret_cast<const uint4*>(w + i);
     const float g[8] = {bf16_lo(wv.x), bf16_hi(wv.x), bf16_lo(wv.y), bf16_hi(wv.y),
                         bf16_lo(wv.z), bf16_hi(wv.z), bf16_lo(wv.w), bf16_hi(wv.w)};
@@ -94,15 +158,19 @@ __global__ void __launch_bounds__(ROPE_THREADS) rope_kv_append_kernel(float* __r
                                                                       __nv_bfloat16* __restrict__ q_out, KvView kv,
                                                                       int q_len, int H, int KV, int hd) {
   pdl_trigger();
-  pdl_wait();
+  if (threadIdx.x == 0) DLI_TRACE_EV(TR_ROPE, 0);
   const int t = blockIdx.x;
   const int b = t / q_len, l = t - b * q_len;
   const int half = hd >> 1;
   const int n_all = (H + 2 * KV) * hd;
   float* row = qkv + (long long)t * n_all;
+  // sequence lengths and the block table are host-side state of the cache, never written by a kernel of the
+  // chain this launch belongs to: look the destination slot up while the projection GEMM is still running
   const int pos = kv.seq_lens[b] + l;
   const int page = kv.block_table[(long long)b * kv.max_pages + pos / kv.page_tokens];
   const int slot = pos % kv.page_tokens;
+  pdl_wait();
+  if (threadIdx.x == 0) DLI_TRACE_EV(TR_ROPE, 1);
   const float* cs = cosT + (long long)l * hd;
   const float* sn = sinT + (long long)l * hd;
 
@@ -139,6 +207,7 @@ __global__ void __launch_bounds__(ROPE_THREADS) rope_kv_append_kernel(float* __r
     *reinterpret_cast<uint2*>(dst) = make_uint2(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w));
     if (zero_after) *reinterpret_cast<float4*>(vrow + e) = make_float4(0.f, 0.f, 0.f, 0.f);
   }
+  if (threadIdx.x == 0) DLI_TRACE_EV(TR_ROPE, 2);
 }
 
 int launch_rope_kv_append(float* qkv, bool zero_after, const float* cos, const float* sin, __nv_bfloat16* q_out,
@@ -291,5 +360,7 @@ int launch_kv_evict(const dli_kv_desc* kv, int n_layers, int batch, int KV, int 
                        (long long)(kv->layer_stride_bytes / 2), v.block_table, v.max_pages, v.page_tokens, KV, hd, cur_len,
                        window, sinks, n_new, cos_hist, sin_hist);
 }
+
+DLI_TRACE_SETTER(trace_set_norm)
 
 }  // namespace dli
