@@ -97,6 +97,7 @@ struct GemmPlan {
   int a_box_rows, b_box_rows;  // TMA box rows of the A-role / B-role operand
   int k_blocks, kb_per_split, splits, stages;
   int grid_x, grid_y;
+  bool pair;          // prefill only: CTA-pair kernel (cta_group::2), B box = 128 rows per CTA
 };
 GemmPlan plan_gemm(int m, int n, int k, int epilogue);
 int make_tmap_bf16(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld, int box_rows);

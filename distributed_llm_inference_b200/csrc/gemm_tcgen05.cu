@@ -555,6 +555,193 @@ gemm_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const 
 }
 
 
+// ---- CTA-pair persistent kernel (prefill, cta_group::2) ----------------------------------------------------
+// The same persistent, double-buffered-accumulator structure as above, but two CTAs on the SMs of one TPC work on
+// ONE 256-token x 256-feature tile: each CTA stages its own 128 token rows of A and only HALF of the B tile (128
+// feature rows); `tcgen05.mma.cta_group::2` (M = 256), issued by the leader CTA alone, feeds both tensor cores from
+// both halves.  Per k-block a CTA now moves 32 KB through TMA and shared memory instead of 48 KB, which is what the
+// single-CTA kernel was short of (ncu: tensor pipe 81-83 % active with the operand ring never empty).
+//   barriers  full[s]   leader only: 1 arrival (expect_tx of both CTAs' bytes) + the tx of both CTAs' TMA loads
+//             empty[s]  in both CTAs: arrival by the leader's multicast tcgen05.commit
+//             tfull[a]  in both CTAs: arrival by the leader's multicast commit after a tile's last k-block
+//             tempty[a] leader only: 8 arrivals = the 4 epilogue warps of each CTA (the peer's arrive remotely)
+// For the fused silu(gate)*up epilogue the pair's B halves are the gate rows (rank 0) and the up rows (rank 1) of
+// the same 128 features, so the accumulator columns are [gate | up] exactly as in the single-CTA kernel.
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+// TMA load into this CTA's shared memory whose completion bytes are counted on a barrier of the pair's leader
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, uint32_t bar_cluster, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar_cluster), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {  // arrives on `bar` of BOTH CTAs of the pair
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+               "h"((uint16_t)3)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster) : "memory");
+}
+
+constexpr int PAIR_BN = 256;       // accumulator columns per CTA (features of the pair's tile)
+constexpr int PAIR_B_ROWS = 128;   // B rows each CTA stages
+constexpr int PAIR_STAGE_BYTES = A_TILE_BYTES + PAIR_B_ROWS * BK * 2;  // 32 KB
+
+template <int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                         const GemmParams p, const int tiles_m, const int tiles_n, const int group_m) {
+  constexpr int BN = PAIR_BN;
+  constexpr int TMEM_COLS = 2 * BN;
+  constexpr int N_PER_TILE = EPI == DLI_EPI_SILU_MUL_BF16 ? BN / 2 : BN;
+  const int n_tiles = tiles_m * tiles_n;
+
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t bars[2 * MAX_STAGES + 4];
+  __shared__ uint32_t tmem_base_slot;
+
+  const uint32_t tiles = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int stages = p.stages;
+  const uint32_t full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[MAX_STAGES]);
+  const uint32_t tfull0 = smem_u32(&bars[2 * MAX_STAGES]), tempty0 = smem_u32(&bars[2 * MAX_STAGES + 2]);
+  const int n_kb = p.k_blocks;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+  const uint32_t full0_leader = mapa_rank(full0, 0), tempty0_leader = mapa_rank(tempty0, 0);
+
+  pdl_trigger();
+  if (threadIdx.x == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull0 + 8 * a, 1);
+      mbar_init(tempty0 + 8 * a, 8);  // 4 epilogue warps of each CTA
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {  // the same warp of both CTAs allocates the pair's accumulator columns
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)),
+                 "r"((uint32_t)TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  cluster_sync_all();  // barriers of both CTAs exist before anyone signals them
+  tcgen05_fence_after();
+  const uint32_t tmem_d = tmem_base_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer of this CTA: its 128 token rows of A and its half of B =====
+    int s = 0;
+    uint32_t ph = 0;
+    bool waited = false;
+    for (int t = pair; t < n_tiles; t += n_pairs) {
+      int mt, nt;
+      tile_coords(t, tiles_m, tiles_n, group_m, mt, nt);
+      const int a_row0 = mt * 2 * BM + (int)rank * BM;
+      const int b_row0 = EPI == DLI_EPI_SILU_MUL_BF16 ? nt * N_PER_TILE + (int)rank * p.up_row_offset
+                                                      : nt * N_PER_TILE + (int)rank * PAIR_B_ROWS;
+      for (int kb = 0; kb < n_kb; ++kb) {
+        mbar_wait(empty0 + 8 * s, ph ^ 1);
+        const uint32_t a_dst = tiles + s * PAIR_STAGE_BYTES, b_dst = a_dst + A_TILE_BYTES;
+        if (elect_one()) {
+          if (leader) mbar_expect_tx(full0 + 8 * s, 2 * PAIR_STAGE_BYTES);
+          tma_load_2d_pair(b_dst, &tma_b, full0_leader + 8 * s, kb * BK, b_row0);
+        }
+        __syncwarp();
+        if (!waited) {  // weights do not depend on the previous kernel; activations do
+          pdl_wait();
+          waited = true;
+        }
+        if (elect_one()) tma_load_2d_pair(a_dst, &tma_a, full0_leader + 8 * s, kb * BK, a_row0);
+        __syncwarp();
+        if (++s == stages) { s = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (leader) {
+      // ===== MMA issuer of the pair =====
+      constexpr uint32_t idesc =
+          (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
+      int s = 0, it = 0;
+      uint32_t ph = 0;
+      for (int t = pair; t < n_tiles; t += n_pairs, ++it) {
+        const int acc = it & 1;
+        mbar_wait(tempty0 + 8 * acc, (((uint32_t)it >> 1) & 1) ^ 1);  // both CTAs have drained this accumulator
+        tcgen05_fence_after();
+        const uint32_t d = tmem_d + (uint32_t)(acc * BN);
+        for (int kb = 0; kb < n_kb; ++kb) {
+          mbar_wait(full0 + 8 * s, ph);
+          tcgen05_fence_after();
+          if (elect_one()) {
+            const uint32_t a_src = tiles + s * PAIR_STAGE_BYTES;
+            const uint64_t adesc = umma_desc_sw128(a_src), bdesc = umma_desc_sw128(a_src + A_TILE_BYTES);
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              umma_bf16_pair(d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            umma_commit_pair(empty0 + 8 * s);
+            if (kb + 1 == n_kb) umma_commit_pair(tfull0 + 8 * acc);
+          }
+          __syncwarp();
+          if (++s == stages) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else {  // ===== epilogue warps: this CTA's 128 token rows of the tile =====
+    pdl_wait();
+    const int q = warp & 3;
+    int it = 0;
+    for (int t = pair; t < n_tiles; t += n_pairs, ++it) {
+      const int acc = it & 1;
+      int mt, nt;
+      tile_coords(t, tiles_m, tiles_n, group_m, mt, nt);
+      const int a_row0 = mt * 2 * BM + (int)rank * BM, b_row0 = nt * N_PER_TILE;
+      mbar_wait(tfull0 + 8 * acc, ((uint32_t)it >> 1) & 1, 100);
+      tcgen05_fence_after();
+      const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+      if constexpr (EPI == DLI_EPI_QKV_ROPE_INTERNAL) epilogue_qkv_rope<BN>(taddr, a_row0 + q * 32 + lane, b_row0, p);
+      else epilogue_token_major<BN, EPI>(taddr, a_row0 + q * 32 + lane, b_row0, p);
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(tempty0_leader + 8 * acc);
+    }
+  }
+
+  tcgen05_fence_before();
+  cluster_sync_all();  // neither CTA leaves (or frees TMEM) while its peer may still read its smem / signal its barriers
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TMEM_COLS) : "memory");
+  }
+}
+
+
 // ---- host side ----------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -626,6 +813,57 @@ static int launch_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const
   if (group_m > tiles_m) group_m = tiles_m;
   return launch_kernel("gemm_tcgen05_persistent_kernel", kern, dim3(grid), dim3(GEMM_THREADS), smem, st, ta, tb, p, tiles_m,
                        tiles_n, group_m);
+}
+
+
+static bool pair_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DLI_NO_PAIR");
+    v = (e && e[0] == '1') ? 0 : 1;
+  }
+  return v == 1;
+}
+
+// CTA-pair kernel: tiles_m counts 256-token tiles; the grid is the largest even number of CTAs <= #SMs
+template <int EPI>
+static int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p_in, int tiles_m, int tiles_n,
+                       cudaStream_t st) {
+  GemmParams p = p_in;
+  p.stages = std::min(6, std::max(2, p.k_blocks));
+  const size_t smem = (size_t)p.stages * PAIR_STAGE_BYTES + 1024;
+  static bool configured = false;
+  auto kern = gemm_tcgen05_pair_kernel<EPI>;
+  if (!configured) {
+    DLI_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+    configured = true;
+  }
+  const int n_tiles = tiles_m * tiles_n;
+  const int pairs = std::min(n_tiles, sm_count() / 2);
+  int group_m = 8;  // bands of 8 x 256 tokens: the same 2048-token activation band as the single-CTA kernel
+  {
+    static int group_env = -1;
+    if (group_env < 0) {
+      const char* e = getenv("DLI_GROUP_M");
+      group_env = e ? atoi(e) : 0;
+    }
+    if (group_env > 0) group_m = std::max(1, group_env / 2);
+  }
+  if (group_m > tiles_m) group_m = tiles_m;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = (pdl_enabled() && !pdl_take_barrier()) ? 1 : 0;  // cluster dims are compiled into the kernel
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, p, tiles_m, tiles_n, group_m);
+  if (e != cudaSuccess) return fail(DLI_ERR_CUDA, "launch of gemm_tcgen05_pair_kernel failed: %s", cudaGetErrorString(e));
+  count_launch();
+  return DLI_OK;
 }
 
 template <int BN>
@@ -707,6 +945,10 @@ GemmPlan plan_gemm(int m, int n, int k, int epilogue) {
       g.grid_y = (n + g.bn - 1) / g.bn;
     }
     g.a_box_rows = BM;
+    // CTA pairs (cta_group::2): each CTA stages 128 weight rows of a 256-column tile (gate rows / up rows for SILU)
+    g.pair = persistent_enabled() && pair_enabled() && m >= 2 * BM &&
+             (epilogue == DLI_EPI_SILU_MUL_BF16 ? n % 128 == 0 : (g.bn == 256 && n % 256 == 0));
+    if (g.pair) g.b_box_rows = 128;
     g.grid_x = tm;
     g.splits = 1;
     g.kb_per_split = g.k_blocks;
@@ -749,6 +991,17 @@ int launch_gemm_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const CUte
       case 32: return launch_epi<32, true>(epilogue, tmap_w, tmap_x, p, grid, st);
       case 64: return launch_epi<64, true>(epilogue, tmap_w, tmap_x, p, grid, st);
       default: return launch_epi<128, true>(epilogue, tmap_w, tmap_x, p, grid, st);
+    }
+  }
+  if (persistent_enabled() && g.pair) {  // prefill, CTA pairs: 256-token x 256-feature tiles, B halves shared
+    const int tm2 = (m + 2 * BM - 1) / (2 * BM);
+    switch (epilogue) {
+      case DLI_EPI_QKV_ROPE_INTERNAL: return launch_pair<DLI_EPI_QKV_ROPE_INTERNAL>(tmap_x, tmap_w, p, tm2, g.grid_y, st);
+      case DLI_EPI_SILU_MUL_BF16: return launch_pair<DLI_EPI_SILU_MUL_BF16>(tmap_x, tmap_w, p, tm2, g.grid_y, st);
+      case DLI_EPI_STORE_F32: return launch_pair<DLI_EPI_STORE_F32>(tmap_x, tmap_w, p, tm2, g.grid_y, st);
+      case DLI_EPI_ADD_F32: return launch_pair<DLI_EPI_ADD_F32>(tmap_x, tmap_w, p, tm2, g.grid_y, st);
+      case DLI_EPI_STORE_BF16: return launch_pair<DLI_EPI_STORE_BF16>(tmap_x, tmap_w, p, tm2, g.grid_y, st);
+      default: return fail(DLI_ERR_ARG, "unknown epilogue %d", epilogue);
     }
   }
   if (persistent_enabled()) {  // prefill: persistent CTAs, double-buffered TMEM accumulators

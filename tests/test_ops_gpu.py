@@ -40,6 +40,8 @@ GEMM_SHAPES = [
     (100, 512, 1408), (128, 384, 512), (16, 4096, 11008), (8, 200, 512),
     # ... and prefill-like (token-major tiles)
     (129, 384, 512), (200, 1024, 768), (512, 2304, 768), (1000, 4096, 1024), (300, 200, 512),
+    # ... enough tiles that every CTA pair of the persistent kernel loops (74 pairs), ragged last token tile
+    (1537, 2560, 1024), (4096, 5120, 512),
 ]
 
 
@@ -63,7 +65,8 @@ def test_gemm(m, n, k, epi):
 
 
 @pytest.mark.parametrize("m,n,k", [(129, 128, 512), (300, 1408, 512), (512, 2048, 768), (1000, 704, 1024),
-                                   (1, 1408, 512), (16, 2048, 768), (100, 704, 1024), (8, 200, 512), (128, 11008, 4096)])
+                                   (1, 1408, 512), (16, 2048, 768), (100, 704, 1024), (8, 200, 512), (128, 11008, 4096),
+                                   (2304, 2816, 512)])
 def test_gemm_silu_mul(m, n, k):
     x = _randn(m, k, seed=6)
     w = _randn(2 * n, k, seed=7, scale=0.05)                                      # gate rows then up rows
