@@ -241,18 +241,35 @@ def run_ours(args):
 
     blk = build_span(shape, layer_ids, dev, max_positions=max(8192, total_ctx + 64))
     cache = PartialLlamaSinkCache(1 << 20, 4, page_tokens=args.page_tokens,
-                                  capacity_tokens=n_mb * BATCH * (total_ctx + 16) + BATCH * 64 + BATCH * (PROMPT + 16))
+                                  capacity_tokens=n_mb * BATCH * (total_ctx + 16) + BATCH * 64 +
+                                  (n_mb if world > 1 else 1) * BATCH * (PROMPT + 16))
     stage = PipelineStage(blk, cache, rank, world, dev)
     gids = [f"mb{m}" for m in range(n_mb)]
 
     # ---- prefill (also timed: prefill tokens/s of the span/pipeline) ----
+    # --prefill-chunk C: every prompt travels as ceil(PROMPT / C) chunks, so that stage s works on chunk c while stage
+    # s + 1 works on chunk c - 1 (config C5: one 8k-token sequence over 4 or 8 stages)
+    chunk = min(args.prefill_chunk or PROMPT, PROMPT)
     prompts = [syn.make_hidden(shape, BATCH, PROMPT, seed=99 + m, device=dev) for m in range(n_mb)]
+    chunks = [(c0, [p[:, c0:c0 + chunk].contiguous() for p in prompts] if rank == 0 else None)
+              for c0 in range(0, PROMPT, chunk)]
+
+    def prefill_round(ids):
+        for c0, ins in chunks:
+            stage.run_round(ids, ins, BATCH, min(chunk, PROMPT - c0), c0, feed_back=False)
+
+    if world > 1:   # untimed pass on throw-away generations: one-time descriptor / workspace / communicator set-up
+        warm_ids = [f"pfw{m}" for m in range(n_mb)]
+        prefill_round(warm_ids)
+        torch.cuda.synchronize()
+        for g in warm_ids:
+            cache.close(g)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    stage.run_round(gids, prompts if rank == 0 else None, BATCH, PROMPT, 0, feed_back=False)
+    prefill_round(gids)
     e1.record()
     torch.cuda.synchronize()
     prefill_ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -403,9 +420,58 @@ def run_ours(args):
                       " per step with pinned-host input copied H2D and output copied D2H, synchronised every step "
                       "(wall clock)"}
 
+    elif graph is not None and stage.handoff == "peer_store":
+        # pipeline: every step, stage 0 copies each micro-batch's input from pinned host memory into the head of the pipe,
+        # the round runs through all stages, the last stage's peer stores land back on stage 0 and are copied to the
+        # host; the next step starts only then (a client needs token t before it can feed token t + 1)
+        stage.drain(n_mb)
+        n_e2e = min(K, 16)
+        g0 = [stage.graphs[g] for g in gids]
+        if rank == 0:
+            hin = [torch.empty(BATCH, 1, shape.hidden_size, dtype=torch.bfloat16).pin_memory() for _ in range(n_mb)]
+            hout = [torch.empty(BATCH, 1, shape.hidden_size, dtype=torch.bfloat16).pin_memory() for _ in range(n_mb)]
+            for m, t in enumerate(hin):
+                t.copy_(syn.make_hidden(shape, BATCH, 1, seed=3 + m))
+        torch.cuda.synchronize()
+        dist.barrier()
+        t0 = time.perf_counter()
+        for k in range(n_e2e):
+            if rank == 0:
+                for m in range(n_mb):
+                    g0[m].x.copy_(hin[m], non_blocking=True)
+                stage.run_round(gids, [g.x for g in g0], BATCH, 1, pos, feed_back=True)
+                stage.drain(n_mb)
+                for m in range(n_mb):
+                    hout[m].copy_(g0[m].x, non_blocking=True)
+                torch.cuda.synchronize()
+            else:
+                stage.run_round(gids, None, BATCH, 1, pos, feed_back=True)
+            pos += 1
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], device=dev)
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        nbytes = n_mb * BATCH * shape.hidden_size * 2
+        e2e = {"value": round(n_mb * BATCH * n_e2e / dt.item(), 1), "unit": UNIT, "h2d_bytes_per_step": nbytes,
+               "d2h_bytes_per_step": nbytes, "steps": n_e2e,
+               "how": f"PipelineStage.run_round over {world} stages, {n_mb} micro-batches per step: pinned-host inputs copied "
+                      "H2D on stage 0, outputs of the last stage copied D2H on stage 0, synchronised every step (wall "
+                      "clock, max over ranks); steps do not overlap, so the pipe fills and drains every step"}
+
     if rank == 0:
         cpu = (cpu_reference_decode(shape, n_total, BATCH, PROMPT, budget_s=args.cpu_budget)
                if (world == 1 and args.cpu_budget > 0) else None)
+        pf_pipe = None
+        if world > 1:   # whole-pipeline prefill: all stages' FLOPs over the max-over-ranks time, against N x the peak
+            h_, i_ = shape.hidden_size, shape.intermediate_size
+            H_, KV_, hd_ = shape.num_attention_heads, shape.num_key_value_heads, shape.head_dim
+            fl = n_mb * n_total * (2 * BATCH * PROMPT * (h_ * H_ * hd_ + 2 * h_ * KV_ * hd_ + H_ * hd_ * h_ + 3 * h_ * i_)
+                                   + BATCH * 2 * PROMPT * PROMPT * H_ * hd_)
+            _, tc_peak_, _ = measured_peaks()
+            pf_ms = prefill_ms.item()
+            pf_pipe = {"ms": round(pf_ms, 3), "chunk_tokens": chunk, "chunks": len(chunks), "sequences": n_mb * BATCH,
+                       "tflops": round(fl / (pf_ms * 1e-3) / 1e12, 1),
+                       "frac_of_n_gpu_peak": round(fl / (pf_ms * 1e-3) / 1e12 / (tc_peak_ * world), 4),
+                       "fill_drain_bound": round(len(chunks) * n_mb / (len(chunks) * n_mb + world - 1), 4)}
         line = {
             "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
@@ -419,7 +485,9 @@ def run_ours(args):
                        "handoff": stage.handoff, "handoff_fallback_reason": stage.handoff_error},
             "p50_ms_per_token": round(lat[len(lat) // 2] / n_mb, 4),
             "prefill_tokens_per_sec": round(n_mb * BATCH * PROMPT / (prefill_ms.item() * 1e-3), 1),
-            "prefill_note": "first call, includes one-time descriptor/workspace set-up", "prefill": prefill,
+            "prefill_note": ("pipelined over the stages in chunks of %d tokens, warm" % chunk) if world > 1 else
+                            "first call, includes one-time descriptor/workspace set-up; the warm figure is in `prefill`",
+            "prefill_pipeline": pf_pipe, "prefill": prefill,
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roofline,
@@ -471,6 +539,7 @@ def main():
     ap.add_argument("--prompt", type=int, default=None, help="prompt length (default 512, the config's)")
     ap.add_argument("--layers", type=int, default=None, help="total layers over all stages (default: the model's)")
     ap.add_argument("--micro-batches", type=int, default=None, help="micro-batches in flight (default: number of stages)")
+    ap.add_argument("--prefill-chunk", type=int, default=None, help="prefill the prompt in chunks of this many tokens")
     ap.add_argument("--nccl-handoff", action="store_true", help="hand off by NCCL isend/irecv instead of peer stores")
     ap.add_argument("--no-graph", action="store_true", help="decode with eager launches instead of the CUDA graph")
     args = ap.parse_args()

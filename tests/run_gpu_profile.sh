@@ -12,10 +12,15 @@ ncu --metrics gpu__time_duration.sum --clock-control none -k "$KN" -s 225 -c 225
 echo "ncu list prefill exit $?"
 ncu --set full --clock-control none --import-source on -k regex:gemm_tcgen05_kernel -s 512 -c 4 -o gpurun_out/prof_gemm_decode $CMD > gpurun_out/ncu_full1.log 2>&1
 echo "ncu gemm decode exit $?"
-ncu --set full --clock-control none --import-source on -k regex:persistent -s 128 -c 4 -o gpurun_out/prof_gemm_prefill $CMD > gpurun_out/ncu_full2.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:pair_kernel -s 128 -c 4 -o gpurun_out/prof_gemm_prefill $CMD > gpurun_out/ncu_full2.log 2>&1
 echo "ncu gemm prefill exit $?"
 ncu --set full --clock-control none --import-source on -k regex:decode_attn_kernel -s 40 -c 1 -o gpurun_out/prof_attn_decode $CMD > gpurun_out/ncu_full3.log 2>&1
 echo "ncu attn decode exit $?"
 ncu --set full --clock-control none --import-source on -k regex:prefill_attn_tc -s 33 -c 1 -o gpurun_out/prof_attn_prefill_tc $CMD > gpurun_out/ncu_full4.log 2>&1
 echo "ncu attn prefill exit $?"
-ls -la gpurun_out | tail -14
+# grouped-query decode attention: one 70B-shaped stage (10 layers), batch 32
+CMD70="python bench.py --steps 2 --warmup 3 --cpu-budget 0 --model 70b --layers 10 --batch 32"
+$CMD70 > gpurun_out/plain70.log 2>&1 || { echo "plain 70b run failed"; tail -5 gpurun_out/plain70.log; exit 1; }
+ncu --set full --clock-control none --import-source on -k regex:decode_attn_gqa -s 25 -c 1 -o gpurun_out/prof_attn_decode_gqa $CMD70 > gpurun_out/ncu_full5.log 2>&1
+echo "ncu attn decode gqa exit $?"
+ls -la gpurun_out | tail -16
