@@ -22,12 +22,28 @@ namespace dli {
 constexpr int DEC_THREADS = 128;
 constexpr int DEC_MAX_SPLITS = 32;
 
-static int decode_splits(int batch, int KV, int max_ctx) {
+// Context splits per (sequence, KV head): as many as keep the whole grid RESIDENT AT ONCE (`slots` = co-resident CTAs
+// of the kernel that will run), never more.  The kernels are HBM-bound and every CTA keeps its own ring of K/V in
+// flight, so one full wave streams at full rate however the work is cut; a second, partly filled wave does not (ncu,
+// 70B B=32: 512 CTAs on 296 slots ran 1.73 waves at 3.2 TB/s), and splits == 1 also spares the combine launch.
+static int decode_splits(int batch, int KV, int max_ctx, int slots) {
   const int by_ctx = (max_ctx + 63) / 64;
-  const int by_fill = (2 * sm_count() + batch * KV - 1) / (batch * KV);
-  int s = by_fill < by_ctx ? by_fill : by_ctx;
+  const int pairs = batch * KV;
+  int s = pairs >= slots ? 1 : slots / pairs;
+  if (s > by_ctx) s = by_ctx;
   if (s > DEC_MAX_SPLITS) s = DEC_MAX_SPLITS;
   return s < 1 ? 1 : s;
+}
+
+// the split count launch_decode_attention will use for this problem (also sizes the static-scratch check)
+static int decode_splits_for(const KvView& kv, int batch, int H, int KV, int hd) {
+  const int G = H / KV;
+  const bool gqa = decode_attn_gqa_supported(kv, G, hd);
+  const bool direct_env = getenv("DLI_DEC_DIRECT") != nullptr;
+  // co-resident CTAs per SM: 2 for the tensor-core GQA kernel (96 KB ring) and the register-staged fallback, 4 for
+  // the staged kernel (48 KB ring, 70 registers) as long as its register-file share allows (G <= 2)
+  const int per_sm = gqa ? 2 : (direct_env || G > 2) ? 2 : 4;
+  return decode_splits(batch, KV, kv.max_ctx, per_sm * sm_count());
 }
 
 size_t decode_attn_scratch_bytes(int batch, int H, int hd, int max_ctx) {
@@ -454,11 +470,12 @@ int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const Kv
   DLI_REQUIRE(q && out && scratch, "dli_decode_attention: null pointer");
   DLI_REQUIRE(batch > 0 && H > 0 && KV > 0 && H % KV == 0, "dli_decode_attention: batch=%d H=%d KV=%d", batch, H, KV);
   const int G = H / KV;
-  const int splits = decode_splits(batch, KV, kv.max_ctx);
+  const bool gqa = decode_attn_gqa_supported(kv, G, hd);
+  const int splits = decode_splits_for(kv, batch, H, KV, hd);
   const size_t need = (size_t)batch * H * splits * (hd + 2) * sizeof(float);
   if (scratch_bytes < need)
     return fail(DLI_ERR_WORKSPACE, "dli_decode_attention: scratch %zu bytes < %zu needed", scratch_bytes, need);
-  if (decode_attn_gqa_supported(kv, G, hd)) {  // grouped-query models: tensor-core kernel (attn_decode_gqa.cu)
+  if (gqa) {  // grouped-query models: tensor-core kernel (attn_decode_gqa.cu)
     int rc = launch_decode_attention_gqa(q, out, kv, batch, H, KV, hd, splits, scratch, early_kv, st);
     if (rc || splits == 1) return rc;
     if (hd == 128)
@@ -521,7 +538,7 @@ extern "C" int dli_decode_attention_static(const void* q_bf16, void* out_bf16, c
   int rc = kv_view(kv, layer, &v);
   if (rc) return rc;
   // same split count the launcher will choose, so the size check here is exact
-  const size_t need = (size_t)batch * n_heads * decode_splits(batch, n_kv_heads, v.max_ctx) * (head_dim + 2) * sizeof(float);
+  const size_t need = (size_t)batch * n_heads * decode_splits_for(v, batch, n_heads, n_kv_heads, head_dim) * (head_dim + 2) * sizeof(float);
   if (need > DLI_STATIC_SCRATCH_BYTES)
     return fail(DLI_ERR_WORKSPACE,
                 "dli_decode_attention_static: this problem needs %zu bytes of split-K scratch but the built-in array holds "

@@ -7,9 +7,12 @@ timeout 900 $TR bench.py --gpus $N --steps 16 --warmup 4 --cpu-budget 0 > gpurun
 if [ $# -gt 0 ]; then
   timeout 900 $TR bench.py --gpus $N --steps 16 --warmup 4 --cpu-budget 0 "$@" > gpurun_out/multi_cfg_$N.json 2> gpurun_out/multi_cfg_$N.err || tail -20 gpurun_out/multi_cfg_$N.err
 fi
+if [ -n "${CFG2:-}" ]; then
+  timeout 900 $TR bench.py --gpus $N --steps 16 --warmup 4 --cpu-budget 0 $CFG2 > gpurun_out/multi_cfg2_$N.json 2> gpurun_out/multi_cfg2_$N.err || tail -20 gpurun_out/multi_cfg2_$N.err
+fi
 python - <<PY
 import json
-for f in ("gpurun_out/multi_default_$N.json", "gpurun_out/multi_cfg_$N.json"):
+for f in ("gpurun_out/multi_default_$N.json", "gpurun_out/multi_cfg_$N.json", "gpurun_out/multi_cfg2_$N.json"):
     try:
         d = json.loads(open(f).read().strip().splitlines()[-1])
     except Exception as e:
