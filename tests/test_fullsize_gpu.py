@@ -32,7 +32,7 @@ def _close(name, a, b, rel=2e-2):
     assert d.mean() <= 0.1 * rel * scale, f"{name}: mean_abs_diff {d.mean():.4e} vs scale {scale:.4e}"
 
 
-@pytest.mark.parametrize("shape_name,B,L", [("7b", 2, 160), ("70b", 1, 136)])
+@pytest.mark.parametrize("shape_name,B,L", [("7b", 2, 160), ("13b", 2, 130), ("70b", 1, 136)])
 def test_full_width_layers_match_oracle(shape_name, B, L):
     """Two layers of the real width: a chunk long enough for the CTA-pair GEMM (>= 256 tokens in total) and the
     tcgen05 attention, then decode steps through the swap-AB GEMMs and the MHA / GQA decode attention."""
@@ -53,7 +53,7 @@ def test_full_width_layers_match_oracle(shape_name, B, L):
         _check(f"{shape_name} decode {step}", got.float().cpu().numpy(), ref.numpy())
 
 
-@pytest.mark.parametrize("shape_name,B,T", [("7b", 16, 512), ("70b", 4, 512), ("70b", 1, 2048)])
+@pytest.mark.parametrize("shape_name,B,T", [("7b", 16, 512), ("13b", 8, 512), ("70b", 4, 512), ("70b", 1, 2048)])
 def test_bench_size_properties(shape_name, B, T):
     shp = syn.SHAPES[shape_name]
     W = syn.make_span_weights(shp, [0, 1], norm_jitter=0.1)
