@@ -11,6 +11,11 @@ if [ "${DLI_TRACE:-0}" = "1" ]; then  # timeline build for tests/exp_trace.py; n
   OUT=libdli_b200_trace.so
   BUILD=build_trace
 fi
+if [ -n "${DLI_VARIANT:-}" ]; then  # A/B experiments on one box: -D$DLI_VARIANT into libdli_b200_$DLI_VARIANT.so (load with DLI_LIB)
+  FLAGS="$FLAGS -D$DLI_VARIANT"
+  OUT=libdli_b200_$DLI_VARIANT.so
+  BUILD=build_$DLI_VARIANT
+fi
 mkdir -p $BUILD
 pids=()
 for f in gemm_tcgen05 norm_rope attn_decode attn_decode_gqa attn_prefill attn_prefill_tc span; do
