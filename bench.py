@@ -242,7 +242,7 @@ def run_ours(args):
     blk = build_span(shape, layer_ids, dev, max_positions=max(8192, total_ctx + 64))
     cache = PartialLlamaSinkCache(1 << 20, 4, page_tokens=args.page_tokens,
                                   capacity_tokens=n_mb * BATCH * (total_ctx + 16) + BATCH * 64 +
-                                  (n_mb if world > 1 else 1) * BATCH * (PROMPT + 16))
+                                  (n_mb if world > 1 else 1) * BATCH * (PROMPT + 16) + (PROMPT + 128))
     stage = PipelineStage(blk, cache, rank, world, dev)
     gids = [f"mb{m}" for m in range(n_mb)]
 
@@ -457,6 +457,31 @@ def run_ours(args):
                       "H2D on stage 0, outputs of the last stage copied D2H on stage 0, synchronised every step (wall "
                       "clock, max over ranks); steps do not overlap, so the pipe fills and drains every step"}
 
+    # ---- configs[1] also names batch 1: per-token latency of the same span with ONE sequence (one GPU only) ----
+    batch1 = None
+    if world == 1 and graph is not None and BATCH != 1:
+        x1 = syn.make_hidden(shape, 1, PROMPT, seed=123, device=dev)
+        blk("b1", x1, past_key_value=cache)
+        n1 = min(K, 32)
+        g1 = blk.graphed_decode("b1", cache, PROMPT + n1 + 8)
+        xt1 = syn.make_hidden(shape, 1, 1, seed=124, device=dev)
+        for _ in range(3):
+            g1.step(xt1)
+        ev1 = [torch.cuda.Event(enable_timing=True) for _ in range(n1 + 1)]
+        torch.cuda.synchronize()
+        ev1[0].record()
+        for k in range(n1):
+            g1.step()
+            ev1[k + 1].record()
+        torch.cuda.synchronize()
+        lat1 = sorted(ev1[k].elapsed_time(ev1[k + 1]) for k in range(n1))
+        ms1 = ev1[0].elapsed_time(ev1[n1]) / n1
+        sb1 = decode_step_bytes(shape, len(layer_ids), 1, PROMPT + 3 + n1 // 2)
+        batch1 = {"tokens_per_sec": round(1e3 / ms1, 1), "ms_per_step": round(ms1, 4), "p50_ms_per_token": round(lat1[n1 // 2], 4),
+                  "steps": n1, "stage_roofline_frac": round(sb1["total"] / (ms1 * 1e-3) / 1e9 / hbm_peak, 4),
+                  "bytes_per_step": sb1["total"]}
+        cache.close("b1")
+
     if rank == 0:
         cpu = (cpu_reference_decode(shape, n_total, BATCH, PROMPT, budget_s=args.cpu_budget)
                if (world == 1 and args.cpu_budget > 0) else None)
@@ -495,7 +520,7 @@ def run_ours(args):
                                "frac": round(stage_gbs / hbm_peak, 4), "bytes_per_stage_step": sb["total"],
                                "note": "whole decode stage-step (all kernels + gaps), SURVEY 8d algorithmic bytes"},
             "kernel_ms_per_step": breakdown, "kernel_ms_per_step_sum": round(step_prof_ms, 4),
-            "e2e": e2e, "cpu_baseline": cpu,
+            "e2e": e2e, "cpu_baseline": cpu, "decode_batch1": batch1,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
