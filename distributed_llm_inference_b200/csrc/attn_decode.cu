@@ -16,6 +16,7 @@
 #include <stdlib.h>
 
 #include "tc_ptx.cuh"
+#include "rope_inline.cuh"
 
 namespace dli {
 
@@ -230,7 +231,8 @@ template <int HD, int G>
 __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const __nv_bfloat16* __restrict__ q, KvView kv,
                                                                          float* __restrict__ scratch,
                                                                          __nv_bfloat16* __restrict__ out, int H, int KV,
-                                                                         float scale_log2, int early_kv) {
+                                                                         float scale_log2, int early_kv,
+                                                                         const DecRope rp) {
   constexpr int LPT = HD / 8;                   // lanes per token
   constexpr int GPW = 32 / LPT;                 // token groups per warp
   constexpr int NG = (DEC_THREADS / 32) * GPW;  // token groups per CTA
@@ -271,6 +273,10 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
   const int t_begin = split * chunk;
   const int t_end = min(T, t_begin + chunk);
   const int n_stages = t_end > t_begin ? (t_end - t_begin + DEC_STAGE_TOK - 1) / DEC_STAGE_TOK : 0;
+  // fused RoPE + append (unsplit contexts only): the pages hold tokens [0, T - 1); the step's own key and value come
+  // from the projection buffer, go to the page AND straight into their row of the last ring stage
+  const bool fused = rp.qkv != nullptr;
+  const int t_copy = fused ? T - 1 : T;  // tokens the producer takes from the pages
 
   float o[G][8], m[G], l[G];
 #pragma unroll
@@ -290,9 +296,8 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
     bool waited = !early_kv;
     for (int i = 0; i < n_stages; ++i) {
       const int slot = i % DEC_STAGES;
-      const int s0 = t_begin + i * DEC_STAGE_TOK, s1 = min(t_end, s0 + DEC_STAGE_TOK);
-      const int p0 = s0 / pt, p1 = (s1 - 1) / pt;
-      // pieces beyond the 32nd (page_tokens == 1 is the only way to get there) are taken in a second pass
+      const int s0 = t_begin + i * DEC_STAGE_TOK, s1 = min(min(t_end, t_copy), s0 + DEC_STAGE_TOK);
+      const int p0 = s0 / pt, p1 = s1 > s0 ? (s1 - 1) / pt : p0 - 1;  // s1 <= s0: the stage holds only the new token
       int page = -1;
       if (p0 + lane <= p1) page = bt[p0 + lane];
       if (!waited && s1 >= T) {  // this stage holds the step's own token: not before the append kernel is done
@@ -300,7 +305,7 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
         waited = true;
       }
       if (i >= DEC_STAGES) mbar_wait(empty0 + 8 * slot, ((uint32_t)(i / DEC_STAGES) - 1) & 1);
-      if (lane == 0) mbar_expect_tx(full0 + 8 * slot, (uint32_t)(s1 - s0) * ROW * 2);
+      if (lane == 0) mbar_expect_tx(full0 + 8 * slot, (uint32_t)max(s1 - s0, 0) * ROW * 2);
       __syncwarp();
       if (page >= 0) {
         const int ta = max(s0, (p0 + lane) * pt), tb = min(s1, (p0 + lane + 1) * pt);
@@ -314,19 +319,43 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
     if (!waited) pdl_wait();  // this warp also stores results below
   } else {
     float qf[G][8];
+    uint4 newrow = make_uint4(0, 0, 0, 0);  // fused: this lane's chunk of the step's own K (lanes < LPT) / V row
 #pragma unroll
     for (int g = 0; g < G; ++g) {
-      const uint4 a = *reinterpret_cast<const uint4*>(q + ((long long)b * H + kvh * G + g) * HD + dl);
+      uint4 a;
+      if (fused) {  // rotate, then round to bf16 exactly as the stand-alone RoPE kernel's q buffer would hold it
+        float r8[8];
+        rope8<HD>(rp.qkv + (long long)b * rp.n_all + (kvh * G + g) * HD, rp.cos, rp.sin, dl, r8);
+        a = make_uint4(pack_bf16(r8[0], r8[1]), pack_bf16(r8[2], r8[3]), pack_bf16(r8[4], r8[5]), pack_bf16(r8[6], r8[7]));
+      } else {
+        a = *reinterpret_cast<const uint4*>(q + ((long long)b * H + kvh * G + g) * HD + dl);
+      }
       qf[g][0] = bf16_lo(a.x) * scale_log2; qf[g][1] = bf16_hi(a.x) * scale_log2;
       qf[g][2] = bf16_lo(a.y) * scale_log2; qf[g][3] = bf16_hi(a.y) * scale_log2;
       qf[g][4] = bf16_lo(a.z) * scale_log2; qf[g][5] = bf16_hi(a.z) * scale_log2;
       qf[g][6] = bf16_lo(a.w) * scale_log2; qf[g][7] = bf16_hi(a.w) * scale_log2;
+    }
+    const int new_row = (T - 1 - t_begin) % DEC_STAGE_TOK;  // row of the step's token inside the last stage
+    if (fused) {
+      newrow = new_kv_chunk<HD>(rp, b, H, KV, kvh, lane);
+      if (warp == 0) append_new_kv<HD>(kv, b, KV, kvh, T - 1, lane, newrow);
     }
     for (int i = 0; i < n_stages; ++i) {
       const int slot = i % DEC_STAGES;
       const int t0 = t_begin + i * DEC_STAGE_TOK;
       const uint32_t kbase = ring + slot * STAGE + (uint32_t)grp * ROW + dl * 2;
       mbar_wait(full0 + 8 * slot, (uint32_t)(i / DEC_STAGES) & 1);
+      if (fused && i == n_stages - 1 && warp == (new_row % NG) / GPW) {
+        // the warp whose token group reads that row puts the new K and V there (the bulk copies never touch it)
+        if (lane < 2 * LPT) {
+          const uint32_t dst = ring + slot * STAGE + (lane < LPT ? 0u : (uint32_t)KPART) + (uint32_t)new_row * ROW +
+                               (uint32_t)(lane % LPT) * 16;
+          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(newrow.x), "r"(newrow.y), "r"(newrow.z),
+                       "r"(newrow.w)
+                       : "memory");
+        }
+        __syncwarp();
+      }
 #pragma unroll
       for (int h = 0; h < UNROLL / UH; ++h) {
         uint4 kk[UH], vv[UH];
@@ -419,6 +448,7 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
       if (d == 0) { dst[HD] = M; dst[HD + 1] = L; }
     }
   }
+  if (fused) zero_consumed<HD, G, DEC_THREADS_STAGED>(rp, b, H, KV, kvh);  // every read of the row is behind the barriers above
   if (threadIdx.x == 0) DLI_TRACE_EV(TR_ATTN, 2);
 }
 
@@ -442,7 +472,7 @@ __global__ void __launch_bounds__(HD) decode_combine_kernel(const float* __restr
 
 template <int HD, int G>
 static int launch_dec(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV, int splits,
-                      float* scratch, bool early_kv, cudaStream_t st) {
+                      float* scratch, bool early_kv, const DecRope& rope, cudaStream_t st) {
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
   static const bool direct = getenv("DLI_DEC_DIRECT") != nullptr;  // A/B switch for the register-staged kernel
   int rc;
@@ -458,25 +488,41 @@ static int launch_dec(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& 
     }
     rc = launch_kernel("decode_attn_kernel", decode_attn_kernel<HD, G>, dim3(splits, KV, batch),
                        dim3(DEC_THREADS_STAGED), dec_smem_bytes<HD, G>(), st, q, kv, scratch, out, H, KV, scale_log2,
-                       early_kv ? 1 : 0);
+                       early_kv ? 1 : 0, rope);
   }
   if (rc || splits == 1) return rc;
   return launch_kernel("decode_combine_kernel", decode_combine_kernel<HD>, dim3(H, batch), dim3(HD), 0, st,
                        (const float*)scratch, out, H, splits);
 }
 
+// One CTA per (sequence, KV head) is the only reader of that head's projection and the only writer of its page slot:
+// the condition under which the attention kernel can do the RoPE kernel's work.
+bool decode_attention_fuses_rope(const KvView& kv, int batch, int H, int KV, int hd) {
+  static const bool off = getenv("DLI_DEC_DIRECT") != nullptr || getenv("DLI_NO_ROPE_FUSE") != nullptr;
+  if (off || KV <= 0 || H % KV != 0 || !(hd == 64 || hd == 128)) return false;
+  const int G = H / KV;
+  if (!(G == 1 || G == 2 || G == 4 || G == 8)) return false;
+  return decode_splits_for(kv, batch, H, KV, hd) == 1;
+}
+
 int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV, int hd,
-                            float* scratch, size_t scratch_bytes, cudaStream_t st, bool early_kv) {
-  DLI_REQUIRE(q && out && scratch, "dli_decode_attention: null pointer");
+                            float* scratch, size_t scratch_bytes, cudaStream_t st, bool early_kv, const DecRope* rope_in) {
+  DLI_REQUIRE((q || rope_in) && out && scratch, "dli_decode_attention: null pointer");
   DLI_REQUIRE(batch > 0 && H > 0 && KV > 0 && H % KV == 0, "dli_decode_attention: batch=%d H=%d KV=%d", batch, H, KV);
   const int G = H / KV;
   const bool gqa = decode_attn_gqa_supported(kv, G, hd);
   const int splits = decode_splits_for(kv, batch, H, KV, hd);
+  DecRope rope{nullptr, nullptr, nullptr, 0};
+  if (rope_in) {
+    DLI_REQUIRE(splits == 1 && rope_in->qkv && rope_in->cos && rope_in->sin,
+                "decode attention with fused RoPE needs an unsplit context (see decode_attention_fuses_rope)");
+    rope = *rope_in;
+  }
   const size_t need = (size_t)batch * H * splits * (hd + 2) * sizeof(float);
   if (scratch_bytes < need)
     return fail(DLI_ERR_WORKSPACE, "dli_decode_attention: scratch %zu bytes < %zu needed", scratch_bytes, need);
   if (gqa) {  // grouped-query models: tensor-core kernel (attn_decode_gqa.cu)
-    int rc = launch_decode_attention_gqa(q, out, kv, batch, H, KV, hd, splits, scratch, early_kv, st);
+    int rc = launch_decode_attention_gqa(q, out, kv, batch, H, KV, hd, splits, scratch, early_kv, rope, st);
     if (rc || splits == 1) return rc;
     if (hd == 128)
       return launch_kernel("decode_combine_kernel", decode_combine_kernel<128>, dim3(H, batch), dim3(128), 0, st,
@@ -485,7 +531,7 @@ int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const Kv
                          (const float*)scratch, out, H, splits);
   }
 #define DLI_DEC_CASE(HD_, G_) \
-  if (hd == HD_ && G == G_) return launch_dec<HD_, G_>(q, out, kv, batch, H, KV, splits, scratch, early_kv, st)
+  if (hd == HD_ && G == G_) return launch_dec<HD_, G_>(q, out, kv, batch, H, KV, splits, scratch, early_kv, rope, st)
   DLI_DEC_CASE(128, 1); DLI_DEC_CASE(128, 2); DLI_DEC_CASE(128, 4); DLI_DEC_CASE(128, 8);
   DLI_DEC_CASE(64, 1); DLI_DEC_CASE(64, 2); DLI_DEC_CASE(64, 4); DLI_DEC_CASE(64, 8);
 #undef DLI_DEC_CASE

@@ -18,6 +18,7 @@
 #include "common.cuh"
 #include "mma_sync.cuh"
 #include "tc_ptx.cuh"
+#include "rope_inline.cuh"
 
 #include <math.h>
 #include <stdlib.h>
@@ -50,7 +51,8 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
                                                                      const __nv_bfloat16* __restrict__ q, KvView kv,
                                                                      float* __restrict__ scratch,
                                                                      __nv_bfloat16* __restrict__ out, int H, int KV,
-                                                                     float scale_log2, int early_kv) {
+                                                                     float scale_log2, int early_kv,
+                                                                     const DecRope rp) {
   static_assert(G <= 8, "one m16 tile holds at most 8 real heads in its lower half");
   constexpr int HALVES = HD / 64;
   constexpr int HALF_BYTES = GQ_STAGE_TOK * 128;
@@ -88,6 +90,10 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
   const int t_begin = split * chunk;
   const int t_end = min(T, t_begin + chunk);
   const int n_stages = t_end > t_begin ? (t_end - t_begin + GQ_STAGE_TOK - 1) / GQ_STAGE_TOK : 0;
+  // fused RoPE + append (unsplit contexts only, rope_inline.cuh): the pages hold tokens [0, T - 1); the step's own key
+  // and value go to the page and straight into their row of the last ring stage
+  const bool fused = rp.qkv != nullptr;
+  const int t_copy = fused ? T - 1 : T;
 
   const int r = lane >> 2, c = lane & 3;  // fragment row (query head of the group) and column pair
   float o[NT][4];
@@ -102,8 +108,8 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
     bool waited = !early_kv;
     for (int i = 0; i < n_stages; ++i) {
       const int slot = i % GQ_STAGES;
-      const int s0 = t_begin + i * GQ_STAGE_TOK, s1 = min(t_end, s0 + GQ_STAGE_TOK);
-      const int n_pages = (s1 - s0 + pt - 1) / pt;  // only pages that hold a token of this split are touched
+      const int s0 = t_begin + i * GQ_STAGE_TOK, s1 = min(min(t_end, t_copy), s0 + GQ_STAGE_TOK);
+      const int n_pages = s1 > s0 ? (s1 - s0 + pt - 1) / pt : 0;  // only pages that hold a (past) token of this split
       int page = -1;
       if (lane < n_pages) page = bt[s0 / pt + lane];
       if (!waited && s1 >= T) {  // this stage holds the step's own token: not before the append kernel is done
@@ -131,17 +137,39 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
     for (int ks = 0; ks < KS; ++ks) {
       qa[ks][0] = qa[ks][1] = 0u;
       if (r < G) {
-        const __nv_bfloat16* src = q + ((long long)b * H + kvh * G + r) * HD + ks * 16 + 2 * c;
-        qa[ks][0] = *reinterpret_cast<const uint32_t*>(src);
-        qa[ks][1] = *reinterpret_cast<const uint32_t*>(src + 8);
+        if (fused) {
+          const float* x = rp.qkv + (long long)b * rp.n_all + (kvh * G + r) * HD;
+          qa[ks][0] = rope2_bf16<HD>(x, rp.cos, rp.sin, ks * 16 + 2 * c);
+          qa[ks][1] = rope2_bf16<HD>(x, rp.cos, rp.sin, ks * 16 + 2 * c + 8);
+        } else {
+          const __nv_bfloat16* src = q + ((long long)b * H + kvh * G + r) * HD + ks * 16 + 2 * c;
+          qa[ks][0] = *reinterpret_cast<const uint32_t*>(src);
+          qa[ks][1] = *reinterpret_cast<const uint32_t*>(src + 8);
+        }
       }
     }
     const int tw = warp * 16;  // this warp's token rows inside a stage
+    const int new_row = (T - 1 - t_begin) % GQ_STAGE_TOK;  // row of the step's token inside the last stage
+    uint4 newrow = make_uint4(0, 0, 0, 0);
+    if (fused) {
+      newrow = new_kv_chunk<HD>(rp, b, H, KV, kvh, lane);
+      if (warp == 0) append_new_kv<HD>(kv, b, KV, kvh, T - 1, lane, newrow);
+    }
     for (int i = 0; i < n_stages; ++i) {
       const int slot = i % GQ_STAGES;
       const int s0 = t_begin + i * GQ_STAGE_TOK;
       const uint32_t kbase = ring + slot * STAGE, vbase = kbase + KPART;
       mbar_wait(full0 + 8 * slot, (uint32_t)(i / GQ_STAGES) & 1);
+      if (fused && i == n_stages - 1 && warp == new_row / 16) {
+        // the warp that owns that token row puts the new K and V there (TMA wrote at most a stale copy of it)
+        if (lane < 2 * CPR) {
+          const uint32_t dst = (lane < CPR ? kbase : vbase) + gq_off(new_row, lane % CPR);
+          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(newrow.x), "r"(newrow.y), "r"(newrow.z),
+                       "r"(newrow.w)
+                       : "memory");
+        }
+        __syncwarp();
+      }
       const int valid = t_end - s0;  // token rows >= valid hold whatever was there before
       if (valid < tw + 16) {
         // P is zero for those rows, but 0 * NaN is NaN: clear the V rows this warp is about to multiply
@@ -249,6 +277,7 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
       if (d == 0) { dst[HD] = M; dst[HD + 1] = L; }
     }
   }
+  if (fused) zero_consumed<HD, G, GQ_THREADS>(rp, b, H, KV, kvh);  // every read of the row is behind the barriers above
   if (threadIdx.x == 0) DLI_TRACE_EV(TR_ATTN_GQA, 2);
 }
 
@@ -263,7 +292,7 @@ bool decode_attn_gqa_supported(const KvView& kv, int G, int hd) {
 template <int HD, int G>
 static int launch_gqa(const CUtensorMap& tk, const CUtensorMap& tv, const __nv_bfloat16* q, __nv_bfloat16* out,
                       const KvView& kv, int batch, int H, int KV, int splits, float* scratch, bool early_kv,
-                      cudaStream_t st) {
+                      const DecRope& rope, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
     DLI_CUDA_OK(cudaFuncSetAttribute(decode_attn_gqa_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -272,12 +301,12 @@ static int launch_gqa(const CUtensorMap& tk, const CUtensorMap& tv, const __nv_b
   }
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
   return launch_kernel("decode_attn_gqa_kernel", decode_attn_gqa_kernel<HD, G>, dim3(splits, KV, batch), dim3(GQ_THREADS),
-                       (size_t)gq_smem_bytes<HD, G>(), st, tk, tv, q, kv, scratch, out, H, KV, scale_log2, early_kv ? 1 : 0);
+                       (size_t)gq_smem_bytes<HD, G>(), st, tk, tv, q, kv, scratch, out, H, KV, scale_log2, early_kv ? 1 : 0, rope);
 }
 
 // Launches the main kernel only; the caller runs the shared combine kernel when splits > 1.
 int launch_decode_attention_gqa(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV,
-                                int hd, int splits, float* scratch, bool early_kv, cudaStream_t st) {
+                                int hd, int splits, float* scratch, bool early_kv, const DecRope& rope, cudaStream_t st) {
   const int G = H / KV;
   CUtensorMap tk, tv;
   const long long pool_rows = (long long)kv.n_pages * KV * kv.page_tokens;
@@ -285,7 +314,7 @@ int launch_decode_attention_gqa(const __nv_bfloat16* q, __nv_bfloat16* out, cons
   if (rc) return rc;
   if ((rc = make_tmap_bf16(&tv, kv.v, pool_rows, hd, hd, kv.page_tokens))) return rc;
 #define DLI_GQA_CASE(HD_, G_) \
-  if (hd == HD_ && G == G_) return launch_gqa<HD_, G_>(tk, tv, q, out, kv, batch, H, KV, splits, scratch, early_kv, st)
+  if (hd == HD_ && G == G_) return launch_gqa<HD_, G_>(tk, tv, q, out, kv, batch, H, KV, splits, scratch, early_kv, rope, st)
   DLI_GQA_CASE(128, 2); DLI_GQA_CASE(128, 4); DLI_GQA_CASE(128, 8);
   DLI_GQA_CASE(64, 2); DLI_GQA_CASE(64, 4); DLI_GQA_CASE(64, 8);
 #undef DLI_GQA_CASE

@@ -116,14 +116,24 @@ int launch_kv_evict(const dli_kv_desc* kv, int n_layers, int batch, int KV, int 
                     int n_new, const float* cos_hist, const float* sin_hist, cudaStream_t st);
 int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st);
 size_t decode_attn_scratch_bytes(int batch, int H, int hd, int max_ctx);
+// Decode attention that applies RoPE and the KV append itself (rope_inline.cuh); qkv == nullptr: q arrives rotated in
+// bf16 and the pages already hold the step's token.  Only for unsplit contexts: decode_attention_fuses_rope().
+struct DecRope {
+  const float* qkv;  // [batch, n_all] fp32 q|k|v projection of the step (split-K accumulation buffer; re-zeroed)
+  const float* cos;  // [hd] of the step's position
+  const float* sin;
+  int n_all;         // (H + 2 KV) * hd
+};
+bool decode_attention_fuses_rope(const KvView& kv, int batch, int H, int KV, int hd);
 bool decode_attn_gqa_supported(const KvView& kv, int G, int hd);
 int launch_decode_attention_gqa(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV,
-                                int hd, int splits, float* scratch, bool early_kv, cudaStream_t st);
+                                int hd, int splits, float* scratch, bool early_kv, const DecRope& rope, cudaStream_t st);
 // early_kv: the K/V pages of every token but the step's own were written before the current chain of launches began
 // (see pdl_barrier_next_launch), so the kernel may stream them before its dependency wait.  The span runner says yes;
 // the op-level ABI, which knows nothing about its caller's stream, says no.
 int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV,
-                            int hd, float* scratch, size_t scratch_bytes, cudaStream_t st, bool early_kv = false);
+                            int hd, float* scratch, size_t scratch_bytes, cudaStream_t st, bool early_kv = false,
+                            const DecRope* rope = nullptr);
 bool prefill_attn_tc_supported(const KvView& kv, int hd);
 int launch_prefill_attention_tc(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H,
                                 int KV, bool causal, cudaStream_t st);

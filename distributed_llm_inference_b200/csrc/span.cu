@@ -378,6 +378,7 @@ int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, i
     // q|k|v projection (modules.py:61-63)
     // prefill: RoPE + KV append are the epilogue of the projection GEMM (whole heads per 256-column tile)
     const bool fused_rope = !skinny && s->n_qkv % 256 == 0 && gemm_persistent_enabled();
+    bool fused_dec_rope = false;
     DLI_MARK(DLI_PROF_GEMM_QKV);
     if (fused_rope) {
       RopeArgs ra{cos, sin, w.qbuf, view, q_len, d.n_heads, d.n_kv_heads, d.head_dim};
@@ -385,11 +386,14 @@ int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, i
       if (rc) return rc;
     } else {
       float* qkv = skinny ? w.qkv_acc : w.qkv;
+      // decode with an unsplit context: the attention kernel rotates q and k, appends k and v and re-zeroes the
+      // accumulation rows itself (rope_inline.cuh) -- one launch less per layer
+      fused_dec_rope = q_len == 1 && skinny && decode_attention_fuses_rope(view, batch, d.n_heads, d.n_kv_heads, d.head_dim);
       rc = DLI_SKIPPED(DLI_PROF_GEMM_QKV) ? 0 : span_gemm(s, w.xn, L.qkv, qkv, s->n_qkv, M, s->n_qkv, h, skinny ? DLI_EPI_ADD_F32 : DLI_EPI_STORE_F32, st);
       if (rc) return rc;
       // RoPE + cache append (modules.py:73-85, cache.py:103-109); re-zeroes the split-K accumulation buffer behind itself
       DLI_MARK(DLI_PROF_ROPE_APPEND);
-      rc = DLI_SKIPPED(DLI_PROF_ROPE_APPEND) ? 0 : launch_rope_kv_append(qkv, skinny, cos, sin, w.qbuf, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim, st);
+      rc = (DLI_SKIPPED(DLI_PROF_ROPE_APPEND) || fused_dec_rope) ? 0 : launch_rope_kv_append(qkv, skinny, cos, sin, w.qbuf, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim, st);
       if (rc) return rc;
     }
     // attention core (modules.py:87-105)
@@ -397,8 +401,11 @@ int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, i
     if (DLI_SKIPPED(DLI_PROF_ATTENTION))
       rc = 0;
     else if (q_len == 1)
+    {
+      const DecRope dr{w.qkv_acc, cos, sin, s->n_qkv};
       rc = launch_decode_attention(w.qbuf, w.attn, view, batch, d.n_heads, d.n_kv_heads, d.head_dim, w.dec_scratch,
-                                   w.dec_scratch_bytes, st, /*early_kv=*/true);
+                                   w.dec_scratch_bytes, st, /*early_kv=*/true, fused_dec_rope ? &dr : nullptr);
+    }
     else
       rc = launch_prefill_attention(w.qbuf, w.attn, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim, causal != 0, st);
     if (rc) return rc;
