@@ -324,6 +324,9 @@ def run_ours(args):
     for _ in range(W):
         xs = decode_round(xs, pos)
         pos += 1
+    round_graph = False
+    if world > 1 and graph is not None and stage.handoff == "peer_store" and not args.no_round_graph:
+        round_graph = stage.capture_round(gids)     # steady-state rounds: one graph launch per round
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -506,7 +509,8 @@ def run_ours(args):
                                    f"{PROMPT + W}..{PROMPT + W + K}; random-init weights, synthetic hidden states",
                        "global_batch": tokens_per_step, "seq_len": PROMPT, "parallelism": f"pp{world}",
                        "l2": "inputs larger than L2 (12.9 GB of weights streamed per step)", "page_tokens": args.page_tokens,
-                       "launch": "cuda_graph" if graph is not None else "eager",
+                       "launch": ("cuda_graph_per_round" if round_graph else "cuda_graph") if graph is not None else "eager",
+                       "round_graph_error": stage.round_error,
                        "handoff": stage.handoff, "handoff_fallback_reason": stage.handoff_error},
             "p50_ms_per_token": round(lat[len(lat) // 2] / n_mb, 4),
             "prefill_tokens_per_sec": round(n_mb * BATCH * PROMPT / (prefill_ms.item() * 1e-3), 1),
@@ -567,6 +571,7 @@ def main():
     ap.add_argument("--prefill-chunk", type=int, default=None, help="prefill the prompt in chunks of this many tokens")
     ap.add_argument("--nccl-handoff", action="store_true", help="hand off by NCCL isend/irecv instead of peer stores")
     ap.add_argument("--no-graph", action="store_true", help="decode with eager launches instead of the CUDA graph")
+    ap.add_argument("--no-round-graph", action="store_true", help="pipeline: one graph per micro-batch instead of per round")
     args = ap.parse_args()
     global BATCH, MODEL, PROMPT
     if args.prompt:

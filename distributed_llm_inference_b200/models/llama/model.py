@@ -296,23 +296,31 @@ class GraphedDecode:
         block(warm, self.x, past_key_value=cache, cache_position=torch.zeros(1, dtype=torch.long, device=device))
         cache.close(warm)
         torch.cuda.synchronize(device)
+        self._launch = launch         # PipelineStage.capture_round re-captures the same launches into a round graph
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             self._keep = launch()
         self.launches = ffi.lib.dli_last_launch_count()
         self._len = gen.length        # host mirror of the device-side position
 
-    def step(self, x: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def before_replay(self) -> None:
         gen = self.cache.generation(self.gid)
         if gen.length + 1 > self.max_ctx:
             raise RuntimeError(f"graphed decode captured for at most {self.max_ctx} tokens")
         if gen.length != self._len:                                    # eager steps ran in between: re-seed the position
             self.pos.fill_(gen.first_pos + gen.seen_tokens)
-        if x is not None and x.data_ptr() != self.x.data_ptr():
-            self.x.copy_(x)
-        self.graph.replay()
+
+    def after_replay(self) -> None:
+        gen = self.cache.generation(self.gid)
         gen.length += 1                                                # host mirror of the device-side add
         self._len = gen.length
         gen.seen_tokens += 1
         self.block.last_launch_count = self.launches
+
+    def step(self, x: Optional[torch.Tensor] = None) -> torch.Tensor:
+        self.before_replay()
+        if x is not None and x.data_ptr() != self.x.data_ptr():
+            self.x.copy_(x)
+        self.graph.replay()
+        self.after_replay()
         return self.out

@@ -33,6 +33,8 @@ class PipelineStage:
         self.handoff_error = None
         self._ring_pending = False
         self.trace = None           # set to [] to collect (recv_wait_ms, step_ms) CUDA-event pairs per micro-batch
+        self._round = None          # (generation ids, CUDA graph of a whole round, kept tensors): capture_round()
+        self.round_error = None
 
     def enable_graphs(self, generation_ids: Sequence[str], max_ctx: int, batch: Optional[int] = None,
                       peer_store: bool = True) -> str:
@@ -81,6 +83,32 @@ class PipelineStage:
         if self.world > 1:
             dist.barrier()
         return self.handoff
+
+    def capture_round(self, generation_ids: Sequence[str]) -> bool:
+        """Peer-store hand-off only: capture a whole steady-state round -- for every micro-batch ``wait(prev) -> stage
+        step -> signal(next)`` -- into ONE CUDA graph, so a round costs one graph launch instead of one per micro-batch
+        plus two semaphore launches each.  All stages must call this together; if any of them cannot capture, none uses
+        it.  The per-micro-batch graphs stay in place for the first round (fresh inputs) and for tracing."""
+        ok = 1 if (self.handoff == "peer_store" and all(g in self.graphs for g in generation_ids)) else 0
+        graph, keep = None, []
+        if ok:
+            try:
+                prev, nxt = (self.rank - 1) % self.world, (self.rank + 1) % self.world
+                torch.cuda.synchronize(self.device)
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    for m, gid in enumerate(generation_ids):
+                        self.hdl.wait_signal(prev, m, 20000)
+                        keep.append(self.graphs[gid]._launch())
+                        self.hdl.put_signal(nxt, m, 20000)
+            except Exception as e:  # noqa: BLE001 - any failure means: keep the per-micro-batch graphs
+                self.round_error = repr(e)
+                ok = 0
+        flag = torch.tensor([ok], device=self.device)
+        if self.world > 1:
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        self._round = (tuple(generation_ids), graph, keep) if flag.item() == 1 else None
+        return self._round is not None
 
     # -- P2P ------------------------------------------------------------------------------------------
     def _send(self, t: torch.Tensor, dst: int) -> None:
@@ -169,6 +197,16 @@ class PipelineStage:
         first, last = self.rank == 0, self.rank == self.world - 1
         prev, nxt = (self.rank - 1) % self.world, (self.rank + 1) % self.world
         launches = 0
+        if (self._round is not None and feed_back and self.trace is None and tuple(generation_ids) == self._round[0]
+                and (not first or self._ring_pending)):
+            gs = [self.graphs[gid] for gid in generation_ids]
+            for g in gs:
+                g.before_replay()
+            self._round[1].replay()
+            for g in gs:
+                g.after_replay()
+            self.launches_per_round = sum(g.launches + 2 for g in gs)
+            return [g.x for g in gs] if first else None
         for m, gid in enumerate(generation_ids):
             g = self.graphs[gid]
             if self.trace is not None:
