@@ -33,6 +33,8 @@ def _worker(rank, world, port, out):
     hist = []
     for step in range(3):
         xs = stage.run_round(gids, xs, 3, 1, 100 + step, feed_back=True)
+        if step == 0:       # no peer-store hand-off on this backend: every stage must agree NOT to use a round graph
+            assert stage.capture_round(gids) is False and stage._round is None
         if rank == 0:
             hist.append([float(t[0, 0, 0]) for t in xs])
     final = stage.run_round(gids, xs, 3, 1, 103, feed_back=False)
