@@ -113,7 +113,9 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
   const uint32_t tS = tmem, tO = tmem + FA_BN;
 
   pdl_wait();  // q, the pages and seq_lens are produced by the preceding kernels of the stream
-  const int m0 = blockIdx.x * FA_BM, h = blockIdx.y, b = blockIdx.z;
+  // causal: a later query tile has more key tiles; launch the long ones of each head first so the grid's last wave is
+  // made of short CTAs (the q-tile index stays the fastest grid dimension: tiles of one head share its K/V in L2)
+  const int m0 = (p.causal ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x) * FA_BM, h = blockIdx.y, b = blockIdx.z;
   const int kvh = h / (p.H / p.KV);
   const int past = p.seq_lens[b];
   const int T = past + p.q_len;
@@ -218,7 +220,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
     const int pos = past + qi;  // absolute position of this query
     float m_ref = -INFINITY, l = 0.f;
     uint32_t v[16];
-    const bool dbg_on = p.dbg != nullptr && blockIdx.x == gridDim.x - 1 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 64;
+    const bool dbg_on = p.dbg != nullptr && m0 == (int)(gridDim.x - 1) * FA_BM && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 64;
     unsigned long long tc[5] = {0, 0, 0, 0, 0}, t0 = 0, t1;
 #define FA_TICK(i) do { if (dbg_on) { t1 = clock64(); tc[i] += t1 - t0; t0 = t1; } } while (0)
     if (dbg_on) t0 = clock64();
