@@ -237,6 +237,7 @@ int launch_prefill_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const K
   DLI_REQUIRE(batch > 0 && q_len > 0 && H > 0 && KV > 0 && H % KV == 0, "dli_prefill_attention: batch=%d q_len=%d H=%d KV=%d",
               batch, q_len, H, KV);
     // head_dim 128: both contractions on tcgen05 (attn_prefill_tc.cu); q_len >= 16 keeps tiny chunks on the light kernel
+  if (prefill_attn_tc2_supported(kv, hd, q_len)) return launch_prefill_attention_tc2(q, out, kv, batch, q_len, H, KV, causal, st);
   if (q_len >= 16 && prefill_attn_tc_supported(kv, hd)) return launch_prefill_attention_tc(q, out, kv, batch, q_len, H, KV, causal, st);
   static int force = -1;
   if (force < 0) {

@@ -18,7 +18,7 @@ if [ -n "${DLI_VARIANT:-}" ]; then  # A/B experiments on one box: -D$DLI_VARIANT
 fi
 mkdir -p $BUILD
 pids=()
-for f in gemm_tcgen05 norm_rope attn_decode attn_decode_gqa attn_prefill attn_prefill_tc span; do
+for f in gemm_tcgen05 norm_rope attn_decode attn_decode_gqa attn_prefill attn_prefill_tc attn_prefill_tc2 span; do
   if [ ! -f $BUILD/$f.o ] || [ $f.cu -nt $BUILD/$f.o ] || [ common.cuh -nt $BUILD/$f.o ] || [ tc_ptx.cuh -nt $BUILD/$f.o ] || [ mma_sync.cuh -nt $BUILD/$f.o ] || [ rope_inline.cuh -nt $BUILD/$f.o ] || [ ../../include/dli_b200.h -nt $BUILD/$f.o ]; then
     ( $NVCC $FLAGS -c $f.cu -o $BUILD/$f.o > $BUILD/$f.log 2>&1 || { cat $BUILD/$f.log; exit 1; } ) &
     pids+=($!)

@@ -135,6 +135,9 @@ int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const Kv
                             int hd, float* scratch, size_t scratch_bytes, cudaStream_t st, bool early_kv = false,
                             const DecRope* rope = nullptr);
 bool prefill_attn_tc_supported(const KvView& kv, int hd);
+bool prefill_attn_tc2_supported(const KvView& kv, int hd, int q_len);
+int launch_prefill_attention_tc2(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H,
+                                 int KV, bool causal, cudaStream_t st);
 int launch_prefill_attention_tc(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H,
                                 int KV, bool causal, cudaStream_t st);
 int launch_prefill_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len,

@@ -18,9 +18,15 @@ e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=Tr
 e0.record(); out = ops.prefill_attention(q, kv, 0, B, L, H, KV, hd, True, max_ctx=L); e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1)
 d = dbg.tolist(); n = d[5]
-print(f"kernel {ms:.3f} ms ({4*L*L*H*hd/2/ms/1e9:.0f} TFLOP/s causal); CTA with {n} tiles, cycles per tile:")
-for name, v in zip(["wait s_full", "pass 1: S load + max", "pass 2: S load + exp + P store", "wait pv_done (+rescale)", "fences + arrives"], d[:5]):
-    print(f"  {name:28s} {v / max(n,1):8.0f}")
+print(f"kernel {ms:.3f} ms ({4*L*L*H*hd/2/ms/1e9:.0f} TFLOP/s causal); CTA with {n} key tiles, cycles per tile:")
+if os.environ.get("DLI_FA_V1"):
+    names = ["wait s_full", "S load", "compute", "wait pv_done (+rescale)", "P store + fences + arrive"]
+    mnames = ["QK warp: wait k_full", "QK warp: wait s_empty", "QK warp: issue+rest", "PV warp: wait v_full", "PV warp: wait p_full", "PV warp: issue+rest"]
+else:
+    names = ["wait s_full", "S load", "mask + max", "row-max exchange barrier", "rescale + exp + P store + arrive"]
+    mnames = ["MMA warp: wait v_full", "MMA warp: wait p_full A", "MMA warp: wait k_full", "MMA warp: wait p_full B", "MMA warp: issue + rest"]
+for name, v in zip(names, d[:5]):
+    print(f"  {name:34s} {v / max(n,1):8.0f}")
 print(f"  total per tile {sum(d[:5]) / max(n,1):8.0f}")
-for name, v in zip(["QK warp: wait k_full", "QK warp: wait s_empty", "QK warp: issue+rest", "PV warp: wait v_full", "PV warp: wait p_full", "PV warp: issue+rest"], d[8:14]):
-    print(f"  {name:28s} {v / max(n,1):8.0f}")
+for name, v in zip(mnames, d[8:14]):
+    print(f"  {name:34s} {v / max(n,1):8.0f}")

@@ -192,7 +192,10 @@ def test_decode_attention_ragged_pages(H, KV, hd, pt, B, T):
 
 
 @pytest.mark.parametrize("H,KV,hd", [(8, 2, 64), (4, 4, 128), (8, 1, 128), (4, 2, 128)])
-@pytest.mark.parametrize("B,past,L", [(1, 0, 1), (2, 0, 9), (1, 0, 64), (2, 0, 200), (1, 37, 100), (3, 5, 65), (1, 0, 1000)])
+@pytest.mark.parametrize("B,past,L", [(1, 0, 1), (2, 0, 9), (1, 0, 64), (2, 0, 200), (1, 37, 100), (3, 5, 65), (1, 0, 1000),
+                                      (2, 0, 256), (1, 100, 300), (2, 130, 515), (1, 700, 257),
+                                      # >= 2048 queries: the two-tile TS-mode kernel (attn_prefill_tc2.cu)
+                                      (1, 0, 2048), (1, 333, 2300), (2, 0, 2100)])
 @pytest.mark.parametrize("causal", [True, False])
 def test_prefill_attention(H, KV, hd, B, past, L, causal):
     T = past + L
