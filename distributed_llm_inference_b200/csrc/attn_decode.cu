@@ -1,15 +1,18 @@
-// Split-K flash-decode attention over the paged KV cache (q_len == 1).
+// Flash-decode attention over the paged KV cache (q_len == 1), multi-head models and the generic fallbacks.
 //
 // Replaces modules.py:87-105 for a decode step: repeat_kv + QK^T/sqrt(hd) + fp32 softmax + PV + head
-// merge.  HBM-bound (every cached K and V element is read exactly once per step), so the kernel is built
-// around 128-bit loads of contiguous [token][head_dim] rows and warp-shuffle reductions; the GQA group
-// (H/KV query heads) shares each loaded K/V vector, so no repeat_kv copy is ever materialised.
+// merge.  HBM-bound (every cached K and V element is read exactly once per step).
 //
-// grid = (splits, KV heads, batch).  A CTA owns one (sequence, kv head, context split); its 4 warps are cut
-// into token groups of hd/8 lanes, each lane holding an 8-wide slice of head_dim.  Scores, running max,
-// running sum and the output accumulator stay in fp32 (online softmax in the exp2 domain).  Per-split
-// partials (unnormalised o, m, l) go to caller-provided fp32 scratch and a small combine kernel merges
-// them.
+// grid = (splits, KV heads, batch).  A CTA owns one (sequence, kv head, context split).  Three kernels:
+//   decode_attn_kernel         (default) a producer warp streams pages into a shared-memory ring with 1-D bulk
+//                              copies; 4 consumer warps, cut into token groups of hd/8 lanes that each hold an 8-wide
+//                              slice of head_dim, do the dot products (warp-shuffle reduce) and the online softmax;
+//   decode_attn_direct_kernel  the first version (128-bit global loads, register double buffering), DLI_DEC_DIRECT=1;
+//   decode_attn_gqa_kernel     (attn_decode_gqa.cu) grouped-query models on tensor cores.
+// Scores, running max, running sum and the output accumulator stay in fp32 (exp2 domain).  A split context leaves
+// per-split partials (unnormalised o, m, l) in caller-provided fp32 scratch and decode_combine_kernel merges them; an
+// unsplit one is normalised and stored directly and, inside the span, also does the RoPE/append kernel's work
+// (rope_inline.cuh).  This file also holds the split heuristic and the allocation-free entry point.
 #include "common.cuh"
 
 #include <math.h>

@@ -9,8 +9,9 @@
 //
 // Round-1 implementation: warp-level mma.sync (m16n8k16, bf16 -> fp32) with ldmatrix-fed fragments; one
 // CTA = 64 or 128 queries of one head (4 or 8 warps x 16 rows), K/V tiles of 64 keys gathered from pages with
-// cp.async into XOR-swizzled, double-buffered shared memory (the next tile loads while this one is consumed).  Attention is <= 7 % of prefill FLOPs at 8k context
-// (SURVEY 8d); the tcgen05 version is later work.
+// cp.async into XOR-swizzled shared memory.  Kept for head_dim 64, chunks of fewer than 16 queries and page sizes the
+// TMA kernels do not take; head_dim 128 goes to the tcgen05 kernels (attn_prefill_tc.cu, attn_prefill_tc2.cu), which
+// this file's launch_prefill_attention dispatches to.
 #include "common.cuh"
 #include "mma_sync.cuh"
 

@@ -14,9 +14,12 @@
 // so neither needs a transpose: TMA lands 64-element (128-byte) K slices with the 128B swizzle and the
 // UMMA shared-memory descriptors consume them directly.
 //
-// Warp roles (192 threads): warp 0 = TMA producer (one lane), warp 1 = TMEM allocator + MMA issuer (one
-// lane), warps 2-5 = epilogue (warp w reads TMEM lanes 32*(w%4) .. +31, as the hardware requires).
-// Pipelines: smem full/empty mbarrier ring (TMA <-> MMA), one tmem_full mbarrier (MMA -> epilogue).
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (both stay converged and
+// issue from one elected lane, see elect_one), warps 2-5 = epilogue (warp w reads TMEM lanes 32*(w%4) .. +31, as the
+// hardware requires).  Pipelines: smem full/empty mbarrier ring (TMA <-> MMA), tmem_full mbarrier (MMA -> epilogue).
+// Three kernels: gemm_tcgen05_kernel (decode: swap-AB, split-K; also the non-persistent token-major form),
+// gemm_tcgen05_persistent_kernel (prefill, one CTA per SM, double-buffered accumulators) and
+// gemm_tcgen05_pair_kernel (prefill, CTA pairs with cta_group::2 -- the default when m >= 256).
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
