@@ -25,7 +25,7 @@ EXPORTS = (
     "dli_decode_attention_scratch_bytes", "dli_decode_attention", "dli_prefill_attention", "dli_silu_mul",
     "dli_cast_f32_bf16", "dli_span_create", "dli_span_destroy", "dli_span_bind_weights",
     "dli_span_workspace_bytes", "dli_span_forward", "dli_last_launch_count", "dli_span_profile",
-    "dli_span_profile_read", "dli_decode_attention_static", "dli_kv_evict",
+    "dli_span_profile_read", "dli_decode_attention_static", "dli_kv_evict", "dli_span_decode_step",
 )
 
 
@@ -80,6 +80,7 @@ def _load() -> C.CDLL:
         "dli_span_profile": (C.c_int, [vp, i32]),
         "dli_span_profile_read": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]),
         "dli_span_forward": (C.c_int, [vp, C.POINTER(KvDesc), i32, i32, i32, vp, vp, vp, vp, vp, vp, sz, vp]),
+        "dli_span_decode_step": (C.c_int, [vp, C.POINTER(KvDesc), i32, vp, vp, vp, vp, vp, i32, vp, sz, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
                                                                          float* __restrict__ scratch,
                                                                          __nv_bfloat16* __restrict__ out, int H, int KV,
                                                                          float scale_log2, int early_kv,
-                                                                         const DecRope rp) {
+                                                                         const DecRope rp_in) {
   constexpr int LPT = HD / 8;                   // lanes per token
   constexpr int GPW = 32 / LPT;                 // token groups per warp
   constexpr int NG = (DEC_THREADS / 32) * GPW;  // token groups per CTA
@@ -278,6 +278,7 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
   const int n_stages = t_end > t_begin ? (t_end - t_begin + DEC_STAGE_TOK - 1) / DEC_STAGE_TOK : 0;
   // fused RoPE + append (unsplit contexts only): the pages hold tokens [0, T - 1); the step's own key and value come
   // from the projection buffer, go to the page AND straight into their row of the last ring stage
+  const DecRope rp = at_step_row<HD>(rp_in);
   const bool fused = rp.qkv != nullptr;
   const int t_copy = fused ? T - 1 : T;  // tokens the producer takes from the pages
 

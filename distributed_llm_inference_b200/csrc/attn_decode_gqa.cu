@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
                                                                      float* __restrict__ scratch,
                                                                      __nv_bfloat16* __restrict__ out, int H, int KV,
                                                                      float scale_log2, int early_kv,
-                                                                     const DecRope rp) {
+                                                                     const DecRope rp_in) {
   static_assert(G <= 8, "one m16 tile holds at most 8 real heads in its lower half");
   constexpr int HALVES = HD / 64;
   constexpr int HALF_BYTES = GQ_STAGE_TOK * 128;
@@ -92,6 +92,7 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
   const int n_stages = t_end > t_begin ? (t_end - t_begin + GQ_STAGE_TOK - 1) / GQ_STAGE_TOK : 0;
   // fused RoPE + append (unsplit contexts only, rope_inline.cuh): the pages hold tokens [0, T - 1); the step's own key
   // and value go to the page and straight into their row of the last ring stage
+  const DecRope rp = at_step_row<HD>(rp_in);
   const bool fused = rp.qkv != nullptr;
   const int t_copy = fused ? T - 1 : T;
 

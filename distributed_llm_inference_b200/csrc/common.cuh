@@ -106,15 +106,26 @@ int launch_gemm_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const CUte
 int launch_gemm(const void* x, long long ldx, const void* w, void* out, long long ldo, int m, int n, int k,
                 int epilogue, cudaStream_t st);
 
+// Decode step whose position lives on the device (dli_span_decode_step): which table row to use, and what the span's
+// last kernel advances afterwards.
+struct StepState {
+  const long long* pos;  // device: position of the step's token; nullptr = cos/sin already point at its row
+  int* seq_lens;         // device [batch]: += 1 by the last kernel when advance
+  long long* pos_rw;     // device: += 1 by the last kernel when advance
+  int batch;
+  bool advance;
+};
+
 // ---- other launchers ----------------------------------------------------------------------------------
 int launch_rmsnorm(const void* x, bool x_is_f32, const __nv_bfloat16* w, __nv_bfloat16* y, float* resid_out,
                    __nv_bfloat16* copy_out, int rows, int h, float eps, float pre_scale, cudaStream_t st);
 int launch_rope_kv_append(float* qkv, bool zero_after, const float* cos, const float* sin, __nv_bfloat16* q_out,
-                          const KvView& kv, int batch, int q_len, int H, int KV, int hd, cudaStream_t st);
+                          const KvView& kv, int batch, int q_len, int H, int KV, int hd, cudaStream_t st,
+                          const long long* pos = nullptr);  // pos: cos/sin are tables, first row = *pos
 int launch_silu_mul(float* gu, __nv_bfloat16* act, int m, int n, bool zero_after, cudaStream_t st);
 int launch_kv_evict(const dli_kv_desc* kv, int n_layers, int batch, int KV, int hd, int cur_len, int window, int sinks,
                     int n_new, const float* cos_hist, const float* sin_hist, cudaStream_t st);
-int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st);
+int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st, const StepState* adv = nullptr);
 size_t decode_attn_scratch_bytes(int batch, int H, int hd, int max_ctx);
 // Decode attention that applies RoPE and the KV append itself (rope_inline.cuh); qkv == nullptr: q arrives rotated in
 // bf16 and the pages already hold the step's token.  Only for unsplit contexts: decode_attention_fuses_rope().
@@ -123,6 +134,7 @@ struct DecRope {
   const float* cos;  // [hd] of the step's position
   const float* sin;
   int n_all;         // (H + 2 KV) * hd
+  const long long* pos;  // nullable: cos/sin are whole tables and the step's row is *pos (device memory)
 };
 bool decode_attention_fuses_rope(const KvView& kv, int batch, int H, int KV, int hd);
 bool decode_attn_gqa_supported(const KvView& kv, int G, int hd);

@@ -156,7 +156,8 @@ __global__ void __launch_bounds__(ROPE_THREADS) rope_kv_append_kernel(float* __r
                                                                       const float* __restrict__ cosT,
                                                                       const float* __restrict__ sinT,
                                                                       __nv_bfloat16* __restrict__ q_out, KvView kv,
-                                                                      int q_len, int H, int KV, int hd) {
+                                                                      int q_len, int H, int KV, int hd,
+                                                                      const long long* __restrict__ pos0) {
   pdl_trigger();
   if (threadIdx.x == 0) DLI_TRACE_EV(TR_ROPE, 0);
   const int t = blockIdx.x;
@@ -171,8 +172,9 @@ __global__ void __launch_bounds__(ROPE_THREADS) rope_kv_append_kernel(float* __r
   const int slot = pos % kv.page_tokens;
   pdl_wait();
   if (threadIdx.x == 0) DLI_TRACE_EV(TR_ROPE, 1);
-  const float* cs = cosT + (long long)l * hd;
-  const float* sn = sinT + (long long)l * hd;
+  const long long row0 = pos0 ? *pos0 : 0;  // tables indexed by absolute position, or rows already gathered
+  const float* cs = cosT + (row0 + l) * hd;
+  const float* sn = sinT + (row0 + l) * hd;
 
   const int pairs2 = (H + KV) * half / 2;  // work items: two adjacent d per thread
   const int tid = blockIdx.y * ROPE_THREADS + threadIdx.x, stride = gridDim.y * ROPE_THREADS;  // a token's work is cut over gridDim.y CTAs
@@ -211,7 +213,8 @@ __global__ void __launch_bounds__(ROPE_THREADS) rope_kv_append_kernel(float* __r
 }
 
 int launch_rope_kv_append(float* qkv, bool zero_after, const float* cos, const float* sin, __nv_bfloat16* q_out,
-                          const KvView& kv, int batch, int q_len, int H, int KV, int hd, cudaStream_t st) {
+                          const KvView& kv, int batch, int q_len, int H, int KV, int hd, cudaStream_t st,
+                          const long long* pos) {
   DLI_REQUIRE(qkv && cos && sin && q_out, "dli_rope_kv_append: null pointer");
   DLI_REQUIRE(batch > 0 && q_len > 0, "dli_rope_kv_append: batch=%d q_len=%d", batch, q_len);
   DLI_REQUIRE(hd % 8 == 0 && H % KV == 0, "dli_rope_kv_append: head_dim %% 8 and H %% KV must be 0 (hd=%d H=%d KV=%d)", hd, H, KV);
@@ -220,7 +223,7 @@ int launch_rope_kv_append(float* qkv, bool zero_after, const float* cos, const f
   int ny = 1;
   if (batch * q_len < 2 * sm_count()) ny = std::max(1, std::min(8, items / ROPE_THREADS));
   return launch_kernel("rope_kv_append_kernel", rope_kv_append_kernel, dim3(batch * q_len, ny), dim3(ROPE_THREADS), 0, st, qkv,
-                       zero_after ? 1 : 0, cos, sin, q_out, kv, q_len, H, KV, hd);
+                       zero_after ? 1 : 0, cos, sin, q_out, kv, q_len, H, KV, hd, pos);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -255,19 +258,28 @@ int launch_silu_mul(float* gu, __nv_bfloat16* act, int m, int n, bool zero_after
   return launch_kernel("silu_mul_kernel", silu_mul_kernel, dim3(blocks), dim3(256), 0, st, gu, act, m, n, zero_after ? 1 : 0);
 }
 
-__global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long n4) {
+__global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long n4,
+                                                   int* __restrict__ seq_lens, long long* __restrict__ pos, int batch) {
   pdl_trigger();
   pdl_wait();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
     const float4 a = *reinterpret_cast<const float4*>(in + i * 4);
     *reinterpret_cast<uint2*>(out + i * 4) = make_uint2(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w));
   }
+  // Last kernel of a decode step whose bookkeeping lives on the device: every kernel that read the lengths or the
+  // position is complete (the wait above is transitive), and the next step starts with a stream-ordered launch.
+  if (seq_lens && blockIdx.x == 0) {
+    for (int b = threadIdx.x; b < batch; b += blockDim.x) seq_lens[b] += 1;
+    if (threadIdx.x == 0 && pos) *pos += 1;
+  }
 }
 
-int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st) {
+int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st, const StepState* adv) {
   DLI_REQUIRE(in && out && n > 0 && n % 4 == 0, "dli_cast_f32_bf16: n=%lld must be a positive multiple of 4", n);
   const int blocks = (int)std::min<long long>((n / 4 + 255) / 256, (long long)sm_count() * 8);
-  return launch_kernel("cast_kernel", cast_kernel, dim3(blocks), dim3(256), 0, st, in, out, n / 4);
+  const bool a = adv && adv->advance;
+  return launch_kernel("cast_kernel", cast_kernel, dim3(blocks), dim3(256), 0, st, in, out, n / 4,
+                       a ? adv->seq_lens : (int*)nullptr, a ? adv->pos_rw : (long long*)nullptr, a ? adv->batch : 0);
 }
 
 

@@ -39,6 +39,17 @@ __device__ __forceinline__ uint32_t rope2_bf16(const float* __restrict__ x, cons
 
 // The step's own key (rotated) and value rows as the pages store them: lanes [0, HD/8) return the 16-byte chunk
 // `lane` of the key row, lanes [HD/8, HD/4) that of the value row; other lanes return zeros.
+// cos/sin rows of the step: the pointers themselves, or row *pos of the tables they point at
+template <int HD>
+__device__ __forceinline__ DecRope at_step_row(DecRope rp) {
+  if (rp.pos) {
+    const long long r = *rp.pos;
+    rp.cos += r * HD;
+    rp.sin += r * HD;
+  }
+  return rp;
+}
+
 template <int HD>
 __device__ __forceinline__ uint4 new_kv_chunk(const DecRope& rp, int b, int H, int KV, int kvh, int lane) {
   constexpr int CPR = HD / 8;

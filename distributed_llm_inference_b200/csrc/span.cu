@@ -341,9 +341,31 @@ size_t dli_span_workspace_bytes(const dli_span* span, int max_tokens, int max_ba
   return carve(span, nullptr, max_tokens, max_batch, max_ctx).total;
 }
 
+static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, int causal, const void* hidden_in,
+                             void* hidden_out, const float* cos, const float* sin, void* all_hidden, void* workspace,
+                             size_t workspace_bytes, dli_stream_t stream, const StepState& step);
+
 int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, int causal, const void* hidden_in,
                      void* hidden_out, const float* cos, const float* sin, void* all_hidden, void* workspace,
                      size_t workspace_bytes, dli_stream_t stream) {
+  const StepState none{nullptr, nullptr, nullptr, 0, false};
+  return span_forward_impl(s, kv, batch, q_len, causal, hidden_in, hidden_out, cos, sin, all_hidden, workspace,
+                           workspace_bytes, stream, none);
+}
+
+int dli_span_decode_step(dli_span* s, const dli_kv_desc* kv, int batch, const void* hidden_in, void* hidden_out,
+                         const float* cos_table, const float* sin_table, long long* position, int advance,
+                         void* workspace, size_t workspace_bytes, dli_stream_t stream) {
+  DLI_REQUIRE(kv && position, "dli_span_decode_step: null pointer");
+  const StepState step{position, static_cast<int*>(const_cast<void*>(static_cast<const void*>(kv->seq_lens))), position, batch,
+                       advance != 0};
+  return span_forward_impl(s, kv, batch, 1, 1, hidden_in, hidden_out, cos_table, sin_table, nullptr, workspace,
+                           workspace_bytes, stream, step);
+}
+
+static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, int causal, const void* hidden_in,
+                             void* hidden_out, const float* cos, const float* sin, void* all_hidden, void* workspace,
+                             size_t workspace_bytes, dli_stream_t stream, const StepState& step) {
   reset_launch_count();
   DLI_REQUIRE(s && kv && hidden_in && hidden_out && cos && sin && workspace, "dli_span_forward: null pointer");
   DLI_REQUIRE(batch > 0 && q_len > 0, "dli_span_forward: batch=%d q_len=%d", batch, q_len);
@@ -393,7 +415,7 @@ int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, i
       if (rc) return rc;
       // RoPE + cache append (modules.py:73-85, cache.py:103-109); re-zeroes the split-K accumulation buffer behind itself
       DLI_MARK(DLI_PROF_ROPE_APPEND);
-      rc = (DLI_SKIPPED(DLI_PROF_ROPE_APPEND) || fused_dec_rope) ? 0 : launch_rope_kv_append(qkv, skinny, cos, sin, w.qbuf, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim, st);
+      rc = (DLI_SKIPPED(DLI_PROF_ROPE_APPEND) || fused_dec_rope) ? 0 : launch_rope_kv_append(qkv, skinny, cos, sin, w.qbuf, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim, st, step.pos);
       if (rc) return rc;
     }
     // attention core (modules.py:87-105)
@@ -402,7 +424,7 @@ int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, i
       rc = 0;
     else if (q_len == 1)
     {
-      const DecRope dr{w.qkv_acc, cos, sin, s->n_qkv};
+      const DecRope dr{w.qkv_acc, cos, sin, s->n_qkv, step.pos};
       rc = launch_decode_attention(w.qbuf, w.attn, view, batch, d.n_heads, d.n_kv_heads, d.head_dim, w.dec_scratch,
                                    w.dec_scratch_bytes, st, /*early_kv=*/true, fused_dec_rope ? &dr : nullptr);
     }
@@ -429,8 +451,8 @@ int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, i
     if (rc) return rc;
   }
   DLI_MARK(DLI_PROF_CAST);
-  if ((rc = launch_cast(w.resid, static_cast<__nv_bfloat16*>(hidden_out), (long long)M * h, st))) return rc;
-  if (hs && (rc = launch_cast(w.resid, hs + (size_t)d.n_layers * M * h, (long long)M * h, st))) return rc;
+  if ((rc = launch_cast(w.resid, static_cast<__nv_bfloat16*>(hidden_out), (long long)M * h, st, hs ? nullptr : &step))) return rc;
+  if (hs && (rc = launch_cast(w.resid, hs + (size_t)d.n_layers * M * h, (long long)M * h, st, &step))) return rc;
   DLI_MARK(-1);
   return DLI_OK;
 }

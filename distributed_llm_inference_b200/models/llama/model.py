@@ -281,14 +281,15 @@ class GraphedDecode:
         self.pos = torch.tensor([gen.first_pos + gen.seen_tokens], dtype=torch.long, device=device)
         kv = cache.kv_desc(gen, max_ctx)
 
+        table = block._table                                                   # [2, max_positions, hd] fp32, model.py:55
+
         def launch():
-            cs = torch.index_select(block._table, 1, self.pos)                  # model.py:55
-            ffi.check(ffi.lib.dli_span_forward(block._span, C.byref(kv), B, 1, 1, self.x.data_ptr(), self.out.data_ptr(),
-                                               cs[0].data_ptr(), cs[1].data_ptr(), None, ws.data_ptr(), ws.numel(),
-                                               ffi.current_stream()))
-            gen.seq_lens.add_(1)
-            self.pos.add_(1)
-            return cs
+            # position and lengths live on the device: the kernels index the cos/sin tables by *pos and the span's last
+            # kernel advances pos and seq_lens, so a replayed step is nothing but the span's own PDL-chained kernels
+            ffi.check(ffi.lib.dli_span_decode_step(block._span, C.byref(kv), B, self.x.data_ptr(), self.out.data_ptr(),
+                                                   table[0].data_ptr(), table[1].data_ptr(), self.pos.data_ptr(), 1,
+                                                   ws.data_ptr(), ws.numel(), ffi.current_stream()))
+            return table
 
         # run the decode-path kernels once outside capture (one-time function attributes, descriptor caches) on a
         # throw-away generation; the capture itself launches nothing, so the live generation is untouched

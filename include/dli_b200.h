@@ -216,6 +216,19 @@ int dli_span_forward(dli_span* span, const dli_kv_desc* kv, int batch, int q_len
                      const void* hidden_in, void* hidden_out, const float* cos, const float* sin,
                      void* all_hidden, void* workspace, size_t workspace_bytes, dli_stream_t stream);
 
+/* One decode step (q_len == 1) whose bookkeeping lives on the device, for replay in a CUDA graph: the same kernels
+ * as dli_span_forward(..., q_len = 1, ...), but
+ *   - cos_table / sin_table are the WHOLE fp32 [max_positions, head_dim] tables and the kernels use row *position
+ *     (device int64) -- no gather launch in front of the step;
+ *   - advance != 0: the span's last kernel adds 1 to kv->seq_lens[b] for b < batch and to *position, so the next
+ *     replay sees the next token -- no length/position update launches behind the step.
+ * The caller keeps *position below max_positions (the host knows how many steps it replayed).
+ * Replaces, at decode, the per-call position/rotary set-up of LlamaBlock.forward (model.py:44-55) and the length
+ * bookkeeping of PartialLlamaSinkCache.update (cache.py:86-87,103-109). */
+int dli_span_decode_step(dli_span* span, const dli_kv_desc* kv, int batch, const void* hidden_in, void* hidden_out,
+                         const float* cos_table, const float* sin_table, long long* position, int advance,
+                         void* workspace, size_t workspace_bytes, dli_stream_t stream);
+
 /* Per-kernel-class timing of dli_span_forward, measured with CUDA events recorded on the call's own stream
  * at every class boundary (bench.py's roofline figures).  dli_span_profile(span, 1) starts collecting (host-side
  * cudaEvent objects are created on demand; no device memory); every forward after that appends intervals;
