@@ -53,7 +53,9 @@ def test_full_width_layers_match_oracle(shape_name, B, L):
         _check(f"{shape_name} decode {step}", got.float().cpu().numpy(), ref.numpy())
 
 
-@pytest.mark.parametrize("shape_name,B,T", [("7b", 16, 512), ("13b", 8, 512), ("70b", 4, 512), ("70b", 1, 2048)])
+# (70b, 32, 512) is the one where the unsplit GQA decode kernel also rotates q/k and appends (rope_inline.cuh)
+@pytest.mark.parametrize("shape_name,B,T", [("7b", 16, 512), ("13b", 8, 512), ("70b", 4, 512), ("70b", 1, 2048),
+                                            ("70b", 32, 512)])
 def test_bench_size_properties(shape_name, B, T):
     shp = syn.SHAPES[shape_name]
     W = syn.make_span_weights(shp, [0, 1], norm_jitter=0.1)
