@@ -387,83 +387,90 @@ static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int 
   __nv_bfloat16* hs = static_cast<__nv_bfloat16*>(all_hidden);
   int rc;
 
+  // one launch class of the step: timing mark, optional skip (DLI_DEBUG_SKIP), error propagation
+#define DLI_STEP(cls, call)                  \
+  do {                                       \
+    DLI_MARK(cls);                           \
+    rc = DLI_SKIPPED(cls) ? DLI_OK : (call); \
+    if (rc) return rc;                       \
+  } while (0)
+  const __nv_bfloat16* attn_in = w.qbuf;
+
   pdl_barrier_next_launch();  // the call's first kernel starts after everything already in the stream
   for (int j = 0; j < d.n_layers; ++j) {
     Layer& L = s->layers[j];
     KvView view;
     if ((rc = kv_view(kv, j, &view))) return rc;
-    // input_layernorm (modules.py:162); layer 0 also opens the fp32 residual stream
+    // input_layernorm (modules.py:162); layer 0 also opens the fp32 residual stream (and is never skipped)
     DLI_MARK(DLI_PROF_RMSNORM);
-    rc = DLI_SKIPPED(DLI_PROF_RMSNORM) && j != 0 ? 0 : launch_rmsnorm(j == 0 ? hidden_in : (const void*)w.resid, j != 0, (const __nv_bfloat16*)L.w.g_in, w.xn,
-                        j == 0 ? w.resid : nullptr, hs ? hs + (size_t)j * M * h : nullptr, M, h, d.eps_input, 1.0f, st);
-    if (rc) return rc;
-    // q|k|v projection (modules.py:61-63)
-    // prefill: RoPE + KV append are the epilogue of the projection GEMM (whole heads per 256-column tile)
+    if (j == 0 || !DLI_SKIPPED(DLI_PROF_RMSNORM)) {
+      rc = launch_rmsnorm(j == 0 ? hidden_in : (const void*)w.resid, j != 0, (const __nv_bfloat16*)L.w.g_in, w.xn,
+                          j == 0 ? w.resid : nullptr, hs ? hs + (size_t)j * M * h : nullptr, M, h, d.eps_input, 1.0f, st);
+      if (rc) return rc;
+    }
+    // q|k|v projection (modules.py:61-63), RoPE and cache append (modules.py:73-85, cache.py:103-109):
+    //   prefill  RoPE + append are the epilogue of the projection GEMM (whole heads per 256-column tile);
+    //   decode   split-K GEMM into the fp32 accumulation buffer, then either the RoPE/append kernel (which re-zeroes
+    //            the buffer behind itself) or, when the context is not split, the attention kernel does that work
+    //            itself (rope_inline.cuh) -- one launch less per layer.
     const bool fused_rope = !skinny && s->n_qkv % 256 == 0 && gemm_persistent_enabled();
-    bool fused_dec_rope = false;
-    DLI_MARK(DLI_PROF_GEMM_QKV);
+    const bool fused_dec_rope = !fused_rope && q_len == 1 && skinny &&
+                                decode_attention_fuses_rope(view, batch, d.n_heads, d.n_kv_heads, d.head_dim);
     if (fused_rope) {
       RopeArgs ra{cos, sin, w.qbuf, view, q_len, d.n_heads, d.n_kv_heads, d.head_dim};
-      rc = span_gemm(s, w.xn, L.qkv, nullptr, 0, M, s->n_qkv, h, DLI_EPI_QKV_ROPE_INTERNAL, st, &ra);
-      if (rc) return rc;
+      DLI_STEP(DLI_PROF_GEMM_QKV, span_gemm(s, w.xn, L.qkv, nullptr, 0, M, s->n_qkv, h, DLI_EPI_QKV_ROPE_INTERNAL, st, &ra));
     } else {
       float* qkv = skinny ? w.qkv_acc : w.qkv;
-      // decode with an unsplit context: the attention kernel rotates q and k, appends k and v and re-zeroes the
-      // accumulation rows itself (rope_inline.cuh) -- one launch less per layer
-      fused_dec_rope = q_len == 1 && skinny && decode_attention_fuses_rope(view, batch, d.n_heads, d.n_kv_heads, d.head_dim);
-      rc = DLI_SKIPPED(DLI_PROF_GEMM_QKV) ? 0 : span_gemm(s, w.xn, L.qkv, qkv, s->n_qkv, M, s->n_qkv, h, skinny ? DLI_EPI_ADD_F32 : DLI_EPI_STORE_F32, st);
-      if (rc) return rc;
-      // RoPE + cache append (modules.py:73-85, cache.py:103-109); re-zeroes the split-K accumulation buffer behind itself
+      DLI_STEP(DLI_PROF_GEMM_QKV, span_gemm(s, w.xn, L.qkv, qkv, s->n_qkv, M, s->n_qkv, h,
+                                            skinny ? DLI_EPI_ADD_F32 : DLI_EPI_STORE_F32, st));
       DLI_MARK(DLI_PROF_ROPE_APPEND);
-      rc = (DLI_SKIPPED(DLI_PROF_ROPE_APPEND) || fused_dec_rope) ? 0 : launch_rope_kv_append(qkv, skinny, cos, sin, w.qbuf, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim, st, step.pos);
-      if (rc) return rc;
+      if (!fused_dec_rope && !DLI_SKIPPED(DLI_PROF_ROPE_APPEND)) {
+        rc = launch_rope_kv_append(qkv, skinny, cos, sin, w.qbuf, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim,
+                                   st, step.pos);
+        if (rc) return rc;
+      }
     }
     // attention core (modules.py:87-105)
-    DLI_MARK(DLI_PROF_ATTENTION);
-    if (DLI_SKIPPED(DLI_PROF_ATTENTION))
-      rc = 0;
-    else if (q_len == 1)
-    {
+    if (q_len == 1) {
       const DecRope dr{w.qkv_acc, cos, sin, s->n_qkv, step.pos};
-      rc = launch_decode_attention(w.qbuf, w.attn, view, batch, d.n_heads, d.n_kv_heads, d.head_dim, w.dec_scratch,
-                                   w.dec_scratch_bytes, st, /*early_kv=*/true, fused_dec_rope ? &dr : nullptr);
+      DLI_STEP(DLI_PROF_ATTENTION,
+               launch_decode_attention(attn_in, w.attn, view, batch, d.n_heads, d.n_kv_heads, d.head_dim, w.dec_scratch,
+                                       w.dec_scratch_bytes, st, /*early_kv=*/true, fused_dec_rope ? &dr : nullptr));
+    } else {
+      DLI_STEP(DLI_PROF_ATTENTION, launch_prefill_attention(attn_in, w.attn, view, batch, q_len, d.n_heads, d.n_kv_heads,
+                                                            d.head_dim, causal != 0, st));
     }
-    else
-      rc = launch_prefill_attention(w.qbuf, w.attn, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim, causal != 0, st);
-    if (rc) return rc;
     // o_proj + residual (modules.py:112,173)
-    DLI_MARK(DLI_PROF_GEMM_O);
-    rc = DLI_SKIPPED(DLI_PROF_GEMM_O) ? 0 : span_gemm(s, w.attn, L.o, w.resid, h, M, h, qdim, DLI_EPI_ADD_F32, st);
-    if (rc) return rc;
+    DLI_STEP(DLI_PROF_GEMM_O, span_gemm(s, w.attn, L.o, w.resid, h, M, h, qdim, DLI_EPI_ADD_F32, st));
     // post_attention_layernorm of h + h (modules.py:179)
-    DLI_MARK(DLI_PROF_RMSNORM);
-    rc = DLI_SKIPPED(DLI_PROF_RMSNORM) ? 0 : launch_rmsnorm(w.resid, true, (const __nv_bfloat16*)L.w.g_post, w.xn, nullptr, nullptr, M, h, d.eps_post,
-                        d.post_prescale, st);
-    if (rc) return rc;
-    // MLP (modules.py:181): gate|up with silu*up, then down + residual (modules.py:182)
-    DLI_MARK(DLI_PROF_GEMM_GATE_UP);
-    // one kernel on both paths: silu(gate) * up is the GEMM epilogue (64 gate + 64 up weight rows per CTA at
-    // decode, 128 + 128 accumulator columns per CTA at prefill)
-    rc = DLI_SKIPPED(DLI_PROF_GEMM_GATE_UP) ? 0 : span_gemm(s, w.xn, L.gu, w.act, inter, M, inter, h, DLI_EPI_SILU_MUL_BF16, st);
-    if (rc) return rc;
-    DLI_MARK(DLI_PROF_GEMM_DOWN);
-    rc = DLI_SKIPPED(DLI_PROF_GEMM_DOWN) ? 0 : span_gemm(s, w.act, L.down, w.resid, h, M, h, inter, DLI_EPI_ADD_F32, st);
-    if (rc) return rc;
+    DLI_STEP(DLI_PROF_RMSNORM, launch_rmsnorm(w.resid, true, (const __nv_bfloat16*)L.w.g_post, w.xn, nullptr, nullptr, M, h,
+                                              d.eps_post, d.post_prescale, st));
+    // MLP (modules.py:181,182): gate|up with silu(gate) * up as the GEMM epilogue on both paths (64 gate + 64 up weight
+    // rows per CTA at decode, 128 + 128 accumulator columns per CTA pair at prefill), then down + residual
+    DLI_STEP(DLI_PROF_GEMM_GATE_UP, span_gemm(s, w.xn, L.gu, w.act, inter, M, inter, h, DLI_EPI_SILU_MUL_BF16, st));
+    DLI_STEP(DLI_PROF_GEMM_DOWN, span_gemm(s, w.act, L.down, w.resid, h, M, h, inter, DLI_EPI_ADD_F32, st));
   }
+#undef DLI_STEP
   DLI_MARK(DLI_PROF_CAST);
-  if ((rc = launch_cast(w.resid, static_cast<__nv_bfloat16*>(hidden_out), (long long)M * h, st, hs ? nullptr : &step))) return rc;
+  if ((rc = launch_cast(w.resid, static_cast<__nv_bfloat16*>(hidden_out), (long long)M * h, st, hs ? nullptr : &step)))
+    return rc;
   if (hs && (rc = launch_cast(w.resid, hs + (size_t)d.n_layers * M * h, (long long)M * h, st, &step))) return rc;
   DLI_MARK(-1);
   return DLI_OK;
 }
-
-
 
 }  // extern "C"
 
 #ifdef DLI_TRACE
 // trace builds only (DLI_TRACE=1 build.sh): point every translation unit's timeline buffer at `buf`
 // (word 0 = event counter, word 1 = capacity in events, then 2 words per event); null disables
-namespace dli { int trace_set_gemm(void*); int trace_set_norm(void*); int trace_set_attn(void*); int trace_set_attn_gqa(void*); }
-extern "C" int dli_debug_trace(void* buf) { return dli::trace_set_gemm(buf) | dli::trace_set_norm(buf) | dli::trace_set_attn(buf) | dli::trace_set_attn_gqa(buf); }
+namespace dli {
+int trace_set_gemm(void*);
+int trace_set_norm(void*);
+int trace_set_attn(void*);
+int trace_set_attn_gqa(void*);
+}  // namespace dli
+extern "C" int dli_debug_trace(void* buf) {
+  return dli::trace_set_gemm(buf) | dli::trace_set_norm(buf) | dli::trace_set_attn(buf) | dli::trace_set_attn_gqa(buf);
+}
 #endif
