@@ -310,7 +310,8 @@ def run_ours(args):
                    "kernel_ms": {c: round(v[0], 3) for c, v in pf_prof.items()}}
 
     # ---- decode: warm-up, then K timed steps ----
-    # one GPU: the whole stage step is one CUDA graph (LlamaBlock.graphed_decode); pipeline: eager + NCCL P2P
+    # one GPU: the whole stage step is one CUDA graph (LlamaBlock.graphed_decode); pipeline: one graph per stage and
+    # micro-batch with peer-store hand-off, then (after warm-up) one graph per stage and round
     xs = [syn.make_hidden(shape, BATCH, 1, seed=7 + m, device=dev) for m in range(n_mb)] if rank == 0 else None
     pos = PROMPT
     graph = None

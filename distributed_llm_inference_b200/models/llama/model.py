@@ -123,9 +123,11 @@ class LlamaBlock(nn.Module):
         """Capture ONE decode step (q_len = 1) of this span for a live generation into a CUDA graph.
 
         The reference hides decode launch latency with three small per-layer graphs (utils/cuda.py:6-77 used at
-        modules.py:28-34,130-144); here the whole stage step — every kernel of every layer plus the rotary-table
-        gather and the length update — is one graph.  Everything that changes between steps (sequence lengths,
-        block table, position) lives in device memory, so the graph is replayed unchanged until ``max_ctx`` tokens.
+        modules.py:28-34,130-144); here the whole stage step — every kernel of every layer, nothing else — is one
+        graph (``dli_span_decode_step``).  Everything that changes between steps (sequence lengths, block table,
+        position) lives in device memory: the kernels read the step's cos/sin row at the device-resident position and
+        the span's last kernel advances position and lengths, so the graph is replayed unchanged until ``max_ctx``
+        tokens.
         ``x`` / ``out`` (optional, bf16 ``[B, 1, h]``) replace the graph's own static input / output buffers; ``out`` may
         be a peer GPU's mapped memory, in which case the span's last kernel stores the hand-off tensor straight into
         the next pipeline stage's input over NVLink.
