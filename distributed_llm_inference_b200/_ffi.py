@@ -100,7 +100,7 @@ def check(rc: int) -> None:
         raise DliError(f"libdli_b200 error {rc}: {lib.dli_last_error().decode(errors='replace')}")
 
 
-def current_stream() -> int:
+def current_stream(device=None) -> int:
     import torch
 
-    return torch.cuda.current_stream().cuda_stream
+    return torch.cuda.current_stream(device).cuda_stream

@@ -43,7 +43,7 @@ static int decode_splits(int batch, int KV, int max_ctx, int slots) {
 static int decode_splits_for(const KvView& kv, int batch, int H, int KV, int hd) {
   const int G = H / KV;
   const bool gqa = decode_attn_gqa_supported(kv, G, hd);
-  const bool direct_env = getenv("DLI_DEC_DIRECT") != nullptr;
+  const bool direct_env = exp_env("DLI_DEC_DIRECT") != nullptr;
   // co-resident CTAs per SM: 2 for the tensor-core GQA kernel (96 KB ring) and the register-staged fallback, 4 for
   // the staged kernel (48 KB ring, 70 registers) as long as its register-file share allows (G <= 2)
   const int per_sm = gqa ? 2 : (direct_env || G > 2) ? 2 : 4;
@@ -478,18 +478,14 @@ template <int HD, int G>
 static int launch_dec(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV, int splits,
                       float* scratch, bool early_kv, const DecRope& rope, cudaStream_t st) {
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
-  static const bool direct = getenv("DLI_DEC_DIRECT") != nullptr;  // A/B switch for the register-staged kernel
+  static const bool direct = exp_env("DLI_DEC_DIRECT") != nullptr;  // A/B switch for the register-staged kernel
   int rc;
   if (direct) {
     rc = launch_kernel("decode_attn_direct_kernel", decode_attn_direct_kernel<HD, G>, dim3(splits, KV, batch),
                        dim3(DEC_THREADS), 0, st, q, kv, scratch, out, H, KV, scale_log2);
   } else {
-    static bool attr_set = false;  // > 48 KB of dynamic shared memory needs the opt-in once per instantiation
-    if (!attr_set) {
-      DLI_CUDA_OK(cudaFuncSetAttribute(decode_attn_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       dec_smem_bytes<HD, G>()));
-      attr_set = true;
-    }
+    DLI_ONCE_PER_DEVICE(cudaFuncSetAttribute(decode_attn_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       dec_smem_bytes<HD, G>()));  // > 48 KB dynamic shared memory: opt-in per device
     rc = launch_kernel("decode_attn_kernel", decode_attn_kernel<HD, G>, dim3(splits, KV, batch),
                        dim3(DEC_THREADS_STAGED), dec_smem_bytes<HD, G>(), st, q, kv, scratch, out, H, KV, scale_log2,
                        early_kv ? 1 : 0, rope);
@@ -502,7 +498,7 @@ static int launch_dec(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& 
 // One CTA per (sequence, KV head) is the only reader of that head's projection and the only writer of its page slot:
 // the condition under which the attention kernel can do the RoPE kernel's work.
 bool decode_attention_fuses_rope(const KvView& kv, int batch, int H, int KV, int hd) {
-  static const bool off = getenv("DLI_DEC_DIRECT") != nullptr || getenv("DLI_NO_ROPE_FUSE") != nullptr;
+  static const bool off = exp_env("DLI_DEC_DIRECT") != nullptr || exp_env("DLI_NO_ROPE_FUSE") != nullptr;
   if (off || KV <= 0 || H % KV != 0 || !(hd == 64 || hd == 128)) return false;
   const int G = H / KV;
   if (!(G == 1 || G == 2 || G == 4 || G == 8)) return false;
@@ -559,7 +555,6 @@ int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const Kv
 constexpr size_t DLI_STATIC_SCRATCH_BYTES = (size_t)8 << 20;  // 8 MiB
 static __device__ __align__(256) float g_decode_scratch[DLI_STATIC_SCRATCH_BYTES / sizeof(float)];
 
-constexpr int DLI_MAX_DEVICES = 64;
 static float* g_decode_scratch_addr[DLI_MAX_DEVICES] = {nullptr};
 
 static int static_scratch_for_current_device(float** out) {

@@ -283,7 +283,7 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
 }
 
 bool decode_attn_gqa_supported(const KvView& kv, int G, int hd) {
-  static const bool off = getenv("DLI_DEC_DIRECT") != nullptr || getenv("DLI_DEC_NO_MMA") != nullptr;
+  static const bool off = exp_env("DLI_DEC_DIRECT") != nullptr || exp_env("DLI_DEC_NO_MMA") != nullptr;
   if (off) return false;
   if (!(G == 2 || G == 4 || G == 8) || !(hd == 64 || hd == 128)) return false;
   const int pt = kv.page_tokens;
@@ -294,12 +294,8 @@ template <int HD, int G>
 static int launch_gqa(const CUtensorMap& tk, const CUtensorMap& tv, const __nv_bfloat16* q, __nv_bfloat16* out,
                       const KvView& kv, int batch, int H, int KV, int splits, float* scratch, bool early_kv,
                       const DecRope& rope, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    DLI_CUDA_OK(cudaFuncSetAttribute(decode_attn_gqa_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     gq_smem_bytes<HD, G>()));
-    attr_set = true;
-  }
+  DLI_ONCE_PER_DEVICE(cudaFuncSetAttribute(decode_attn_gqa_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     gq_smem_bytes<HD, G>()));  // > 48 KB dynamic shared memory: opt-in per device
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
   return launch_kernel("decode_attn_gqa_kernel", decode_attn_gqa_kernel<HD, G>, dim3(splits, KV, batch), dim3(GQ_THREADS),
                        (size_t)gq_smem_bytes<HD, G>(), st, tk, tv, q, kv, scratch, out, H, KV, scale_log2, early_kv ? 1 : 0, rope);

@@ -221,11 +221,7 @@ static int launch_pf(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& k
                      bool causal, cudaStream_t st) {
   constexpr int BM = NWARPS * 16;
   const size_t smem = (size_t)(BM + 2 * NBUF * PF_BN) * HD * 2;
-  static bool configured = false;
-  if (!configured) {
-    DLI_CUDA_OK(cudaFuncSetAttribute(prefill_attn_kernel<HD, NWARPS, NBUF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
-  }
+  DLI_ONCE_PER_DEVICE(cudaFuncSetAttribute(prefill_attn_kernel<HD, NWARPS, NBUF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));  // > 48 KB dynamic shared memory: opt-in per device
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
   dim3 grid((q_len + BM - 1) / BM, H, batch);
   return launch_kernel("prefill_attn_kernel", prefill_attn_kernel<HD, NWARPS, NBUF>, grid, dim3(NWARPS * 32), smem, st, q, out, kv,
@@ -242,7 +238,7 @@ int launch_prefill_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const K
   if (q_len >= 16 && prefill_attn_tc_supported(kv, hd)) return launch_prefill_attention_tc(q, out, kv, batch, q_len, H, KV, causal, st);
   static int force = -1;
   if (force < 0) {
-    const char* e = getenv("DLI_PF_WARPS");
+    const char* e = exp_env("DLI_PF_WARPS");
     force = e ? atoi(e) : 0;
   }
   // measured on B200 (70B shape, 8k tokens): 4 warps + single K/V buffer (48 KB, 3 CTAs/SM) 68.7 ms per 10 layers,

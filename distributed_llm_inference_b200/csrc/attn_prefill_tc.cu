@@ -338,7 +338,7 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
 bool prefill_attn_tc_supported(const KvView& kv, int hd) {
   static int legacy = -1;
   if (legacy < 0) {
-    const char* e = getenv("DLI_ATTN_LEGACY");
+    const char* e = exp_env("DLI_ATTN_LEGACY");
     legacy = (e && e[0] == '1') ? 1 : 0;
   }
   return !legacy && hd == FA_HD && kv.page_tokens >= 8 && kv.page_tokens % 8 == 0 && FA_BN % kv.page_tokens == 0;
@@ -352,11 +352,7 @@ int launch_prefill_attention_tc(const __nv_bfloat16* q, __nv_bfloat16* out, cons
   const long long pool_rows = (long long)kv.n_pages * KV * kv.page_tokens;
   if ((rc = make_tmap_bf16(&tk, kv.k, pool_rows, FA_HD, FA_HD, kv.page_tokens))) return rc;
   if ((rc = make_tmap_bf16(&tv, kv.v, pool_rows, FA_HD, FA_HD, kv.page_tokens))) return rc;
-  static bool configured = false;
-  if (!configured) {
-    DLI_CUDA_OK(cudaFuncSetAttribute(prefill_attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM));
-    configured = true;
-  }
+  DLI_ONCE_PER_DEVICE(cudaFuncSetAttribute(prefill_attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM));  // > 48 KB dynamic shared memory: opt-in per device
   FaParams p{};
   p.out = out;
   p.block_table = kv.block_table;
@@ -369,7 +365,7 @@ int launch_prefill_attention_tc(const __nv_bfloat16* q, __nv_bfloat16* out, cons
   p.causal = causal ? 1 : 0;
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)FA_HD);
   {
-    const char* e = getenv("DLI_FA_DBG_PTR");  // experiments: device pointer (hex) receiving cycle counters
+    const char* e = exp_env("DLI_FA_DBG_PTR");  // experiments: device pointer (hex) receiving cycle counters
     p.dbg = e ? reinterpret_cast<unsigned long long*>(strtoull(e, nullptr, 16)) : nullptr;
   }
   dim3 grid((q_len + FA_BM - 1) / FA_BM, H, batch);

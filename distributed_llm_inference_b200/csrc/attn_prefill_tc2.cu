@@ -380,10 +380,10 @@ prefill_attn_tc2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_
 }
 
 bool prefill_attn_tc2_supported(const KvView& kv, int hd, int q_len) {
-  static const bool off = getenv("DLI_FA_V1") != nullptr || (getenv("DLI_ATTN_LEGACY") && getenv("DLI_ATTN_LEGACY")[0] == '1');
+  static const bool off = exp_env("DLI_FA_V1") != nullptr || (exp_env("DLI_ATTN_LEGACY") && exp_env("DLI_ATTN_LEGACY")[0] == '1');
   // Long chunks only: with few key tiles per CTA the one-CTA-per-SM kernel pays its fill and drain (16 x 512 tokens:
   // 5.6 ms against 4.6 ms for attn_prefill_tc.cu); at 8k it is ~10 % faster inside the stage (20.0 vs 22.3 ms per 10 layers).
-  static const int min_q = getenv("DLI_FA_V2_MIN_Q") ? atoi(getenv("DLI_FA_V2_MIN_Q")) : 2048;
+  static const int min_q = exp_env("DLI_FA_V2_MIN_Q") ? atoi(exp_env("DLI_FA_V2_MIN_Q")) : 2048;
   return !off && hd == F2_HD && q_len >= min_q && q_len >= 2 * F2_BM && kv.page_tokens >= 8 && kv.page_tokens % 8 == 0 &&
          F2_BN % kv.page_tokens == 0;
 }
@@ -396,11 +396,7 @@ int launch_prefill_attention_tc2(const __nv_bfloat16* q, __nv_bfloat16* out, con
   const long long pool_rows = (long long)kv.n_pages * KV * kv.page_tokens;
   if ((rc = make_tmap_bf16(&tk, kv.k, pool_rows, F2_HD, F2_HD, kv.page_tokens))) return rc;
   if ((rc = make_tmap_bf16(&tv, kv.v, pool_rows, F2_HD, F2_HD, kv.page_tokens))) return rc;
-  static bool configured = false;
-  if (!configured) {
-    DLI_CUDA_OK(cudaFuncSetAttribute(prefill_attn_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, F2_SMEM));
-    configured = true;
-  }
+  DLI_ONCE_PER_DEVICE(cudaFuncSetAttribute(prefill_attn_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, F2_SMEM));  // > 48 KB dynamic shared memory: opt-in per device
   Fa2Params p{};
   p.out = out;
   p.block_table = kv.block_table;
@@ -413,7 +409,7 @@ int launch_prefill_attention_tc2(const __nv_bfloat16* q, __nv_bfloat16* out, con
   p.causal = causal ? 1 : 0;
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)F2_HD);
   {
-    const char* e = getenv("DLI_FA_DBG_PTR");  // experiments: device pointer (hex) receiving cycle counters
+    const char* e = exp_env("DLI_FA_DBG_PTR");  // experiments: device pointer (hex) receiving cycle counters
     p.dbg = e ? reinterpret_cast<unsigned long long*>(strtoull(e, nullptr, 16)) : nullptr;
   }
   dim3 grid((q_len + 2 * F2_BM - 1) / (2 * F2_BM), H, batch);

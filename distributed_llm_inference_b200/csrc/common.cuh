@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../../include/dli_b200.h"
 
@@ -38,8 +39,34 @@ void reset_launch_count();
     if (!(cond)) return ::dli::fail(DLI_ERR_ARG, __VA_ARGS__);   \
   } while (0)
 
-int sm_count();  // SMs of the current device (cached)
-bool pdl_enabled();  // programmatic dependent launch for the span's kernel chain (DLI_NO_PDL=1 turns it off)
+int sm_count();  // SMs of the current device (cached per device)
+bool pdl_enabled();  // programmatic dependent launch for the span's kernel chain
+
+// A/B and timing switches read from the environment exist only in experiment builds (DLI_EXPERIMENTS=1 build.sh ->
+// libdli_b200_exp.so, loaded with DLI_LIB); the product library never looks at the environment.
+#ifdef DLI_EXPERIMENTS
+inline const char* exp_env(const char* name) { return getenv(name); }
+#else
+inline const char* exp_env(const char*) { return nullptr; }
+#endif
+
+// One-time set-up that CUDA keeps PER DEVICE (function attributes such as the > 48 KB dynamic shared memory
+// opt-in): `slot` is a static array owned by the call site (one per kernel instantiation).
+constexpr int DLI_MAX_DEVICES = 64;
+struct OncePerDevice {
+  bool done[DLI_MAX_DEVICES] = {};
+};
+int current_device(int* dev);  // cudaGetDevice with range check against DLI_MAX_DEVICES
+#define DLI_ONCE_PER_DEVICE(expr)                        \
+  do {                                                   \
+    static ::dli::OncePerDevice _once;                   \
+    int _dev = 0;                                        \
+    if (int _rc = ::dli::current_device(&_dev)) return _rc; \
+    if (!_once.done[_dev]) {                             \
+      DLI_CUDA_OK(expr);                                 \
+      _once.done[_dev] = true;                           \
+    }                                                    \
+  } while (0)
 // The next launch_kernel() of this thread is launched WITHOUT the attribute, i.e. it starts only when everything
 // before it in the stream has completed.  dli_span_forward does this for its first kernel, which bounds how far
 // back a pre-wait prologue can overlap: nothing launched before the current forward call is still running when

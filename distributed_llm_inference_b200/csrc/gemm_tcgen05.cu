@@ -784,12 +784,8 @@ template <int BN, int EPI, bool SWAP>
 static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, dim3 grid, cudaStream_t st) {
   constexpr int STAGE_BYTES = A_TILE_BYTES + BN * BK * 2;
   const size_t smem = (size_t)p.stages * STAGE_BYTES + 1024;
-  static bool configured = false;  // per instantiation
   auto kern = gemm_tcgen05_kernel<BN, EPI, SWAP>;
-  if (!configured) {
-    DLI_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
-    configured = true;
-  }
+  DLI_ONCE_PER_DEVICE(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));  // > 48 KB dynamic shared memory: opt-in per device
   return launch_kernel("gemm_tcgen05_kernel", kern, grid, dim3(GEMM_THREADS), smem, st, ta, tb, p);
 }
 
@@ -798,17 +794,13 @@ static int launch_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const
                              cudaStream_t st) {
   constexpr int STAGE_BYTES = A_TILE_BYTES + BN * BK * 2;
   const size_t smem = (size_t)p.stages * STAGE_BYTES + 1024;
-  static bool configured = false;
   auto kern = gemm_tcgen05_persistent_kernel<BN, EPI>;
-  if (!configured) {
-    DLI_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
-    configured = true;
-  }
+  DLI_ONCE_PER_DEVICE(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));  // > 48 KB dynamic shared memory: opt-in per device
   const int n_tiles = tiles_m * tiles_n;
   const int grid = n_tiles < sm_count() ? n_tiles : sm_count();
   static int group_env = -1;
   if (group_env < 0) {
-    const char* e = getenv("DLI_GROUP_M");
+    const char* e = exp_env("DLI_GROUP_M");
     group_env = e ? atoi(e) : 0;
   }
   // band height: activations of a band (group_m x 128 tokens x K) should fit comfortably in one die's share of L2
@@ -822,7 +814,7 @@ static int launch_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const
 static bool pair_enabled() {
   static int v = -1;
   if (v < 0) {
-    const char* e = getenv("DLI_NO_PAIR");
+    const char* e = exp_env("DLI_NO_PAIR");
     v = (e && e[0] == '1') ? 0 : 1;
   }
   return v == 1;
@@ -835,19 +827,15 @@ static int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   GemmParams p = p_in;
   p.stages = std::min(6, std::max(2, p.k_blocks));
   const size_t smem = (size_t)p.stages * PAIR_STAGE_BYTES + 1024;
-  static bool configured = false;
   auto kern = gemm_tcgen05_pair_kernel<EPI>;
-  if (!configured) {
-    DLI_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
-    configured = true;
-  }
+  DLI_ONCE_PER_DEVICE(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));  // > 48 KB dynamic shared memory: opt-in per device
   const int n_tiles = tiles_m * tiles_n;
   const int pairs = std::min(n_tiles, sm_count() / 2);
   int group_m = 8;  // bands of 8 x 256 tokens: the same 2048-token activation band as the single-CTA kernel
   {
     static int group_env = -1;
     if (group_env < 0) {
-      const char* e = getenv("DLI_GROUP_M");
+      const char* e = exp_env("DLI_GROUP_M");
       group_env = e ? atoi(e) : 0;
     }
     if (group_env > 0) group_m = std::max(1, group_env / 2);
@@ -883,7 +871,7 @@ static int launch_persistent_epi(int epi, const CUtensorMap& ta, const CUtensorM
 static bool persistent_enabled() {
   static int v = -1;
   if (v < 0) {
-    const char* e = getenv("DLI_NO_PERSISTENT");
+    const char* e = exp_env("DLI_NO_PERSISTENT");
     v = (e && e[0] == '1') ? 0 : 1;
   }
   return v == 1;
@@ -917,9 +905,9 @@ GemmPlan plan_gemm(int m, int n, int k, int epilogue) {
       // two co-resident CTAs per SM keep ~200 KB of weight tiles in flight per SM; every split keeps >= 4 k-blocks
       static int min_kb = 0, ctas_per_sm_x2 = 0;
       if (!min_kb) {
-        const char* e = getenv("DLI_MIN_KB");
+        const char* e = exp_env("DLI_MIN_KB");
         min_kb = e ? max(1, atoi(e)) : 4;
-        const char* f = getenv("DLI_FILL_X2");
+        const char* f = exp_env("DLI_FILL_X2");
         ctas_per_sm_x2 = f ? max(1, atoi(f)) : 4;  // target CTAs per SM, times two
       }
       const int want = (ctas_per_sm_x2 * sms / 2) / tiles;

@@ -30,20 +30,28 @@ int fail(int code, const char* fmt, ...) {
 void count_launch(int n) { g_launches += n; }
 void reset_launch_count() { g_launches = 0; }
 
+int current_device(int* dev) {
+  DLI_CUDA_OK(cudaGetDevice(dev));
+  if (*dev < 0 || *dev >= DLI_MAX_DEVICES) return fail(DLI_ERR_UNSUPPORTED, "device ordinal %d outside [0, %d)", *dev, DLI_MAX_DEVICES);
+  return DLI_OK;
+}
+
 int sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-      n = 148;
+  static int n[DLI_MAX_DEVICES] = {};
+  int dev = 0;
+  if (current_device(&dev) != DLI_OK) return 148;
+  if (n[dev] == 0) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+    n[dev] = v;
   }
-  return n;
+  return n[dev];
 }
 
 bool pdl_enabled() {
   static int v = -1;
   if (v < 0) {
-    const char* e = getenv("DLI_NO_PDL");
+    const char* e = exp_env("DLI_NO_PDL");
     v = (e && e[0] == '1') ? 0 : 1;
   }
   return v == 1;
@@ -380,10 +388,14 @@ static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int 
   cudaStream_t st = (cudaStream_t)stream;
   const int h = d.hidden_size, inter = d.intermediate_size, qdim = d.n_heads * d.head_dim;
   const bool skinny = M <= 128;  // weight-streaming GEMM path accumulates into pre-zeroed fp32 buffers
-  // timing experiments only (results are garbage): bit c set in DLI_DEBUG_SKIP drops every launch of dli_prof_class c,
-  // which measures what that class costs inside the PDL-chained, graph-replayed step
+  // experiment builds only (DLI_EXPERIMENTS; results are garbage): bit c set in DLI_DEBUG_SKIP drops every launch of
+  // dli_prof_class c, which measures what that class costs inside the PDL-chained, graph-replayed step
+#ifdef DLI_EXPERIMENTS
   static const unsigned skip_mask = getenv("DLI_DEBUG_SKIP") ? (unsigned)strtoul(getenv("DLI_DEBUG_SKIP"), nullptr, 0) : 0u;
 #define DLI_SKIPPED(cls) (skip_mask & (1u << (cls)))
+#else
+#define DLI_SKIPPED(cls) false
+#endif
   __nv_bfloat16* hs = static_cast<__nv_bfloat16*>(all_hidden);
   int rc;
 

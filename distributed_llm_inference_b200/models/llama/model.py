@@ -61,6 +61,8 @@ class LlamaBlock(nn.Module):
         self.rope_theta = float(rp.get("rope_theta", getattr(config, "rope_theta", 10000.0)))
         if rp.get("rope_type", "default") != "default":
             raise NotImplementedError("only rope_type='default' is implemented")
+        # rows of the cos/sin table; grown on demand (the reference computes cos/sin for arbitrary positions, model.py:55,
+        # so its sink cache keeps generating past max_position_embeddings)
         self.max_positions = int(getattr(config, "max_position_embeddings", 4096))
         self._span = None           # dli_span* (ctypes void pointer)
         self._bound_ptrs = None
@@ -107,6 +109,18 @@ class LlamaBlock(nn.Module):
                 self._ffi().lib.dli_span_destroy(self._span)
         except Exception:
             pass
+
+    def _rope_table(self, device, min_rows: int = 0) -> torch.Tensor:
+        """``[2, rows, hd]`` fp32 cos/sin table on ``device`` with at least ``min_rows`` rows (doubling growth; a captured
+        decode graph holds pointers into the table it was captured with, so ``GraphedDecode`` keeps its own reference)."""
+        t = self._table
+        if t is None or t.device != device or t.shape[1] < min_rows:
+            rows = self.max_positions
+            while rows < min_rows:
+                rows *= 2
+            self.max_positions = rows
+            self._table = t = rope_table(self.head_dim, self.rope_theta, rows, self.rope, device)
+        return t
 
     def _workspace(self, tokens: int, batch: int, max_ctx: int, device) -> torch.Tensor:
         key = self._ws_key
@@ -185,7 +199,8 @@ class LlamaBlock(nn.Module):
         B, L, h = hidden_states.shape
         if h != self.config.hidden_size:
             raise ValueError(f"hidden size {h} != config.hidden_size {self.config.hidden_size}")
-        self._ensure_span(device)
+        with torch.cuda.device(device):
+            self._ensure_span(device)
 
         cache = past_key_value
         gid = generation_id
@@ -215,9 +230,19 @@ class LlamaBlock(nn.Module):
                              "position vector over the batch (modules.py:17-20)")
         causal = self._causal_flag(attention_mask, L, past)
 
-        if self._table is None or self._table.device != device:
-            self._table = rope_table(self.head_dim, self.rope_theta, self.max_positions, self.rope, device)
-        cs = torch.index_select(self._table, 1, position_ids[0].to(device))       # [2, L, hd] fp32 (model.py:55)
+        # positions of a generation are contiguous (the reference's sink cache assumes the same for its cos/sin history,
+        # cache.py:91-101), so the host knows an upper bound without reading the device tensor: the table is grown to
+        # cover it and the gather index is clamped, so an out-of-range id can never fault on the device
+        explicit_pos = cache_position_given or position_ids_given
+        first_call = gen is None or (gen.length == 0 and gen.seen_tokens == 0)
+        if first_call:
+            first_pos = int(position_ids[0, 0].item()) if explicit_pos else 0   # once per generation
+        else:
+            first_pos = gen.first_pos
+        seen = 0 if gen is None else gen.seen_tokens
+        table = self._rope_table(device, first_pos + seen + L)
+        idx = position_ids[0].to(device).clamp(0, table.shape[1] - 1)
+        cs = torch.index_select(table, 1, idx)                                      # [2, L, hd] fp32 (model.py:55)
 
         if gen is None:
             pass
@@ -226,25 +251,26 @@ class LlamaBlock(nn.Module):
                 raise NotImplementedError("a multi-token chunk that overflows window_length is not supported by the "
                                           "B200 span (the reference's mask becomes position-dependent there)")
             p0, W = gen.first_pos, cache.window_length
-            if p0 + W > self._table.shape[1]:
-                raise ValueError("cos/sin history exceeds max_position_embeddings")
-            cache.evict(gid, L, self._table[0, p0:p0 + W], self._table[1, p0:p0 + W])
+            table = self._rope_table(device, p0 + W)
+            cache.evict(gid, L, table[0, p0:p0 + W], table[1, p0:p0 + W])
             past = gen.length
         gen = cache.reserve(gid, B, past + L)
-        if gen.first_pos + gen.seen_tokens + L > self.max_positions and (gen.length or gen.seen_tokens):
-            raise ValueError(f"position {gen.first_pos + gen.seen_tokens + L} exceeds max_position_embeddings="
-                             f"{self.max_positions} (the rotary table)")
-        if gen.length == 0 and gen.seen_tokens == 0:
-            gen.first_pos = int(position_ids[0, 0].item()) if (cache_position_given or position_ids_given) else 0
+        if first_call:
+            gen.first_pos = first_pos
         max_ctx = past + L
-        ws = self._workspace(B * L, B, max_ctx, device)
         x = hidden_states.contiguous()
         out = torch.empty_like(x)
         all_h = torch.empty(len(self.layers) + 1, B, L, h, dtype=x.dtype, device=device) if output_hidden_states else None
         kv = cache.kv_desc(gen, max_ctx)
-        ffi.check(ffi.lib.dli_span_forward(
-            self._span, C.byref(kv), B, L, causal, x.data_ptr(), out.data_ptr(), cs[0].data_ptr(), cs[1].data_ptr(),
-            all_h.data_ptr() if all_h is not None else None, ws.data_ptr(), ws.numel(), ffi.current_stream()))
+        with torch.cuda.device(device):                  # kernels launch on the tensors' device, whatever is current
+            ws = self._workspace(B * L, B, max_ctx, device)
+            try:
+                ffi.check(ffi.lib.dli_span_forward(
+                    self._span, C.byref(kv), B, L, causal, x.data_ptr(), out.data_ptr(), cs[0].data_ptr(), cs[1].data_ptr(),
+                    all_h.data_ptr() if all_h is not None else None, ws.data_ptr(), ws.numel(), ffi.current_stream(device)))
+            except ffi.DliError:
+                self._ws = None                          # a chain that stopped half-way leaves partial sums behind: the
+                raise                                    # next call gets a freshly zeroed workspace (include/dli_b200.h)
         self.last_launch_count = ffi.lib.dli_last_launch_count()
         cache.advance(gid, L)
         if past_key_value is None:
@@ -271,10 +297,10 @@ class GraphedDecode:
         if max_ctx >= cache.window_length:
             raise ValueError("graphed decode cannot cross window_length (eviction is a separate launch)")
         cache.reserve(generation_id, B, max_ctx)                    # block table fixed for the graph's lifetime
-        block._ensure_span(device)
-        if block._table is None or block._table.device != device:
-            block._table = rope_table(block.head_dim, block.rope_theta, block.max_positions, block.rope, device)
-        ws = block._workspace(B, B, max_ctx, device)
+        with torch.cuda.device(device):
+            block._ensure_span(device)
+            ws = block._workspace(B, B, max_ctx, device)
+        table = block._rope_table(device, gen.first_pos + gen.seen_tokens + (max_ctx - gen.length) + 1)
         for t in (x, out):
             if t is not None and (tuple(t.shape) != (B, 1, h) or t.dtype != torch.bfloat16 or not t.is_contiguous()):
                 raise ValueError(f"graphed_decode buffers must be contiguous bf16 [{B}, 1, {h}]")
@@ -283,15 +309,18 @@ class GraphedDecode:
         self.pos = torch.tensor([gen.first_pos + gen.seen_tokens], dtype=torch.long, device=device)
         kv = cache.kv_desc(gen, max_ctx)
 
-        table = block._table                                                   # [2, max_positions, hd] fp32, model.py:55
-
+        self.device = device
         def launch():
             # position and lengths live on the device: the kernels index the cos/sin tables by *pos and the span's last
             # kernel advances pos and seq_lens, so a replayed step is nothing but the span's own PDL-chained kernels
-            ffi.check(ffi.lib.dli_span_decode_step(block._span, C.byref(kv), B, self.x.data_ptr(), self.out.data_ptr(),
-                                                   table[0].data_ptr(), table[1].data_ptr(), self.pos.data_ptr(), 1,
-                                                   ws.data_ptr(), ws.numel(), ffi.current_stream()))
-            return table
+            try:
+                ffi.check(ffi.lib.dli_span_decode_step(block._span, C.byref(kv), B, self.x.data_ptr(), self.out.data_ptr(),
+                                                       table[0].data_ptr(), table[1].data_ptr(), self.pos.data_ptr(), 1,
+                                                       ws.data_ptr(), ws.numel(), ffi.current_stream(device)))
+            except ffi.DliError:
+                block._ws = None
+                raise
+            return table, ws
 
         # run the decode-path kernels once outside capture (one-time function attributes, descriptor caches) on a
         # throw-away generation; the capture itself launches nothing, so the live generation is untouched
@@ -301,7 +330,7 @@ class GraphedDecode:
         torch.cuda.synchronize(device)
         self._launch = launch         # PipelineStage.capture_round re-captures the same launches into a round graph
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        with torch.cuda.device(device), torch.cuda.graph(self.graph):
             self._keep = launch()
         self.launches = ffi.lib.dli_last_launch_count()
         self._len = gen.length        # host mirror of the device-side position

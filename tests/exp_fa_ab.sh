@@ -1,6 +1,8 @@
 #!/usr/bin/env bash
 # same-box A/B of the two tcgen05 prefill attention kernels (DLI_FA_V1=1 selects the first generation)
 mkdir -p gpurun_out
+# environment switches exist only in the experiment build: DLI_EXPERIMENTS=1 distributed_llm_inference_b200/csrc/build.sh
+export DLI_LIB=${DLI_LIB:-$(pwd)/distributed_llm_inference_b200/csrc/libdli_b200_exp.so}
 for rep in 1 2; do
   for v1 in "" 1; do
     if [ -n "$v1" ]; then export DLI_FA_V1=1; else unset DLI_FA_V1; fi

@@ -177,3 +177,27 @@ def test_greedy_c1_matches_reference(case):
     # steps whose margin is below twice the measured logit error are reported, not asserted.
     assert agree_tf[margin > 2 * max(err, top_err)].all()
     assert agree_tf.sum() >= case.n_new - 4
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_two_spans_on_two_devices_in_one_process():
+    """Function attributes (the > 48 KB shared-memory opt-in) and the SM count are per device, and the kernels launch on
+    the device of the tensors, not on whichever device is current: a client that drives two spans on two GPUs from
+    one process (client.py hand_off) gets oracle-exact results from both."""
+    shp = syn.SHAPES["test_hd128"]
+    W = syn.make_span_weights(shp, [0, 1, 2, 3], norm_jitter=0.1)
+    osp = oracle_make_span(shp, W, "eager", "float")
+    spans = [gpu_make_span(shp, W[:2], "eager", "float").to("cuda:0"),
+             gpu_make_span(shp, W[2:], "eager", "float", first_layer=2).to("cuda:1")]
+    caches = [gpu_make_cache(4096, 4), gpu_make_cache(4096, 4)]
+    oc = so.SinkCacheOracle(4096, 4)
+    pos = 0
+    for step, L in enumerate([140, 1, 1]):
+        x = syn.make_hidden(shp, 2, L, seed=70 + step)
+        cp = torch.arange(pos, pos + L)
+        ref = osp.forward("g", x.float(), past_key_value=oc, cache_position=cp)[0]
+        h = x.to("cuda:0")
+        h = spans[0]("g", h, past_key_value=caches[0], cache_position=cp.to("cuda:0"))[0]
+        h = spans[1]("g", h.to("cuda:1"), past_key_value=caches[1], cache_position=cp.to("cuda:1"))[0]
+        _check(f"two-device step {step}", h.float().cpu().numpy(), ref.numpy())
+        pos += L

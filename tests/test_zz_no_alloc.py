@@ -6,8 +6,9 @@ out-of-memory failure when the pool is full) in the middle of a request is not a
 its split-K partials in an 8 MiB array compiled into the library instead.
 
 The test drives it through the C ABI twice in a row, with different inputs, and compares each result with the
-ordinary entry point (caller-provided scratch) on the same inputs; the second call would expose anything that
-wrongly survives in the shared array.  It also checks that a problem too big for the array is refused with a
+ordinary entry point (caller-provided scratch) on the same inputs AND with the attention arithmetic of the
+reference (modules.py:87-105) evaluated in fp32 on the host, so an error shared by both entry points cannot hide;
+the second call would expose anything that wrongly survives in the shared array.  It also checks that a problem too big for the array is refused with a
 message rather than run.  The file name makes pytest collect it last, so a failure here cannot hide the other tests.
 """
 import ctypes as C
@@ -17,6 +18,7 @@ import torch
 
 from distributed_llm_inference_b200 import _ffi
 from tests import gpu_ops as ops
+from tests.test_ops_gpu import _attn_ref
 
 pytestmark = pytest.mark.gpu
 
@@ -44,6 +46,9 @@ def test_static_scratch_matches_caller_scratch_twice(H, KV, hd):
         torch.cuda.synchronize()
         msg, err, scale = ops.err_report(f"static decode attention call {call}", got, want)
         assert err <= 8e-3 * scale + 1e-3, msg                    # same bound as test_decode_attention
+        ref = _attn_ref(q.view(B, H, 1, hd).float().cpu(), K.float().cpu(), V.float().cpu(), False, T - 1)[:, 0]
+        msg, err, scale = ops.err_report(f"static decode attention call {call} vs fp32 reference math", got, ref)
+        assert err <= 8e-3 * scale + 1e-3, msg
 
 
 def test_static_scratch_refuses_oversized_problem():
