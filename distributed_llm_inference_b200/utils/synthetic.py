@@ -115,3 +115,100 @@ def make_hidden(shape: LlamaShape, batch: int, length: int, seed: int = 7, dtype
     gen.manual_seed(seed)
     x = torch.empty(batch, length, shape.hidden_size, dtype=torch.float32).normal_(0, scale, generator=gen)
     return x.to(torch.bfloat16).to(dtype).to(device)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# "Decidable" client: greedy token identity between a bf16 and an fp32 run is only a meaningful assertion when
+# the model's top-1/top-2 margins are well above the arithmetic error.  A model whose every tensor is
+# N(0, 0.02^2) has margins down to 1e-3 (the reference's own bf16 run disagrees with its fp32
+# run).  This recipe — fixed here, before any GPU result was looked at — keeps the decoder layers exactly as
+# above and only shapes the client tensors the way a trained model is shaped: unit-scale embeddings, and an
+# output head tied to the embedding through a fixed permutation of the vocabulary,
+#     lm_head[perm[t]] = (alpha / sqrt(h)) * embed[t],
+# so the hidden state of token t (its embedding plus everything the layers add) scores highest for perm[t].
+# Logits of the other tokens stay O(alpha); the layers still move every logit, so the 2e-2 logit bound keeps
+# testing the arithmetic, while the argmax is decided by a margin of order alpha * sqrt(h) / rms(residual).
+# ---------------------------------------------------------------------------------------------------------
+DECIDABLE_ALPHA = 0.5
+DECIDABLE_SEED = 2468
+
+
+def make_decidable_client_weights(shape: LlamaShape, device="cpu", dtype=torch.bfloat16, seed: int = DECIDABLE_SEED,
+                                  alpha: float = DECIDABLE_ALPHA):
+    gen = torch.Generator(device="cpu")
+    gen.manual_seed(seed)
+    emb = torch.empty(shape.vocab_size, shape.hidden_size, dtype=torch.float32).normal_(0, 1.0, generator=gen)
+    emb = emb.to(torch.bfloat16)
+    perm = torch.randperm(shape.vocab_size, generator=gen)
+    head = torch.empty_like(emb)
+    head[perm] = (emb.float() * (alpha / shape.hidden_size ** 0.5)).to(torch.bfloat16)
+    norm = torch.ones(shape.hidden_size, dtype=torch.bfloat16)
+    return {"embed_tokens": emb.to(dtype).to(device), "norm": norm.to(dtype).to(device), "lm_head": head.to(dtype).to(device)}
+
+
+def write_checkpoint(model_dir: str, shape: LlamaShape, layer_weights: Dict[int, Dict[str, torch.Tensor]],
+                     client: Optional[Dict[str, torch.Tensor]] = None, shard_layers: int = 0,
+                     attn_implementation: str = "eager", max_position_embeddings: int = 8192) -> None:
+    """A local Hugging-Face-style checkpoint directory (config.json + safetensors [+ index]) holding the given layers
+    under the names the reference's loader looks for, ``model.layers.{global_idx}.<param>.weight``
+    (distributed_llm_inference/utils/model.py:40,64-70), and the client tensors under ``model.embed_tokens.weight``,
+    ``model.norm.weight``, ``lm_head.weight``.  ``shard_layers > 0`` splits the layers over several files behind a
+    ``model.safetensors.index.json`` weight map."""
+    import json
+    import os
+
+    from safetensors.torch import save_file
+
+    os.makedirs(model_dir, exist_ok=True)
+    cfg = shape.to_hf_config(attn_implementation, max_position_embeddings)
+    cfg.architectures = ["LlamaForCausalLM"]
+    cfg.save_pretrained(model_dir)
+    tensors = {}
+    for g, w in layer_weights.items():
+        for name, t in w.items():
+            tensors[f"model.layers.{g}.{name}.weight"] = t.contiguous().cpu()
+    extra = {}
+    if client is not None:
+        extra = {"model.embed_tokens.weight": client["embed_tokens"].contiguous().cpu(),
+                 "model.norm.weight": client["norm"].contiguous().cpu(),
+                 "lm_head.weight": client["lm_head"].contiguous().cpu()}
+    if shard_layers <= 0:
+        save_file({**tensors, **extra}, os.path.join(model_dir, "model.safetensors"))
+        return
+    ids = sorted(layer_weights)
+    groups = [ids[i:i + shard_layers] for i in range(0, len(ids), shard_layers)]
+    n_files = len(groups) + (1 if extra else 0)
+    weight_map = {}
+    for fi, grp in enumerate(groups):
+        fname = f"model-{fi + 1:05d}-of-{n_files:05d}.safetensors"
+        part = {k: v for k, v in tensors.items() if int(k.split(".")[2]) in grp}
+        save_file(part, os.path.join(model_dir, fname))
+        weight_map.update({k: fname for k in part})
+    if extra:
+        fname = f"model-{n_files:05d}-of-{n_files:05d}.safetensors"
+        save_file(extra, os.path.join(model_dir, fname))
+        weight_map.update({k: fname for k in extra})
+    with open(os.path.join(model_dir, "model.safetensors.index.json"), "w") as f:
+        json.dump({"metadata": {}, "weight_map": weight_map}, f)
+
+
+def read_client_weights(model_dir: str, device="cpu", dtype=torch.bfloat16) -> Dict[str, torch.Tensor]:
+    """The client tensors of a checkpoint written by ``write_checkpoint`` (embedding, final norm, head)."""
+    import json
+    import os
+
+    import safetensors
+
+    names = {"model.embed_tokens.weight": "embed_tokens", "model.norm.weight": "norm", "lm_head.weight": "lm_head"}
+    index = os.path.join(model_dir, "model.safetensors.index.json")
+    if os.path.exists(index):
+        with open(index) as f:
+            wm = json.load(f)["weight_map"]
+        files = {k: os.path.join(model_dir, wm[k]) for k in names}
+    else:
+        files = {k: os.path.join(model_dir, "model.safetensors") for k in names}
+    out = {}
+    for k, short in names.items():
+        with safetensors.safe_open(files[k], framework="pt", device="cpu") as f:
+            out[short] = f.get_tensor(k).to(dtype).to(device)
+    return out

@@ -3,7 +3,7 @@
 
 Run from the repo root in the build container (the GPU box has no /root/reference):
 
-    python -m tests.golden.make_golden
+    python -m tests.golden.make_golden [span|greedy|all]
 
 The reference files are imported where they lie through oracle/ref_shim.py (two import shims, three
 crash repairs — see that file); fp32, CPU.  Inputs and weights are regenerated from seeds by
@@ -42,17 +42,18 @@ def ref_make_span(shp, weights, attn_implementation, rope):
 
 
 def main():
+    only = sys.argv[1] if len(sys.argv) > 1 else "all"      # "span" | "greedy" | "all"
     torch.set_grad_enabled(False)
     meta = dict(torch=torch.__version__, reference="Dylan102938/distributed-llm-inference @ /root/reference",
                 dtype="float32")
-    for case in SPAN_CASES:
+    for case in (SPAN_CASES if only in ("all", "span") else ()):
         out = run_span_case(case, ref_make_span, ref_shim.make_cache)
         path = os.path.join(HERE, f"span_{case.name}.npz")
         np.savez_compressed(path, prefill=out["prefill"], decode=out["decode"],
                             meta=np.array(repr({**meta, **case.__dict__})))
         print("wrote", path, out["prefill"].shape, out["decode"].shape)
 
-    for case in GREEDY_CASES:
+    for case in (GREEDY_CASES if only in ("all", "greedy") else ()):
         shp, span_w, cw = greedy_case_weights(case, torch.float32)
         spans = [ref_make_span(shp, w, case.attn_implementation, case.rope) for w in span_w]
         caches = [ref_shim.make_cache(case.window, case.sinks) for _ in spans]

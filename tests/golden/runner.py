@@ -59,5 +59,6 @@ def greedy_case_weights(case: GreedyCase, dtype, device="cpu"):
     shp = syn.SHAPES[case.shape]
     spans = [[{k: v.to(device) for k, v in w.items()} for w in
               syn.make_span_weights(shp, list(range(a, b)), dtype=dtype, device="cpu")] for a, b in case.spans]
-    client = {k: v.to(device) for k, v in syn.make_client_weights(shp, dtype=dtype, device="cpu").items()}
+    make = syn.make_decidable_client_weights if case.client == "decidable" else syn.make_client_weights
+    client = {k: v.to(device) for k, v in make(shp, dtype=dtype, device="cpu").items()}
     return shp, spans, client

@@ -150,17 +150,31 @@ def test_span_without_cache_and_error_behaviour():
 
 
 @pytest.mark.parametrize("case", GREEDY_CASES, ids=lambda c: c.name)
-def test_greedy_c1_matches_reference(case):
-    """BASELINE.json configs[0]: tiny Llama, 2 spans x 6 layers, batch 1, 128-token prompt, 32 greedy steps.
-    North-star bar: greedy tokens identical, per-step logits within 2e-2 max-abs (bf16 vs fp32 reference)."""
+def test_greedy_c1_matches_reference(case, tmp_path):
+    """BASELINE.json configs[0]: tiny Llama, 2 spans x 6 layers, batch 1, 128-token prompt, 64 greedy steps, against the
+    fixture the reference itself produced.  North-star bar: greedy tokens identical for 64 steps, per-step logits within
+    2e-2 max-abs (bf16 vs fp32 reference).
+
+    The spans are loaded the way a server loads them: the case's weights are written as a local
+    safetensors checkpoint and every span comes from ``load_block(dir, layer_ids)``.
+    ``assert_tokens`` cases (head tied to a unit-scale embedding, margins ~ 9: synthetic.make_decidable_client_weights)
+    assert identity on every step, teacher-forced AND free-running.  The N(0, 0.02^2) cases have margins down to
+    5e-4 -- below the arithmetic error of any bf16 run, the reference's own included -- so there the logit
+    bound is asserted and the agreement is printed."""
+    from distributed_llm_inference_b200.utils.model import load_block
+
     gold = np.load(os.path.join(GOLD, f"greedy_{case.name}.npz"))
     shp, span_w, cw = greedy_case_weights(case, torch.bfloat16)
-    spans = [gpu_make_span(shp, w, case.attn_implementation, case.rope, first_layer=a)
-             for w, (a, _) in zip(span_w, case.spans)]
+    layers = {g: w for ws, (a, b) in zip(span_w, case.spans) for g, w in zip(range(a, b), ws)}
+    syn.write_checkpoint(str(tmp_path), shp, layers, client=cw, shard_layers=4, attn_implementation=case.attn_implementation)
+    spans = [load_block(str(tmp_path), list(range(a, b)), rope=case.rope,
+                        attn_implementation=case.attn_implementation).to(DEV) for a, b in case.spans]
+    cw = syn.read_client_weights(str(tmp_path), device=DEV)
     caches = [gpu_make_cache(case.window, case.sinks) for _ in spans]
-    client = SequentialClient(cw["embed_tokens"].to(DEV), cw["norm"].to(DEV), cw["lm_head"].to(DEV), spans, caches)
+    client = SequentialClient(cw["embed_tokens"], cw["norm"], cw["lm_head"], spans, caches)
     prompt = syn.make_prompt(shp, case.batch, case.prompt, device=DEV)
     forced = torch.from_numpy(gold["tokens"]).to(DEV)
+    assert gold["tokens"].shape[1] == case.n_new == 64
     toks_tf, logs = client.greedy("tf", prompt, case.n_new, forced=forced)        # teacher-forced: comparable logits
     L = torch.stack(logs, dim=1).float().cpu().numpy()
     err = np.abs(L[:, :, :: case.vocab_stride] - gold["logits_strided"]).max()
@@ -172,11 +186,39 @@ def test_greedy_c1_matches_reference(case):
     print(f"\n{case.name}: logits max_abs_err {err:.4e} (top-1 {top_err:.4e}); teacher-forced {agree_tf.sum()}/{agree_tf.size} "
           f"free-running {agree_free.sum()}/{agree_free.size}; min margin {margin.min():.2e}")
     assert err <= 2e-2 and top_err <= 2e-2
-    # Token identity is asserted wherever it is decidable: the random-init model's top-1/top-2 margins go down to
-    # 1e-3..2e-3 (the reference's own bf16 run disagrees with its fp32 run on 4 of these 32 steps), so
-    # steps whose margin is below twice the measured logit error are reported, not asserted.
-    assert agree_tf[margin > 2 * max(err, top_err)].all()
-    assert agree_tf.sum() >= case.n_new - 4
+    if case.assert_tokens:
+        assert margin.min() > 1.0                      # the fixture itself: decidable on every step
+        assert agree_tf.all() and agree_free.all()
+    else:
+        assert agree_tf[margin > 2 * max(err, top_err)].all()
+
+
+def test_load_block_runs_on_gpu(tmp_path):
+    """SURVEY 8 f3 (utils/model.py:75-90): a span loaded from a sharded local checkpoint by its GLOBAL layer ids, moved to
+    the GPU with convert_to_optimized_block, gives the oracle's outputs for those layers' weights -- prefill, cached
+    decode and a graphed step."""
+    from distributed_llm_inference_b200.utils.model import convert_to_optimized_block, load_block
+
+    shp = syn.SHAPES["test_gqa"]
+    ids = [0, 1, 2, 3]
+    W = syn.make_span_weights(shp, ids, norm_jitter=0.1)
+    syn.write_checkpoint(str(tmp_path), shp, dict(zip(ids, W)), shard_layers=1)
+    blk = convert_to_optimized_block(load_block(str(tmp_path), [1, 2], rope="float", attn_implementation="eager"))
+    assert blk.layer_ids == [1, 2] and next(blk.parameters()).is_cuda
+    osp = oracle_make_span(shp, W[1:3], "eager", "float")
+    gc, oc = gpu_make_cache(4096, 4), so.SinkCacheOracle(4096, 4)
+    pos = 0
+    for step, L in enumerate([40, 1, 1]):
+        x = syn.make_hidden(shp, 2, L, seed=30 + step)
+        cp = torch.arange(pos, pos + L)
+        ref = osp.forward("g", x.float(), past_key_value=oc, cache_position=cp)[0]
+        got = blk("g", x.to(DEV), past_key_value=gc, cache_position=cp.to(DEV))[0]
+        _check(f"loaded span step {step}", got.float().cpu().numpy(), ref.numpy())
+        pos += L
+    graph = blk.graphed_decode("g", gc, max_ctx=64)
+    xt = syn.make_hidden(shp, 2, 1, seed=44)
+    ref = osp.forward("g", xt.float(), past_key_value=oc, cache_position=torch.tensor([pos]))[0]
+    _check("loaded span graphed step", graph.step(xt.to(DEV)).float().cpu().numpy(), ref.numpy())
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
