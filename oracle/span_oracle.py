@@ -77,6 +77,7 @@ def rope_tables(
     Returns cos, sin of shape ``[Bp, L, head_dim]``.
     """
     inv_freq = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.int64).float() / head_dim))
+    inv_freq = inv_freq.to(position_ids.device)   # the oracle also runs in fp32 on a GPU for full-depth checks
     inv = inv_freq[None, :, None].float().expand(position_ids.shape[0], -1, 1)
     pos = position_ids[:, None, :].float()
     freqs = (inv @ pos).transpose(1, 2)
@@ -226,10 +227,10 @@ def build_mask(
     min_dtype = torch.finfo(dtype).min
     L = hidden.shape[1]
     target = attention_mask.shape[-1] if isinstance(attention_mask, torch.Tensor) else past_seen + L + 1
-    m = torch.full((L, target), fill_value=min_dtype, dtype=dtype)
+    m = torch.full((L, target), fill_value=min_dtype, dtype=dtype, device=hidden.device)
     if L != 1:
         m = torch.triu(m, diagonal=1)
-    m = m * (torch.arange(target) > cache_position.reshape(-1, 1))
+    m = m * (torch.arange(target, device=hidden.device) > cache_position.reshape(-1, 1))
     m = m[None, None, :, :].expand(hidden.shape[0], 1, -1, -1)
     if attention_mask is not None:
         m = m.clone()
@@ -324,7 +325,7 @@ class OracleSpan:
         cache_position: Optional[torch.Tensor] = None,
     ):
         if cache_position is None:                                                     # model.py:39-42
-            cache_position = torch.arange(0, hidden_states.shape[1])
+            cache_position = torch.arange(0, hidden_states.shape[1], device=hidden_states.device)
         past_seen = 0
         if past_key_value is not None:                                                 # model.py:91 (D2 repaired)
             past_seen = past_key_value.get_seq_length(0, generation_id)
