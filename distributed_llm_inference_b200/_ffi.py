@@ -26,6 +26,7 @@ EXPORTS = (
     "dli_cast_f32_bf16", "dli_span_create", "dli_span_destroy", "dli_span_bind_weights",
     "dli_span_workspace_bytes", "dli_span_forward", "dli_last_launch_count", "dli_span_profile",
     "dli_span_profile_read", "dli_decode_attention_static", "dli_kv_evict", "dli_span_decode_step",
+    "dli_stage_decode_step", "dli_flag_wait", "dli_lm_head_argmax",
 )
 
 
@@ -49,6 +50,14 @@ class SpanDesc(C.Structure):
 class LayerWeights(C.Structure):
     _fields_ = [("wqkv", C.c_void_p), ("wo", C.c_void_p), ("wgu", C.c_void_p), ("wdown", C.c_void_p),
                 ("g_in", C.c_void_p), ("g_post", C.c_void_p)]
+
+
+class StageIo(C.Structure):
+    _fields_ = [("hidden_in", C.c_void_p), ("token_ids", C.c_void_p), ("embed_table", C.c_void_p),
+                ("hidden_out", C.c_void_p), ("final_norm", C.c_void_p), ("lm_head", C.c_void_p),
+                ("logits", C.c_void_p), ("tokens_out", C.c_void_p), ("vocab", C.c_int32), ("eps_final", C.c_float),
+                ("wait_flag", C.c_void_p), ("signal_flag", C.c_void_p), ("state", C.c_void_p),
+                ("wait_lag", C.c_int32), ("chain", C.c_int32), ("timeout_ms", C.c_int32)]
 
 
 def _load() -> C.CDLL:
@@ -81,6 +90,9 @@ def _load() -> C.CDLL:
         "dli_span_profile_read": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]),
         "dli_span_forward": (C.c_int, [vp, C.POINTER(KvDesc), i32, i32, i32, vp, vp, vp, vp, vp, vp, sz, vp]),
         "dli_span_decode_step": (C.c_int, [vp, C.POINTER(KvDesc), i32, vp, vp, vp, vp, vp, i32, vp, sz, vp]),
+        "dli_stage_decode_step": (C.c_int, [vp, C.POINTER(KvDesc), i32, C.POINTER(StageIo), vp, vp, vp, i32, vp, sz, vp]),
+        "dli_flag_wait": (C.c_int, [vp, C.c_uint32, vp, i32, vp]),
+        "dli_lm_head_argmax": (C.c_int, [vp, i32, vp, f32, vp, i32, i32, i32, vp, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

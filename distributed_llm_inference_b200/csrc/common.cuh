@@ -143,7 +143,32 @@ struct StepState {
   bool advance;
 };
 
+// Hand-off of a pipeline stage step, folded into the step's own first and last kernels (dli_stage_decode_step):
+//   entry  the first kernel spins on a flag in THIS GPU's memory until the producer (previous stage, or the last stage
+//          through the ring closure) has stored this step's input; with token_ids the input rows are gathered from an
+//          embedding table (stage 0 of a token ring);
+//   exit   the last kernel, after every CTA's stores (possibly into a peer GPU's memory) are fenced system-wide,
+//          bumps the step counter and releases the consumer's flag.
+// state: 4 words in this GPU's memory: [0] steps completed, [1] CTA ticket (0 between steps), [2] sticky error
+// (a wait gave up after timeout_ns), [3] unused.
+struct EntryArgs {
+  const int* token_ids;       // nullable
+  const uint32_t* wait_flag;  // nullable
+  uint32_t* state;            // nullable when wait_flag is
+  int lag;                    // wait until *wait_flag + lag >= state[0] + 1
+  unsigned long long timeout_ns;
+};
+struct ExitArgs {
+  uint32_t* signal_flag;  // nullable
+  uint32_t* state;        // nullable: no counter, no signal
+};
+
 // ---- other launchers ----------------------------------------------------------------------------------
+int launch_rmsnorm_entry(const void* x, const __nv_bfloat16* w, __nv_bfloat16* y, float* resid_out, int rows, int h, float eps,
+                         const EntryArgs& ea, cudaStream_t st);
+int launch_argmax(const float* logits, int32_t* tokens_out, int batch, int vocab, cudaStream_t st, const StepState* adv,
+                  const ExitArgs& xa);
+int launch_flag_wait(const uint32_t* flag, uint32_t at_least, uint32_t* state, unsigned long long timeout_ns, cudaStream_t st);
 int launch_rmsnorm(const void* x, bool x_is_f32, const __nv_bfloat16* w, __nv_bfloat16* y, float* resid_out,
                    __nv_bfloat16* copy_out, int rows, int h, float eps, float pre_scale, cudaStream_t st);
 int launch_rope_kv_append(float* qkv, bool zero_after, const float* cos, const float* sin, __nv_bfloat16* q_out,
@@ -152,7 +177,8 @@ int launch_rope_kv_append(float* qkv, bool zero_after, const float* cos, const f
 int launch_silu_mul(float* gu, __nv_bfloat16* act, int m, int n, bool zero_after, cudaStream_t st);
 int launch_kv_evict(const dli_kv_desc* kv, int n_layers, int batch, int KV, int hd, int cur_len, int window, int sinks,
                     int n_new, const float* cos_hist, const float* sin_hist, cudaStream_t st);
-int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st, const StepState* adv = nullptr);
+int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st, const StepState* adv = nullptr,
+                const ExitArgs* xa = nullptr);
 size_t decode_attn_scratch_bytes(int batch, int H, int hd, int max_ctx);
 // Decode attention that applies RoPE and the KV append itself (rope_inline.cuh); qkv == nullptr: q arrives rotated in
 // bf16 and the pages already hold the step's token.  Only for unsplit contexts: decode_attention_fuses_rope().
@@ -237,6 +263,69 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 }
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
+// ---- cross-GPU flags (system scope) ---------------------------------------------------------------------
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// 128-bit load of data another GPU may have stored while this kernel was already running (a hand-off inbox): never
+// through the non-coherent path, never from a stale L1 line
+__device__ __forceinline__ uint4 ld_relaxed_sys_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+// One thread: wait until *flag has reached `need` (counters only grow; compared modulo 2^32).  Gives up after
+// timeout_ns -- or at once if an earlier wait on this state already gave up -- and records that in state[2], so a
+// producer that never signals turns into an error the host can read, not a hung GPU.
+__device__ __forceinline__ void flag_wait(const uint32_t* flag, uint32_t need, uint32_t* state, unsigned long long timeout_ns) {
+  if ((int)(ld_acquire_sys(flag) - need) >= 0) return;
+  const unsigned long long t0 = global_timer_ns();
+  unsigned ns = 32;
+  while (true) {
+    if ((int)(ld_acquire_sys(flag) - need) >= 0) return;
+    if (ld_relaxed_sys(state + 2) != 0) return;
+    if (global_timer_ns() - t0 > timeout_ns) {
+      atomicExch(state + 2, 1u);
+      return;
+    }
+    __nanosleep(ns);
+    if (ns < 256) ns *= 2;
+  }
+}
+// Last kernel of a stage step, called by ALL threads of every CTA after their output stores: fence them system-wide,
+// take a ticket, and let the last CTA to arrive bump the step counter and release the consumer's flag.
+__device__ __forceinline__ void step_exit(const ExitArgs& xa) {
+  if (!xa.state) return;
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned total = gridDim.x * gridDim.y * gridDim.z;
+    const unsigned ticket = atomicAdd(xa.state + 1, 1u);
+    if (ticket == total - 1) {
+      __threadfence_system();
+      xa.state[1] = 0;
+      const uint32_t done = xa.state[0] + 1;
+      xa.state[0] = done;
+      if (xa.signal_flag) st_release_sys(xa.signal_flag, done);
+    }
+  }
+}
+
 // 128-bit streaming load that does not allocate in L1 (data read once: weights, KV pages)
 __device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
   uint4 r;

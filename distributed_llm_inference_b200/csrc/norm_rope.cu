@@ -13,9 +13,13 @@ namespace dli {
 // ---------------------------------------------------------------------------------------------------
 constexpr int NORM_THREADS = 256;
 
-template <bool F32IN>
+template <bool F32IN, bool COHERENT = false>
 __device__ __forceinline__ void load8(const void* x, long long i, float (&v)[8]) {
-  if (F32IN) {
+  if (COHERENT) {  // bf16 rows another GPU may have stored while this kernel was already resident (hand-off inbox)
+    const uint4 a = ld_relaxed_sys_v4((const __nv_bfloat16*)x + i);
+    v[0] = bf16_lo(a.x); v[1] = bf16_hi(a.x); v[2] = bf16_lo(a.y); v[3] = bf16_hi(a.y);
+    v[4] = bf16_lo(a.z); v[5] = bf16_hi(a.z); v[6] = bf16_lo(a.w); v[7] = bf16_hi(a.w);
+  } else if (F32IN) {
     const float4 a = *reinterpret_cast<const float4*>((const float*)x + i);
     const float4 b = *reinterpret_cast<const float4*>((const float*)x + i + 4);
     v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
@@ -33,15 +37,20 @@ __device__ __forceinline__ void load8(const void* x, long long i, float (&v)[8])
 // ring cannot cover.)  Wider rows take the two-pass path.
 constexpr int NORM_CHUNKS = 4;
 
-template <bool F32IN>
+// ENTRY (first kernel of a pipeline stage step, bf16 input): the input rows are either a hand-off inbox that the
+// previous stage fills over NVLink -- thread 0 waits for the producer's flag after the dependency wait, the rows are
+// then read with coherent loads -- or rows of an embedding table picked by device-resident token ids (stage 0 of a
+// token ring; the ids are what the flag guards).
+template <bool F32IN, bool ENTRY = false>
 __global__ void __launch_bounds__(NORM_THREADS) rmsnorm_kernel(const void* __restrict__ x, const __nv_bfloat16* __restrict__ w,
                                                                __nv_bfloat16* __restrict__ y, float* __restrict__ resid_out,
                                                                __nv_bfloat16* __restrict__ copy_out, int h, float eps,
-                                                               float s) {
+                                                               float s, EntryArgs ea) {
   __shared__ float red[NORM_THREADS / 32];
   pdl_trigger();
   if (threadIdx.x == 0) DLI_TRACE_EV(TR_RMSNORM, 0);
-  const long long base = (long long)blockIdx.x * h;
+  long long in_base = (long long)blockIdx.x * h;
+  const long long base = in_base;
   const int i0 = threadIdx.x * 8;
   if (h <= NORM_THREADS * 8 * NORM_CHUNKS) {
     uint4 wv[NORM_CHUNKS];
@@ -53,11 +62,21 @@ __global__ void __launch_bounds__(NORM_THREADS) rmsnorm_kernel(const void* __res
     }
     pdl_wait();
     if (threadIdx.x == 0) DLI_TRACE_EV(TR_RMSNORM, 1);
+    if (ENTRY) {
+      if (ea.wait_flag) {
+        if (threadIdx.x == 0) flag_wait(ea.wait_flag, ld_relaxed_sys(ea.state) + 1u - (uint32_t)ea.lag, ea.state, ea.timeout_ns);
+        __syncthreads();
+      }
+      if (ea.token_ids) in_base = (long long)ld_relaxed_sys(reinterpret_cast<const uint32_t*>(ea.token_ids) + blockIdx.x) * h;
+    }
     float ss = 0.f;
 #pragma unroll
     for (int c = 0; c < NORM_CHUNKS; ++c) {
       const int i = i0 + c * NORM_THREADS * 8;
-      if (i < h) load8<F32IN>(x, base + i, v[c]);
+      if (i < h) {
+        if (ENTRY && !ea.token_ids) load8<F32IN, true>(x, in_base + i, v[c]);
+        else load8<F32IN>(x, in_base + i, v[c]);
+      }
     }
 #pragma unroll
     for (int c = 0; c < NORM_CHUNKS; ++c) {
@@ -142,7 +161,17 @@ int launch_rmsnorm(const void* x, bool x_is_f32, const __nv_bfloat16* w, __nv_bf
   DLI_REQUIRE(x && w && y, "dli_rmsnorm: null pointer");
   DLI_REQUIRE(rows > 0 && h > 0 && h % 8 == 0, "dli_rmsnorm: rows=%d h=%d (h must be a positive multiple of 8)", rows, h);
   return launch_kernel("rmsnorm_kernel", x_is_f32 ? rmsnorm_kernel<true> : rmsnorm_kernel<false>, dim3(rows),
-                       dim3(NORM_THREADS), 0, st, x, w, y, resid_out, copy_out, h, eps, pre_scale);
+                       dim3(NORM_THREADS), 0, st, x, w, y, resid_out, copy_out, h, eps, pre_scale, EntryArgs{});
+}
+
+int launch_rmsnorm_entry(const void* x, const __nv_bfloat16* w, __nv_bfloat16* y, float* resid_out, int rows, int h, float eps,
+                         const EntryArgs& ea, cudaStream_t st) {
+  DLI_REQUIRE(x && w && y && resid_out, "stage step entry: null pointer");
+  DLI_REQUIRE(rows > 0 && h > 0 && h % 8 == 0 && h <= NORM_THREADS * 8 * NORM_CHUNKS,
+              "stage step entry: rows=%d h=%d (h must be a multiple of 8, at most %d)", rows, h, NORM_THREADS * 8 * NORM_CHUNKS);
+  DLI_REQUIRE(!ea.wait_flag || ea.state, "stage step entry: a wait flag needs the step state");
+  return launch_kernel("rmsnorm_kernel<entry>", rmsnorm_kernel<false, true>, dim3(rows), dim3(NORM_THREADS), 0, st, x, w, y,
+                       resid_out, (__nv_bfloat16*)nullptr, h, eps, 1.0f, ea);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -259,7 +288,8 @@ int launch_silu_mul(float* gu, __nv_bfloat16* act, int m, int n, bool zero_after
 }
 
 __global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long n4,
-                                                   int* __restrict__ seq_lens, long long* __restrict__ pos, int batch) {
+                                                   int* __restrict__ seq_lens, long long* __restrict__ pos, int batch,
+                                                   ExitArgs xa) {
   pdl_trigger();
   pdl_wait();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
@@ -272,14 +302,85 @@ __global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ in,
     for (int b = threadIdx.x; b < batch; b += blockDim.x) seq_lens[b] += 1;
     if (threadIdx.x == 0 && pos) *pos += 1;
   }
+  step_exit(xa);  // pipeline stage: `out` may be the next stage's inbox on a peer GPU
 }
 
-int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st, const StepState* adv) {
+int launch_cast(const float* in, __nv_bfloat16* out, long long n, cudaStream_t st, const StepState* adv, const ExitArgs* xa) {
   DLI_REQUIRE(in && out && n > 0 && n % 4 == 0, "dli_cast_f32_bf16: n=%lld must be a positive multiple of 4", n);
   const int blocks = (int)std::min<long long>((n / 4 + 255) / 256, (long long)sm_count() * 8);
   const bool a = adv && adv->advance;
   return launch_kernel("cast_kernel", cast_kernel, dim3(blocks), dim3(256), 0, st, in, out, n / 4,
-                       a ? adv->seq_lens : (int*)nullptr, a ? adv->pos_rw : (long long*)nullptr, a ? adv->batch : 0);
+                       a ? adv->seq_lens : (int*)nullptr, a ? adv->pos_rw : (long long*)nullptr, a ? adv->batch : 0,
+                       xa ? *xa : ExitArgs{nullptr, nullptr});
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Greedy sampling at the end of the last pipeline stage: token[b] = argmax_v logits[b, v] (lowest index on ties).
+// One CTA per sequence; the result may go straight into stage 0's token inbox on a peer GPU.  As the last kernel of
+// that stage's step it also advances the device-resident lengths / position and signals the consumer.
+// ---------------------------------------------------------------------------------------------------
+constexpr int ARGMAX_THREADS = 512;
+
+__global__ void __launch_bounds__(ARGMAX_THREADS) argmax_kernel(const float* __restrict__ logits, int32_t* __restrict__ tokens_out,
+                                                                int vocab, int* __restrict__ seq_lens,
+                                                                long long* __restrict__ pos, int batch, ExitArgs xa) {
+  __shared__ float sv[ARGMAX_THREADS / 32];
+  __shared__ int si[ARGMAX_THREADS / 32];
+  pdl_trigger();
+  pdl_wait();
+  const float* row = logits + (long long)blockIdx.x * vocab;
+  float best = -INFINITY;
+  int arg = 0x7fffffff;
+  const int v4 = vocab / 4;
+  for (int i = threadIdx.x; i < v4; i += ARGMAX_THREADS) {
+    const float4 a = *reinterpret_cast<const float4*>(row + 4 * i);
+    const float e[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (e[j] > best) { best = e[j]; arg = 4 * i + j; }   // indices grow within a thread: first maximum wins
+  }
+  for (int i = 4 * v4 + threadIdx.x; i < vocab; i += ARGMAX_THREADS)
+    if (row[i] > best) { best = row[i]; arg = i; }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (ob > best || (ob == best && oa < arg)) { best = ob; arg = oa; }
+  }
+  if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = arg; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int k = 1; k < ARGMAX_THREADS / 32; ++k)
+      if (sv[k] > best || (sv[k] == best && si[k] < arg)) { best = sv[k]; arg = si[k]; }
+    tokens_out[blockIdx.x] = arg == 0x7fffffff ? 0 : arg;
+  }
+  if (seq_lens && blockIdx.x == 0) {
+    for (int b = threadIdx.x; b < batch; b += blockDim.x) seq_lens[b] += 1;
+    if (threadIdx.x == 0 && pos) *pos += 1;
+  }
+  step_exit(xa);
+}
+
+int launch_argmax(const float* logits, int32_t* tokens_out, int batch, int vocab, cudaStream_t st, const StepState* adv,
+                  const ExitArgs& xa) {
+  DLI_REQUIRE(logits && tokens_out && batch > 0 && vocab > 0, "argmax: null pointer or empty problem");
+  DLI_REQUIRE((reinterpret_cast<uintptr_t>(logits) & 15) == 0 && vocab % 4 == 0, "argmax: logits must be 16-byte aligned rows (vocab %% 4 == 0)");
+  const bool a = adv && adv->advance;
+  return launch_kernel("argmax_kernel", argmax_kernel, dim3(batch), dim3(ARGMAX_THREADS), 0, st, logits, tokens_out, vocab,
+                       a ? adv->seq_lens : (int*)nullptr, a ? adv->pos_rw : (long long*)nullptr, a ? adv->batch : 0, xa);
+}
+
+// A stream-ordered wait for a hand-off flag (one thread): what a host-side client puts in front of the copy that reads
+// a result another GPU delivers (token ids arriving in stage 0's inbox).
+__global__ void flag_wait_kernel(const uint32_t* flag, uint32_t at_least, uint32_t* state, unsigned long long timeout_ns) {
+  flag_wait(flag, at_least, state, timeout_ns);
+}
+
+int launch_flag_wait(const uint32_t* flag, uint32_t at_least, uint32_t* state, unsigned long long timeout_ns, cudaStream_t st) {
+  DLI_REQUIRE(flag && state, "dli_flag_wait: null pointer");
+  flag_wait_kernel<<<1, 1, 0, st>>>(flag, at_least, state, timeout_ns);
+  DLI_CHECK_LAUNCH("flag_wait_kernel");
+  return DLI_OK;
 }
 
 

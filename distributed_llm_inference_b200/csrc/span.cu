@@ -108,6 +108,9 @@ struct dli_span {
   int n_qkv;  // (H + 2 KV) * hd
   std::vector<dli::Layer> layers;
   std::vector<dli::ActMapKey> act_maps;  // activation-side TMA descriptors, keyed by (pointer, shape, box)
+  const void* head_ptr = nullptr;        // lm_head matrix the maps below describe (dli_stage_decode_step)
+  int head_vocab = 0;
+  dli::WeightMaps head;
   // optional per-kernel-class timing (dli_span_profile_*): one event at every class boundary of the forward
   bool profiling = false;
   std::vector<dli::ProfMark> marks;
@@ -351,7 +354,8 @@ size_t dli_span_workspace_bytes(const dli_span* span, int max_tokens, int max_ba
 
 static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, int causal, const void* hidden_in,
                              void* hidden_out, const float* cos, const float* sin, void* all_hidden, void* workspace,
-                             size_t workspace_bytes, dli_stream_t stream, const StepState& step);
+                             size_t workspace_bytes, dli_stream_t stream, const StepState& step,
+                             const dli_stage_io* io = nullptr);
 
 int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, int causal, const void* hidden_in,
                      void* hidden_out, const float* cos, const float* sin, void* all_hidden, void* workspace,
@@ -371,11 +375,53 @@ int dli_span_decode_step(dli_span* s, const dli_kv_desc* kv, int batch, const vo
                            workspace_bytes, stream, step);
 }
 
+int dli_stage_decode_step(dli_span* s, const dli_kv_desc* kv, int batch, const dli_stage_io* io, const float* cos_table,
+                          const float* sin_table, long long* position, int advance, void* workspace,
+                          size_t workspace_bytes, dli_stream_t stream) {
+  DLI_REQUIRE(s && kv && io && position, "dli_stage_decode_step: null pointer");
+  DLI_REQUIRE(io->hidden_in || (io->token_ids && io->embed_table), "dli_stage_decode_step: no input (hidden_in, or token_ids + embed_table)");
+  DLI_REQUIRE(io->hidden_out || io->lm_head, "dli_stage_decode_step: no output (hidden_out, or lm_head + tokens_out)");
+  if (io->lm_head) {
+    DLI_REQUIRE(io->final_norm && io->logits && io->tokens_out && io->vocab > 0 && io->vocab % 8 == 0,
+                "dli_stage_decode_step: the head needs final_norm, logits, tokens_out and a vocabulary that is a multiple of 8");
+    if (s->head_ptr != io->lm_head || s->head_vocab != io->vocab) {
+      int rc;
+      if ((rc = make_tmap_bf16(&s->head.box128, io->lm_head, io->vocab, s->d.hidden_size, s->d.hidden_size, 128))) return rc;
+      if ((rc = make_tmap_bf16(&s->head.box64, io->lm_head, io->vocab, s->d.hidden_size, s->d.hidden_size, 64))) return rc;
+      if ((rc = make_tmap_bf16(&s->head.box256, io->lm_head, io->vocab, s->d.hidden_size, s->d.hidden_size, 256))) return rc;
+      s->head_ptr = io->lm_head;
+      s->head_vocab = io->vocab;
+    }
+  }
+  DLI_REQUIRE(!(io->wait_flag || io->signal_flag) || io->state, "dli_stage_decode_step: flags need the 4-word step state");
+  const StepState step{position, static_cast<int*>(const_cast<void*>(static_cast<const void*>(kv->seq_lens))), position, batch,
+                       advance != 0};
+  return span_forward_impl(s, kv, batch, 1, 1, io->hidden_in, io->hidden_out, cos_table, sin_table, nullptr, workspace,
+                           workspace_bytes, stream, step, io);
+}
+
+int dli_flag_wait(const uint32_t* flag, uint32_t at_least, uint32_t* state, int timeout_ms, dli_stream_t stream) {
+  return launch_flag_wait(flag, at_least, state, (unsigned long long)(timeout_ms > 0 ? timeout_ms : 2000) * 1000000ull,
+                          (cudaStream_t)stream);
+}
+
+int dli_lm_head_argmax(const void* hidden, int hidden_is_f32, const void* final_norm_bf16, float eps, const void* lm_head_bf16,
+                       int vocab, int h, int batch, void* xn_bf16, float* logits, int32_t* tokens_out, dli_stream_t stream) {
+  DLI_REQUIRE(hidden && final_norm_bf16 && lm_head_bf16 && xn_bf16 && logits && tokens_out, "dli_lm_head_argmax: null pointer");
+  DLI_REQUIRE(batch > 0 && batch <= 128, "dli_lm_head_argmax: batch %d outside [1, 128]", batch);
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = launch_rmsnorm(hidden, hidden_is_f32 != 0, (const __nv_bfloat16*)final_norm_bf16, (__nv_bfloat16*)xn_bf16, nullptr,
+                          nullptr, batch, h, eps, 1.0f, st);
+  if (rc) return rc;
+  if ((rc = launch_gemm(xn_bf16, h, lm_head_bf16, logits, vocab, batch, vocab, h, DLI_EPI_STORE_F32, st))) return rc;
+  return launch_argmax(logits, tokens_out, batch, vocab, st, nullptr, ExitArgs{nullptr, nullptr});
+}
+
 static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, int causal, const void* hidden_in,
                              void* hidden_out, const float* cos, const float* sin, void* all_hidden, void* workspace,
-                             size_t workspace_bytes, dli_stream_t stream, const StepState& step) {
+                             size_t workspace_bytes, dli_stream_t stream, const StepState& step, const dli_stage_io* io) {
   reset_launch_count();
-  DLI_REQUIRE(s && kv && hidden_in && hidden_out && cos && sin && workspace, "dli_span_forward: null pointer");
+  DLI_REQUIRE(s && kv && cos && sin && workspace && (io || (hidden_in && hidden_out)), "dli_span_forward: null pointer");
   DLI_REQUIRE(batch > 0 && q_len > 0, "dli_span_forward: batch=%d q_len=%d", batch, q_len);
   DLI_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "dli_span_forward: workspace must be 256-byte aligned");
   const dli_span_desc& d = s->d;
@@ -408,14 +454,23 @@ static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int 
   } while (0)
   const __nv_bfloat16* attn_in = w.qbuf;
 
-  pdl_barrier_next_launch();  // the call's first kernel starts after everything already in the stream
+  // the call's first kernel starts after everything already in the stream -- unless the caller of a stage step vouches
+  // that what precedes it in the stream belongs to OTHER generations (micro-batches of a pipeline round): then the
+  // steps are chained like the kernels inside one
+  if (!(io && io->chain)) pdl_barrier_next_launch();
   for (int j = 0; j < d.n_layers; ++j) {
     Layer& L = s->layers[j];
     KvView view;
     if ((rc = kv_view(kv, j, &view))) return rc;
     // input_layernorm (modules.py:162); layer 0 also opens the fp32 residual stream (and is never skipped)
     DLI_MARK(DLI_PROF_RMSNORM);
-    if (j == 0 || !DLI_SKIPPED(DLI_PROF_RMSNORM)) {
+    if (j == 0 && io) {  // pipeline stage step: flag wait and/or embedding gather inside the entry kernel
+      const EntryArgs ea{io->token_ids, io->wait_flag, io->state, io->wait_lag,
+                         (unsigned long long)(io->timeout_ms > 0 ? io->timeout_ms : 2000) * 1000000ull};
+      rc = launch_rmsnorm_entry(io->token_ids ? io->embed_table : hidden_in, (const __nv_bfloat16*)L.w.g_in, w.xn, w.resid, M, h,
+                                d.eps_input, ea, st);
+      if (rc) return rc;
+    } else if (j == 0 || !DLI_SKIPPED(DLI_PROF_RMSNORM)) {
       rc = launch_rmsnorm(j == 0 ? hidden_in : (const void*)w.resid, j != 0, (const __nv_bfloat16*)L.w.g_in, w.xn,
                           j == 0 ? w.resid : nullptr, hs ? hs + (size_t)j * M * h : nullptr, M, h, d.eps_input, 1.0f, st);
       if (rc) return rc;
@@ -464,6 +519,22 @@ static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int 
   }
 #undef DLI_STEP
   DLI_MARK(DLI_PROF_CAST);
+  if (io) {  // pipeline stage step: the LAST kernel advances the device-resident state and signals the consumer
+    const ExitArgs xa{io->signal_flag, io->state}, none{nullptr, nullptr};
+    const bool head = io->lm_head != nullptr;
+    if (hidden_out && (rc = launch_cast(w.resid, static_cast<__nv_bfloat16*>(hidden_out), (long long)M * h, st,
+                                        head ? nullptr : &step, head ? &none : &xa)))
+      return rc;
+    if (head) {  // last stage of a token ring: final RMSNorm -> lm_head -> greedy argmax (the client's tail, on the GPU)
+      if ((rc = launch_rmsnorm(w.resid, true, (const __nv_bfloat16*)io->final_norm, w.xn, nullptr, nullptr, M, h, io->eps_final,
+                               1.0f, st)))
+        return rc;
+      if ((rc = span_gemm(s, w.xn, s->head, io->logits, io->vocab, M, io->vocab, h, DLI_EPI_STORE_F32, st))) return rc;
+      if ((rc = launch_argmax(io->logits, io->tokens_out, M, io->vocab, st, &step, xa))) return rc;
+    }
+    DLI_MARK(-1);
+    return DLI_OK;
+  }
   if ((rc = launch_cast(w.resid, static_cast<__nv_bfloat16*>(hidden_out), (long long)M * h, st, hs ? nullptr : &step)))
     return rc;
   if (hs && (rc = launch_cast(w.resid, hs + (size_t)d.n_layers * M * h, (long long)M * h, st, &step))) return rc;

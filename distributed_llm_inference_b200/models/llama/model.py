@@ -15,6 +15,7 @@ must be present; anything else raises.
 from __future__ import annotations
 
 import ctypes as C
+from dataclasses import dataclass
 from typing import List, Optional
 
 import torch
@@ -40,6 +41,43 @@ def rope_table(head_dim: int, theta: float, max_pos: int, mode: str, device) -> 
     elif mode != "float":
         raise ValueError(f"rope must be 'literal' or 'float', got {mode!r}")
     return torch.stack([cos, sin]).contiguous().to(device)
+
+
+@dataclass
+class StageIO:
+    """Inputs, outputs and hand-off flags of a pipeline stage step (``dli_stage_io`` in include/dli_b200.h), as tensors:
+    views of this GPU's memory, or of a peer GPU's symmetric-memory buffer for ``hidden_out`` / ``tokens_out`` /
+    ``signal_flag``.  ``parallel/pipeline.py`` builds these; ``GraphedDecode`` keeps them alive."""
+    hidden_in: Optional[torch.Tensor] = None       # bf16 [B, 1, h]
+    token_ids: Optional[torch.Tensor] = None       # int32 [B] (with embed_table: stage 0 of a token ring)
+    embed_table: Optional[torch.Tensor] = None     # bf16 [V, h]
+    hidden_out: Optional[torch.Tensor] = None      # bf16 [B, 1, h]
+    final_norm: Optional[torch.Tensor] = None      # bf16 [h]
+    lm_head: Optional[torch.Tensor] = None         # bf16 [V, h]
+    logits: Optional[torch.Tensor] = None          # fp32 [B, V]
+    tokens_out: Optional[torch.Tensor] = None      # int32 [B]
+    eps_final: float = 1e-6
+    wait_flag: Optional[torch.Tensor] = None       # int32 view, word 0 is the flag
+    signal_flag: Optional[torch.Tensor] = None
+    state: Optional[torch.Tensor] = None           # int32 [4]
+    wait_lag: int = 0
+    chain: int = 0
+    timeout_ms: int = 2000
+
+    def to_ffi(self, ffi):
+        p = lambda t: None if t is None else t.data_ptr()
+        for name, t, dt in (("hidden_in", self.hidden_in, torch.bfloat16), ("hidden_out", self.hidden_out, torch.bfloat16),
+                            ("embed_table", self.embed_table, torch.bfloat16), ("lm_head", self.lm_head, torch.bfloat16),
+                            ("final_norm", self.final_norm, torch.bfloat16), ("logits", self.logits, torch.float32),
+                            ("token_ids", self.token_ids, torch.int32), ("tokens_out", self.tokens_out, torch.int32),
+                            ("wait_flag", self.wait_flag, torch.int32), ("signal_flag", self.signal_flag, torch.int32),
+                            ("state", self.state, torch.int32)):
+            if t is not None and (t.dtype != dt or not t.is_contiguous()):
+                raise TypeError(f"StageIO.{name} must be a contiguous {dt} tensor")
+        return ffi.StageIo(p(self.hidden_in), p(self.token_ids), p(self.embed_table), p(self.hidden_out), p(self.final_norm),
+                           p(self.lm_head), p(self.logits), p(self.tokens_out),
+                           0 if self.lm_head is None else self.lm_head.shape[0], self.eps_final,
+                           p(self.wait_flag), p(self.signal_flag), p(self.state), self.wait_lag, self.chain, self.timeout_ms)
 
 
 class LlamaBlock(nn.Module):
@@ -133,7 +171,8 @@ class LlamaBlock(nn.Module):
 
     # ------------------------------------------------------------------ whole-step CUDA graph
     def graphed_decode(self, generation_id: str, cache: PartialLlamaSinkCache, max_ctx: int,
-                       x: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> "GraphedDecode":
+                       x: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+                       stage: Optional[StageIO] = None) -> "GraphedDecode":
         """Capture ONE decode step (q_len = 1) of this span for a live generation into a CUDA graph.
 
         The reference hides decode launch latency with three small per-layer graphs (utils/cuda.py:6-77 used at
@@ -145,8 +184,11 @@ class LlamaBlock(nn.Module):
         ``x`` / ``out`` (optional, bf16 ``[B, 1, h]``) replace the graph's own static input / output buffers; ``out`` may
         be a peer GPU's mapped memory, in which case the span's last kernel stores the hand-off tensor straight into
         the next pipeline stage's input over NVLink.
+        ``stage`` (instead of ``x`` / ``out``): the step is a pipeline stage step (``dli_stage_decode_step``) whose entry
+        kernel waits for the producer's flag (or gathers embedding rows by token id) and whose last kernel stores the
+        result into the consumer's memory and releases its flag -- see ``StageIO``.
         """
-        return GraphedDecode(self, cache, generation_id, max_ctx, x=x, out=out)
+        return GraphedDecode(self, cache, generation_id, max_ctx, x=x, out=out, stage=stage)
 
     # ------------------------------------------------------------------ instrumentation (bench.py)
     def profile(self, enable: bool = True) -> None:
@@ -286,7 +328,7 @@ class GraphedDecode:
     (a static buffer that the next ``step`` overwrites)."""
 
     def __init__(self, block: LlamaBlock, cache: PartialLlamaSinkCache, generation_id: str, max_ctx: int,
-                 x: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None):
+                 x: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None, stage: Optional[StageIO] = None):
         gen = cache.generation(generation_id)
         if gen is None or gen.length == 0:
             raise ValueError("graphed_decode needs a generation that has been prefilled through this span")
@@ -310,6 +352,19 @@ class GraphedDecode:
         kv = cache.kv_desc(gen, max_ctx)
 
         self.device = device
+        self.stage = stage
+        io = stage.to_ffi(ffi) if stage is not None else None
+
+        def launch_stage():
+            try:
+                ffi.check(ffi.lib.dli_stage_decode_step(block._span, C.byref(kv), B, C.byref(io), table[0].data_ptr(),
+                                                        table[1].data_ptr(), self.pos.data_ptr(), 1, ws.data_ptr(),
+                                                        ws.numel(), ffi.current_stream(device)))
+            except ffi.DliError:
+                block._ws = None
+                raise
+            return table, ws, stage
+
         def launch():
             # position and lengths live on the device: the kernels index the cos/sin tables by *pos and the span's last
             # kernel advances pos and seq_lens, so a replayed step is nothing but the span's own PDL-chained kernels
@@ -327,6 +382,15 @@ class GraphedDecode:
         warm = "__dli_graph_warmup__"
         block(warm, self.x, past_key_value=cache, cache_position=torch.zeros(1, dtype=torch.long, device=device))
         cache.close(warm)
+        if stage is not None:
+            launch = launch_stage
+            if stage.lm_head is not None:     # the head's GEMM instantiation, outside capture as well
+                V = stage.lm_head.shape[0]
+                with torch.cuda.device(device):
+                    ffi.check(ffi.lib.dli_lm_head_argmax(
+                        self.x.data_ptr(), 0, stage.final_norm.data_ptr(), stage.eps_final, stage.lm_head.data_ptr(), V, h, B,
+                        torch.empty(B, h, dtype=torch.bfloat16, device=device).data_ptr(), stage.logits.data_ptr(),
+                        torch.empty(B, dtype=torch.int32, device=device).data_ptr(), ffi.current_stream(device)))
         torch.cuda.synchronize(device)
         self._launch = launch         # PipelineStage.capture_round re-captures the same launches into a round graph
         self.graph = torch.cuda.CUDAGraph()

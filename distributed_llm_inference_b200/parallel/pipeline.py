@@ -1,116 +1,206 @@
-"""Span-to-span hand-off on one NVSwitch box: one pipeline stage per GPU, NCCL P2P instead of a network hop.
+"""Span-to-span hand-off on one NVSwitch box: one pipeline stage per GPU instead of a network hop.
 
 In the reference, consecutive spans live on different servers and the hidden states travel through hivemind
 (serialize -> socket -> deserialize; only imported at server/backend.py:4-7, never exercised by code in the tree).
-Here stage ``r`` owns layers ``[r*n, (r+1)*n)`` and their KV pages; the ``[B, L, h]`` bf16 hand-off tensor goes to
-stage ``r+1`` with ``torch.distributed`` ``isend/irecv`` (NCCL over NVLink 5; gloo on CPU in the tests), and the
-last stage closes the ring back to stage 0 (where the client would sample and embed the next token).  Several
-micro-batches are interleaved so that every stage is busy once the pipe is full: steady-state utilisation is
-``min(1, micro_batches / stages)``.
+Here stage ``r`` owns layers ``[r*n, (r+1)*n)`` and their KV pages, and several micro-batches are interleaved so that
+every stage is busy once the pipe is full: steady-state utilisation is ``min(1, micro_batches / stages)``.  The exchange
+is exactly one hand-off per stage boundary per micro-batch; there is no all-reduce / all-gather (the reference has no
+tensor parallelism).
 
-The exchange is exactly one send/recv per stage boundary per micro-batch; there is no all-reduce / all-gather
-(the reference has no tensor parallelism).
+Decode hand-off (``enable_graphs``): every stage owns, in symmetric (peer-mapped) memory, an inbox slot and a flag per
+micro-batch.  A stage step is ONE C call (``dli_stage_decode_step``) whose own kernels do the hand-off: the entry kernel
+spins on the stage's flag until the producer has stored the step's input, the exit kernel stores the ``[B, 1, h]``
+tensor straight into the next stage's inbox over NVLink, fences, and releases that stage's flag -- no send/recv kernel, no
+separate semaphore launches, no stream barrier between micro-batches (the steps of different micro-batches are chained
+with programmatic dependent launch).  Two kinds of ring:
+
+``hidden``  the last stage stores its output hidden states into stage 0's inbox (what the benchmark's device-timed
+            ``value`` measures: the spans alone, as the reference defines them -- it has no embedding and no head);
+``tokens``  SURVEY 8e: stage 0 looks the step's input up in the embedding table by device-resident token ids, the
+            last stage ends in final RMSNorm -> lm_head -> greedy argmax and stores token ids ``[B]`` into stage 0's
+            token inbox: the sequential client of the north star, closed on the GPUs.
+
+A whole steady-state round (every micro-batch once) is replayed as one CUDA graph per stage.  Prefill chunks and the
+fallback when symmetric memory is unavailable use ``torch.distributed`` ``isend/irecv`` (NCCL; gloo on CPU in tests).
 """
 from __future__ import annotations
 
-from typing import List, Optional, Sequence
+import ctypes as C
+from typing import Dict, List, Optional, Sequence
 
 import torch
 import torch.distributed as dist
 
 
+def _align(n: int, a: int = 256) -> int:
+    return (n + a - 1) // a * a
+
+
+class _Ring:
+    """Buffers, flags and captured step graphs of one ring kind on one stage."""
+
+    def __init__(self, kind: str):
+        self.kind = kind
+        self.graphs: Dict[str, object] = {}     # generation id -> GraphedDecode
+        self.round = None                        # (generation ids, CUDAGraph, kept objects)
+        self.steps = 0                           # stage steps launched per micro-batch so far (host mirror of state[:, 0])
+        self.gids: Sequence[str] = ()
+
+
 class PipelineStage:
     def __init__(self, span, cache, rank: int, world: int, device, hidden_size: Optional[int] = None,
-                 dtype=torch.bfloat16):
+                 dtype=torch.bfloat16, client: Optional[dict] = None):
+        """``client`` (token ring only): ``{"embed_tokens": [V, h]}`` on stage 0 and ``{"norm": [h], "lm_head": [V, h],
+        "norm_eps": float}`` on the last stage, bf16 on this stage's device."""
         self.span, self.cache = span, cache
         self.rank, self.world, self.device = rank, world, device
         self.hidden_size = hidden_size if hidden_size is not None else span.config.hidden_size
         self.dtype = dtype
+        self.client = client or {}
         self.launches_per_round = 0
         self._pending = []          # (work, tensor) of sends still in flight: keep tensors alive
-        self.graphs = {}            # generation id -> GraphedDecode (whole stage step as one CUDA graph)
+        self.rings: Dict[str, _Ring] = {}
         self.handoff = "nccl" if world > 1 else "local"
         self.handoff_error = None
-        self._ring_pending = False
-        self.trace = None           # set to [] to collect (recv_wait_ms, step_ms) CUDA-event pairs per micro-batch
-        self._round = None          # (generation ids, CUDA graph of a whole round, kept tensors): capture_round()
         self.round_error = None
+        self.trace = None           # set to [] to collect (start, end) CUDA-event pairs per micro-batch (per-step graphs)
 
-    def enable_graphs(self, generation_ids: Sequence[str], max_ctx: int, batch: Optional[int] = None,
-                      peer_store: bool = True) -> str:
-        """Capture this stage's decode step of every (prefilled) micro-batch into a CUDA graph.
+    # back-compat views used by bench.py / tests: the hidden ring's graphs
+    @property
+    def graphs(self):
+        r = self.rings.get("hidden")
+        return r.graphs if r is not None else {}
 
-        ``peer_store`` (multi-GPU, NVLink/NVSwitch): every stage owns an "inbox" ``[micro_batches, B, 1, h]`` in
-        symmetric memory (peer-mapped by all ranks).  Stage r's graph for micro-batch m reads its input from its own
-        inbox slot m and its LAST KERNEL writes the hand-off tensor directly into slot m of stage r+1's inbox over
-        NVLink — no send/recv kernel, no extra copy, nothing competing for SMs on a second stream; a one-word
-        semaphore per (edge, micro-batch) orders producer and consumer.  If symmetric memory cannot be set up the
-        stage falls back to NCCL ``isend/irecv`` into the graphs' static buffers.  Returns the hand-off mode."""
-        self.handoff = "local"
-        peer = None
-        if self.world > 1 and peer_store:
+    # ------------------------------------------------------------------------------------------ set-up
+    def _alloc_ring(self, ring: _Ring, n_mb: int, batch: int, peer_store: bool) -> bool:
+        """Inbox, token inbox and flags: symmetric memory when there are peers, plain device memory on one GPU."""
+        h = self.hidden_size
+        off_flags = 0
+        off_tok = _align(n_mb * 64)                                   # one 64-byte line per flag
+        off_inbox = off_tok + _align(n_mb * batch * 4)
+        total = off_inbox + _align(n_mb * batch * h * 2)
+        peers = {}
+        if self.world > 1:
+            if not peer_store:
+                return False
             try:
                 import torch.distributed._symmetric_memory as symm_mem
 
-                if batch is None:
-                    batch = self.cache.generation(generation_ids[0]).batch
-                shape = (len(generation_ids), batch, 1, self.hidden_size)
                 if hasattr(symm_mem, "enable_symm_mem_for_group"):
                     try:
                         symm_mem.enable_symm_mem_for_group(dist.group.WORLD.group_name)
                     except Exception:
                         pass
-                self.inbox = symm_mem.empty(shape, dtype=self.dtype, device=self.device)
-                self.inbox.zero_()
-                self.hdl = symm_mem.rendezvous(self.inbox, dist.group.WORLD)
-                peer = self.hdl.get_buffer((self.rank + 1) % self.world, shape, self.dtype)
-                self.handoff = "peer_store"
+                buf = symm_mem.empty((total,), dtype=torch.uint8, device=self.device)
+                buf.zero_()
+                hdl = symm_mem.rendezvous(buf, dist.group.WORLD)
+                for p in {(self.rank + 1) % self.world, 0}:
+                    peers[p] = hdl.get_buffer(p, (total,), torch.uint8)
+                ring.hdl = hdl
             except Exception as e:  # noqa: BLE001 - any failure means: use NCCL
                 self.handoff_error = repr(e)
-                peer = None
-        if self.world > 1 and peer is None:
-            self.handoff = "nccl"
-        ok = torch.tensor([1 if self.handoff != "nccl" else 0], device=self.device)
+                return False
+        else:
+            buf = torch.zeros(total, dtype=torch.uint8, device=self.device)
+            peers[0] = buf
+
+        def carve(b):
+            return (b[off_flags:off_flags + n_mb * 64].view(torch.int32).view(n_mb, 16),
+                    b[off_tok:off_tok + n_mb * batch * 4].view(torch.int32).view(n_mb, batch),
+                    b[off_inbox:off_inbox + n_mb * batch * h * 2].view(torch.bfloat16).view(n_mb, batch, 1, h))
+
+        ring.buf = buf
+        ring.flags, ring.tok_inbox, ring.inbox = carve(buf)
+        ring.peer = {p: carve(b) for p, b in peers.items()}
+        ring.state = torch.zeros(n_mb, 4, dtype=torch.int32, device=self.device)
+        return True
+
+    def enable_graphs(self, generation_ids: Sequence[str], max_ctx: int, batch: Optional[int] = None,
+                      peer_store: bool = True, ring: str = "hidden") -> str:
+        """Capture this stage's decode step of every (prefilled) micro-batch into a CUDA graph and set up the hand-off.
+        All stages call this together.  Returns the hand-off mode: ``peer_store`` (in-kernel flags over peer memory),
+        ``local`` (one GPU) or ``nccl`` (fallback: graphs with static buffers, isend/irecv between them)."""
+        from distributed_llm_inference_b200.models.llama.model import StageIO
+
+        if ring not in ("hidden", "tokens"):
+            raise ValueError(ring)
+        r = _Ring(ring)
+        first, last = self.rank == 0, self.rank == self.world - 1
+        if batch is None:
+            batch = self.cache.generation(generation_ids[0]).batch
+        n_mb = len(generation_ids)
+        ok = self._alloc_ring(r, n_mb, batch, peer_store)
+        flag = torch.tensor([1 if ok else 0], device=self.device)
         if self.world > 1:          # all stages must agree on the protocol
-            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-            if ok.item() == 0:
-                self.handoff, peer = "nccl", None
-        for m, gid in enumerate(generation_ids):
-            if peer is not None:
-                self.graphs[gid] = self.span.graphed_decode(gid, self.cache, max_ctx, x=self.inbox[m], out=peer[m])
-            else:
-                self.graphs[gid] = self.span.graphed_decode(gid, self.cache, max_ctx)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            ok = flag.item() == 1
+        if ring == "tokens" and not ok:
+            raise RuntimeError(f"the token ring needs peer-mapped memory: {self.handoff_error}")
+        r.gids = tuple(generation_ids)
+        if not ok:
+            self.handoff = "nccl"
+            for gid in generation_ids:
+                r.graphs[gid] = self.span.graphed_decode(gid, self.cache, max_ctx)
+        else:
+            self.handoff = "peer_store" if self.world > 1 else "local"
+            nxt = (self.rank + 1) % self.world
+            tokens = ring == "tokens"
+            if tokens and last:
+                V = self.client["lm_head"].shape[0]
+                r.logits = torch.zeros(batch, V, dtype=torch.float32, device=self.device)
+            for m, gid in enumerate(generation_ids):
+                p_flags, p_tok, p_inbox = r.peer[nxt]
+                io = StageIO(
+                    hidden_in=None if (tokens and first) else r.inbox[m],
+                    token_ids=r.tok_inbox[m] if (tokens and first) else None,
+                    embed_table=self.client["embed_tokens"] if (tokens and first) else None,
+                    hidden_out=None if (tokens and last) else p_inbox[m],
+                    final_norm=self.client["norm"] if (tokens and last) else None,
+                    lm_head=self.client["lm_head"] if (tokens and last) else None,
+                    logits=r.logits if (tokens and last) else None,
+                    tokens_out=p_tok[m] if (tokens and last) else None,
+                    eps_final=float(self.client.get("norm_eps", 1e-6)),
+                    wait_flag=r.flags[m], signal_flag=p_flags[m], state=r.state[m],
+                    wait_lag=1 if first else 0,
+                    chain=1 if n_mb > 1 else 0)       # consecutive steps in the stream belong to different generations
+                r.graphs[gid] = self.span.graphed_decode(gid, self.cache, max_ctx, stage=io)
+        self.rings[ring] = r
         if self.world > 1:
+            torch.cuda.synchronize(self.device)
             dist.barrier()
         return self.handoff
 
-    def capture_round(self, generation_ids: Sequence[str]) -> bool:
-        """Peer-store hand-off only: capture a whole steady-state round -- for every micro-batch ``wait(prev) -> stage
-        step -> signal(next)`` -- into ONE CUDA graph, so a round costs one graph launch instead of one per micro-batch
-        plus two semaphore launches each.  All stages must call this together; if any of them cannot capture, none uses
-        it.  The per-micro-batch graphs stay in place for the first round (fresh inputs) and for tracing."""
-        ok = 1 if (self.handoff == "peer_store" and all(g in self.graphs for g in generation_ids)) else 0
+    def capture_round(self, generation_ids: Sequence[str], ring: str = "hidden") -> bool:
+        """Peer-store hand-off only: capture a whole steady-state round -- every micro-batch's stage step, chained --
+        into ONE CUDA graph, so a round costs one graph launch.  All stages must call this together; if any of them
+        cannot capture, none uses it.  The per-micro-batch graphs stay in place (tracing, host-fed rounds)."""
+        r = self.rings.get(ring)
+        ok = 1 if (r is not None and self.handoff in ("peer_store", "local")
+                   and all(g in r.graphs for g in generation_ids)) else 0
         graph, keep = None, []
         if ok:
             try:
-                prev, nxt = (self.rank - 1) % self.world, (self.rank + 1) % self.world
                 torch.cuda.synchronize(self.device)
                 graph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(graph):
-                    for m, gid in enumerate(generation_ids):
-                        self.hdl.wait_signal(prev, m, 20000)
-                        keep.append(self.graphs[gid]._launch())
-                        self.hdl.put_signal(nxt, m, 20000)
+                    for gid in generation_ids:
+                        keep.append(r.graphs[gid]._launch())
             except Exception as e:  # noqa: BLE001 - any failure means: keep the per-micro-batch graphs
                 self.round_error = repr(e)
                 ok = 0
         flag = torch.tensor([ok], device=self.device)
         if self.world > 1:
             dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-        self._round = (tuple(generation_ids), graph, keep) if flag.item() == 1 else None
-        return self._round is not None
+        if r is not None:
+            r.round = (tuple(generation_ids), graph, keep) if flag.item() == 1 else None
+        return r is not None and r.round is not None
 
-    # -- P2P ------------------------------------------------------------------------------------------
+    @property
+    def _round(self):               # back-compat for tests
+        r = self.rings.get("hidden")
+        return None if r is None else r.round
+
+    # -- P2P (prefill chunks, NCCL fallback) --------------------------------------------------------------
     def _send(self, t: torch.Tensor, dst: int) -> None:
         self._pending.append((dist.isend(t, dst), t))
 
@@ -126,14 +216,18 @@ class PipelineStage:
 
     # -- one round: every micro-batch passes through this stage once --------------------------------------
     def run_round(self, generation_ids: Sequence[str], inputs: Optional[List[torch.Tensor]], batch: int, q_len: int,
-                  start_pos: int, feed_back: bool = True) -> Optional[List[torch.Tensor]]:
-        """Stage 0 consumes ``inputs`` (one ``[B, q_len, h]`` tensor per micro-batch); other stages receive theirs
-        from the previous stage.  Returns, on stage 0, the tensors that came back from the last stage (the next
-        round's inputs when ``feed_back``); ``None`` elsewhere."""
+                  start_pos: int, feed_back: bool = True, ring: str = "hidden") -> Optional[List[torch.Tensor]]:
+        """Stage 0 consumes ``inputs`` (one tensor per micro-batch: ``[B, q_len, h]`` hidden states, or ``[B]`` int32
+        token ids for the token ring); other stages receive theirs from the previous stage.  Returns, on stage 0, what
+        came back from the last stage (the next round's inputs when ``feed_back``); ``None`` elsewhere.  Graphed decode
+        rounds over peer memory always close the ring; pass ``inputs=None`` on stage 0 to let them feed themselves."""
         first, last = self.rank == 0, self.rank == self.world - 1
         self._reap()
-        if q_len == 1 and self.graphs:
-            return self._run_round_graphed(generation_ids, inputs, batch, feed_back)
+        r = self.rings.get(ring)
+        if q_len == 1 and r is not None and r.graphs:
+            if self.handoff == "nccl":
+                return self._run_round_graphed_nccl(r, generation_ids, inputs, batch, feed_back)
+            return self._run_round_flags(r, generation_ids, inputs)
         cp = torch.arange(start_pos, start_pos + q_len, device=self.device)
         shape = (batch, q_len, self.hidden_size)
         outs, launches = [], 0
@@ -154,28 +248,18 @@ class PipelineStage:
             return [self._recv(shape, self.world - 1) for _ in generation_ids]
         return outs if last else None
 
-    def _run_round_graphed(self, generation_ids, inputs, batch, feed_back):
-        if self.handoff == "peer_store":
-            return self._run_round_peer_store(generation_ids, inputs, feed_back)
+    def _run_round_graphed_nccl(self, r, generation_ids, inputs, batch, feed_back):
         first, last = self.rank == 0, self.rank == self.world - 1
         shape = (batch, 1, self.hidden_size)
         outs, launches = [], 0
         for m, gid in enumerate(generation_ids):
-            g = self.graphs[gid]
-            if self.trace is not None:
-                ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-                ev[0].record()
+            g = r.graphs[gid]
             if first:
                 if inputs[m].data_ptr() != g.x.data_ptr():
                     g.x.copy_(inputs[m])
             else:
                 self._recv(shape, self.rank - 1, out=g.x)
-            if self.trace is not None:
-                ev[1].record()
             y = g.step()
-            if self.trace is not None:
-                ev[2].record()
-                self.trace.append(ev)
             launches += g.launches
             if not last:
                 self._send(y, self.rank + 1)
@@ -187,55 +271,87 @@ class PipelineStage:
         if self.world == 1:
             return outs
         if first and feed_back:   # ring closure straight into the graphs' input buffers
-            return [self._recv(shape, self.world - 1, out=self.graphs[gid].x) for gid in generation_ids]
+            return [self._recv(shape, self.world - 1, out=r.graphs[gid].x) for gid in generation_ids]
         return outs if last else None
 
-    def _run_round_peer_store(self, generation_ids, inputs, feed_back):
-        """wait(prev, m) -> graph m (last kernel stores into the next stage's inbox) -> signal(next, m), all on one
-        stream.  A slot is never overwritten early: the producer's next write to it depends, through the ring, on the
-        consumer's previous step."""
-        first, last = self.rank == 0, self.rank == self.world - 1
-        prev, nxt = (self.rank - 1) % self.world, (self.rank + 1) % self.world
-        launches = 0
-        if (self._round is not None and feed_back and self.trace is None and tuple(generation_ids) == self._round[0]
-                and (not first or self._ring_pending)):
-            gs = [self.graphs[gid] for gid in generation_ids]
+    def inject(self, ring: str, m: int, x: torch.Tensor) -> None:
+        """Stage 0: put a fresh input (hidden states or token ids) at the head of the pipe for micro-batch ``m``.  The
+        slot is also the target of the ring closure, so the copy is ordered behind the arrival of the previous round's
+        result (a one-thread flag wait on this stream): the last stage can no longer overwrite what is injected."""
+        from distributed_llm_inference_b200 import _ffi
+
+        r = self.rings[ring]
+        dst = r.tok_inbox[m] if ring == "tokens" else r.inbox[m]
+        if x.data_ptr() == dst.data_ptr():
+            return
+        if r.steps > 0:
+            _ffi.check(_ffi.lib.dli_flag_wait(r.flags[m].data_ptr(), r.steps, r.state[m].data_ptr(), 2000,
+                                              _ffi.current_stream(self.device)))
+        dst.copy_(x.view(dst.shape) if x.numel() == dst.numel() else x, non_blocking=True)
+
+    def _run_round_flags(self, r, generation_ids, inputs):
+        """Every micro-batch's stage step, back to back on one stream; the cross-GPU order is carried by the flags the
+        steps' own entry / exit kernels wait on and release."""
+        first = self.rank == 0
+        gs = [r.graphs[gid] for gid in generation_ids]
+        if first and inputs is not None:
+            for m, x in enumerate(inputs):
+                self.inject(r.kind, m, x)
+        for g in gs:
+            g.before_replay()
+        if r.round is not None and self.trace is None and tuple(generation_ids) == r.round[0]:
+            r.round[1].replay()
+        else:
             for g in gs:
-                g.before_replay()
-            self._round[1].replay()
-            for g in gs:
-                g.after_replay()
-            self.launches_per_round = sum(g.launches + 2 for g in gs)
-            return [g.x for g in gs] if first else None
-        for m, gid in enumerate(generation_ids):
-            g = self.graphs[gid]
-            if self.trace is not None:
-                ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-                ev[0].record()
-            if first and not self._ring_pending:
-                if inputs[m].data_ptr() != g.x.data_ptr():
-                    g.x.copy_(inputs[m])                   # fresh input injected at the head of the pipe
-            else:
-                self.hdl.wait_signal(prev, m, 20000)
-            if self.trace is not None:
-                ev[1].record()
-            g.step()
-            if not last or feed_back:
-                self.hdl.put_signal(nxt, m, 20000)
-            if self.trace is not None:
-                ev[2].record()
-                self.trace.append(ev)
-            launches += g.launches + 2
-        self.launches_per_round = launches
+                if self.trace is not None:
+                    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+                    ev[0].record()
+                g.graph.replay()
+                if self.trace is not None:
+                    ev[1].record()
+                    self.trace.append(ev)
+        for g in gs:
+            g.after_replay()
+        r.steps += 1
+        self.launches_per_round = sum(g.launches for g in gs)
         if first:
-            self._ring_pending = feed_back
-        if first and feed_back:
-            return [self.graphs[gid].x for gid in generation_ids]   # filled by the last stage; waited on next round
+            return [r.tok_inbox[m] if r.kind == "tokens" else r.inbox[m] for m in range(len(gs))]
         return None
 
-    def drain(self, n_micro_batches: int) -> None:
-        """Stage 0: consume the ring-closure signals of the last round (before switching hand-off mode)."""
-        if self.handoff == "peer_store" and self.rank == 0 and self._ring_pending:
-            for m in range(n_micro_batches):
-                self.hdl.wait_signal(self.world - 1, m, 20000)
-            self._ring_pending = False
+    def step_one(self, ring: str, m: int) -> None:
+        """Launch micro-batch ``m``'s stage step alone (host-fed rounds interleave host work between the steps); the
+        caller finishes the round with ``end_round``."""
+        g = self.rings[ring].graphs[self.rings[ring].gids[m]]
+        g.before_replay()
+        g.graph.replay()
+        g.after_replay()
+
+    def end_round(self, ring: str) -> None:
+        self.rings[ring].steps += 1
+
+    def wait_result(self, ring: str, m: int, stream) -> None:
+        """Stage 0: make ``stream`` wait until the last stage's result of the LATEST launched round for micro-batch ``m``
+        has arrived in this stage's inbox (one-thread kernel; time-out recorded in the step state)."""
+        from distributed_llm_inference_b200 import _ffi
+
+        r = self.rings[ring]
+        _ffi.check(_ffi.lib.dli_flag_wait(r.flags[m].data_ptr(), r.steps, r.state[m].data_ptr(), 2000, stream.cuda_stream))
+
+    def check_errors(self) -> None:
+        """After a synchronise: raise if any in-kernel flag wait gave up (a producer never signalled)."""
+        for kind, r in self.rings.items():
+            if hasattr(r, "state") and bool(r.state[:, 2].any().item()):
+                raise RuntimeError(f"stage {self.rank}: a hand-off wait of the {kind} ring timed out "
+                                   f"(state {r.state.tolist()}, flags {r.flags[:, 0].tolist()})")
+
+    def drain(self, n_micro_batches: int = 0) -> None:
+        """Wait until everything launched so far -- including the ring closure into stage 0 -- has completed."""
+        if str(self.device) != "cpu":
+            for kind, r in self.rings.items():
+                if self.rank == 0 and r.steps > 0 and hasattr(r, "flags"):
+                    from distributed_llm_inference_b200 import _ffi
+
+                    for m in range(len(r.gids)):
+                        _ffi.check(_ffi.lib.dli_flag_wait(r.flags[m].data_ptr(), r.steps, r.state[m].data_ptr(), 2000,
+                                                          _ffi.current_stream(self.device)))
+            torch.cuda.synchronize(self.device)

@@ -229,6 +229,68 @@ int dli_span_decode_step(dli_span* span, const dli_kv_desc* kv, int batch, const
                          const float* cos_table, const float* sin_table, long long* position, int advance,
                          void* workspace, size_t workspace_bytes, dli_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Pipeline stage step: dli_span_decode_step plus the hand-off between consecutive spans, which in the reference is
+ * a network hop through hivemind (only imported, server/backend.py:4-7; SURVEY 8b "dli_p2p_*", 8e) and here is done by
+ * the step's own first and last kernels over NVLink peer memory:
+ *   - INPUT   hidden_in: bf16 [batch, h] in THIS GPU's memory (a hand-off inbox the previous stage stores into), or
+ *             token_ids + embed_table: device int32 [batch] ids whose rows of the bf16 [vocab, h] table are the input
+ *             (stage 0 of a ring that carries tokens: the embedding the client would look up).
+ *   - WAIT    wait_flag (this GPU's memory, nullable): the entry kernel spins on it (ld.acquire.sys) until
+ *             *wait_flag + wait_lag >= state[0] + 1, i.e. until the producer has finished the step that feeds this one.
+ *             wait_lag = 0 when the producer runs the same round earlier (stage r-1 -> r), 1 when it is a round behind
+ *             (ring closure: last stage -> stage 0, which therefore starts round 0 without waiting).
+ *   - OUTPUT  hidden_out: bf16 [batch, h], this GPU's or a PEER's memory (the next stage's inbox), nullable when the
+ *             stage ends in the head; lm_head (nullable): bf16 [vocab, h] -- final RMSNorm (final_norm, eps_final) ->
+ *             logits fp32 [batch, vocab] (this GPU) -> greedy argmax -> tokens_out int32 [batch] (this GPU's or a
+ *             peer's memory: stage 0's token inbox).  The tail of the client (norm, head, argmax; absent from the
+ *             reference, model.py:19-23) as three more kernels of the same chain.
+ *   - SIGNAL  after all of the last kernel's stores are fenced system-wide, state[0] += 1 and, if signal_flag is not
+ *             NULL, *signal_flag = state[0] (st.release.sys; usually the consumer's wait_flag in peer memory).
+ *   state: 4 x uint32 in this GPU's memory, zero-initialised by the caller: [0] steps completed, [1] ticket (0 between
+ *   steps), [2] sticky error: a wait gave up after timeout_ms (default 2000) -- later waits return at once and the step
+ *   computes garbage instead of hanging the GPU; the host checks it after synchronising.  [3] unused.
+ *   chain != 0: the entry kernel is launched with programmatic dependent launch like the kernels inside the step, no
+ *   stream barrier in front of it.  Only valid when the launches that precede the step in the stream belong to OTHER
+ *   generations (the other micro-batches of a pipeline round, a whole round between two steps of the same one):
+ *   pre-wait prologues read the generation's lengths and past K/V.
+ * Everything else (cos/sin tables, *position, advance, workspace) is as in dli_span_decode_step. */
+typedef struct dli_stage_io {
+  const void* hidden_in;
+  const int32_t* token_ids;
+  const void* embed_table;
+  void* hidden_out;
+  const void* final_norm; /* bf16 [h] */
+  const void* lm_head;    /* bf16 [vocab, h] */
+  float* logits;
+  int32_t* tokens_out;
+  int32_t vocab;
+  float eps_final;
+  const uint32_t* wait_flag;
+  uint32_t* signal_flag;
+  uint32_t* state;
+  int32_t wait_lag;
+  int32_t chain;
+  int32_t timeout_ms;
+} dli_stage_io;
+
+int dli_stage_decode_step(dli_span* span, const dli_kv_desc* kv, int batch, const dli_stage_io* io,
+                          const float* cos_table, const float* sin_table, long long* position, int advance,
+                          void* workspace, size_t workspace_bytes, dli_stream_t stream);
+
+/* Stream-ordered wait (one thread) until *flag has reached at_least (counters compared modulo 2^32), with the same
+ * time-out and sticky error word (state[2]) as the in-kernel wait: what a client puts on a side stream in front of
+ * the copy that reads a result another GPU delivers.  No counterpart in the reference. */
+int dli_flag_wait(const uint32_t* flag, uint32_t at_least, uint32_t* state, int timeout_ms, dli_stream_t stream);
+
+/* Client tail as one call: xn = RMSNorm(hidden; final_norm, eps) (bf16 [batch, h] scratch), logits = xn . lm_head^T
+ * (fp32 [batch, vocab]), tokens_out[b] = argmax_v logits[b, v] (int32, lowest index on ties).  hidden is bf16 or fp32
+ * [batch, h], batch <= 128.  The reference builds neither norm nor head (model.py:19-23); this is what its client
+ * would run after the last span. */
+int dli_lm_head_argmax(const void* hidden, int hidden_is_f32, const void* final_norm_bf16, float eps,
+                       const void* lm_head_bf16, int vocab, int h, int batch, void* xn_bf16, float* logits,
+                       int32_t* tokens_out, dli_stream_t stream);
+
 /* Per-kernel-class timing of dli_span_forward, measured with CUDA events recorded on the call's own stream
  * at every class boundary (bench.py's roofline figures).  dli_span_profile(span, 1) starts collecting (host-side
  * cudaEvent objects are created on demand; no device memory); every forward after that appends intervals;
