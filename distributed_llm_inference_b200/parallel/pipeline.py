@@ -11,8 +11,7 @@ Decode hand-off (``enable_graphs``): every stage owns, in symmetric (peer-mapped
 micro-batch.  A stage step is ONE C call (``dli_stage_decode_step``) whose own kernels do the hand-off: the entry kernel
 spins on the stage's flag until the producer has stored the step's input, the exit kernel stores the ``[B, 1, h]``
 tensor straight into the next stage's inbox over NVLink, fences, and releases that stage's flag -- no send/recv kernel, no
-separate semaphore launches, no stream barrier between micro-batches (the steps of different micro-batches are chained
-with programmatic dependent launch).  Two kinds of ring:
+separate semaphore launches.  Two kinds of ring:
 
 ``hidden``  the last stage stores its output hidden states into stage 0's inbox (what the benchmark's device-timed
             ``value`` measures: the spans alone, as the reference defines them -- it has no embedding and no head);
@@ -63,6 +62,8 @@ class PipelineStage:
         self.handoff = "nccl" if world > 1 else "local"
         self.handoff_error = None
         self.round_error = None
+        self.chain_steps = False    # True: chain the steps of different micro-batches with programmatic dependent launch
+                                    # (measured on 2 GPUs: no gain over the stream barrier in front of each step)
         self.trace = None           # set to [] to collect (start, end) CUDA-event pairs per micro-batch (per-step graphs)
 
     # back-compat views used by bench.py / tests: the hidden ring's graphs
@@ -162,7 +163,7 @@ class PipelineStage:
                     eps_final=float(self.client.get("norm_eps", 1e-6)),
                     wait_flag=r.flags[m], signal_flag=p_flags[m], state=r.state[m],
                     wait_lag=1 if first else 0,
-                    chain=1 if n_mb > 1 else 0)       # consecutive steps in the stream belong to different generations
+                    chain=1 if (n_mb > 1 and self.chain_steps) else 0)       # consecutive steps in the stream belong to different generations
                 r.graphs[gid] = self.span.graphed_decode(gid, self.cache, max_ctx, stage=io)
         self.rings[ring] = r
         if self.world > 1:
