@@ -27,6 +27,7 @@ EXPORTS = (
     "dli_span_workspace_bytes", "dli_span_forward", "dli_last_launch_count", "dli_span_profile",
     "dli_span_profile_read", "dli_decode_attention_static", "dli_kv_evict", "dli_span_decode_step",
     "dli_stage_decode_step", "dli_flag_wait", "dli_lm_head_argmax",
+    "dli_span_forward_masked", "dli_prefill_attention_masked", "dli_decode_attention_masked",
 )
 
 
@@ -50,6 +51,10 @@ class SpanDesc(C.Structure):
 class LayerWeights(C.Structure):
     _fields_ = [("wqkv", C.c_void_p), ("wo", C.c_void_p), ("wgu", C.c_void_p), ("wdown", C.c_void_p),
                 ("g_in", C.c_void_p), ("g_post", C.c_void_p)]
+
+
+class AttnMask(C.Structure):
+    _fields_ = [("key_limit", C.c_void_p), ("key_valid", C.c_void_p), ("key_stride", C.c_int32)]
 
 
 class StageIo(C.Structure):
@@ -92,6 +97,9 @@ def _load() -> C.CDLL:
         "dli_span_decode_step": (C.c_int, [vp, C.POINTER(KvDesc), i32, vp, vp, vp, vp, vp, i32, vp, sz, vp]),
         "dli_stage_decode_step": (C.c_int, [vp, C.POINTER(KvDesc), i32, C.POINTER(StageIo), vp, vp, vp, i32, vp, sz, vp]),
         "dli_flag_wait": (C.c_int, [vp, C.c_uint32, vp, i32, vp]),
+        "dli_span_forward_masked": (C.c_int, [vp, C.POINTER(KvDesc), i32, i32, i32, C.POINTER(AttnMask), vp, vp, vp, vp, vp, vp, sz, vp]),
+        "dli_prefill_attention_masked": (C.c_int, [vp, vp, C.POINTER(KvDesc), i32, i32, i32, i32, i32, i32, i32, C.POINTER(AttnMask), vp]),
+        "dli_decode_attention_masked": (C.c_int, [vp, vp, C.POINTER(KvDesc), i32, i32, i32, i32, i32, C.POINTER(AttnMask), vp, sz, vp]),
         "dli_lm_head_argmax": (C.c_int, [vp, i32, vp, f32, vp, i32, i32, i32, vp, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():

@@ -61,7 +61,7 @@ template <int HD, int G>
 __global__ void __launch_bounds__(DEC_THREADS) decode_attn_direct_kernel(const __nv_bfloat16* __restrict__ q, KvView kv,
                                                                   float* __restrict__ scratch,
                                                                   __nv_bfloat16* __restrict__ out, int H, int KV,
-                                                                  float scale_log2) {
+                                                                  float scale_log2, AttnMask mask) {
   constexpr int LPT = HD / 8;                // lanes per token
   constexpr int GPW = 32 / LPT;              // token groups per warp
   constexpr int NG = (DEC_THREADS / 32) * GPW;  // token groups per CTA
@@ -119,7 +119,10 @@ __global__ void __launch_bounds__(DEC_THREADS) decode_attn_direct_kernel(const _
     fetch(t0 + NG * UNROLL, nk, nv);
     bool ok[UNROLL];
 #pragma unroll
-    for (int u = 0; u < UNROLL; ++u) ok[u] = t0 + grp + u * NG < t_end;
+    for (int u = 0; u < UNROLL; ++u) {
+      const int tt = t0 + grp + u * NG;
+      ok[u] = tt < t_end && (!mask.key_valid || mask.key_valid[(long long)b * mask.key_stride + tt] != 0);  // padded keys
+    }
     float s[UNROLL][G];
 #pragma unroll
     for (int u = 0; u < UNROLL; ++u) {
@@ -185,7 +188,7 @@ __global__ void __launch_bounds__(DEC_THREADS) decode_attn_direct_kernel(const _
       }
     }
     if (n_splits == 1) {  // the whole context in one CTA: normalise and store, no combine pass
-      out[((long long)b * H + kvh * G + g) * HD + d] = __float2bfloat16_rn(O / L);
+      out[((long long)b * H + kvh * G + g) * HD + d] = __float2bfloat16_rn(L > 0.f ? O / L : 0.f);
     } else {
       float* dst = scratch + (((long long)b * H + kvh * G + g) * n_splits + split) * (HD + 2);
       dst[d] = O;
@@ -471,7 +474,7 @@ __global__ void __launch_bounds__(HD) decode_combine_kernel(const float* __restr
     L = fmaf(src[s * (HD + 2) + HD + 1], w, L);
     O = fmaf(src[s * (HD + 2) + d], w, O);
   }
-  out[((long long)b * H + h) * HD + d] = __float2bfloat16_rn(O / L);
+  out[((long long)b * H + h) * HD + d] = __float2bfloat16_rn(L > 0.f ? O / L : 0.f);
 }
 
 template <int HD, int G>
@@ -482,7 +485,7 @@ static int launch_dec(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& 
   int rc;
   if (direct) {
     rc = launch_kernel("decode_attn_direct_kernel", decode_attn_direct_kernel<HD, G>, dim3(splits, KV, batch),
-                       dim3(DEC_THREADS), 0, st, q, kv, scratch, out, H, KV, scale_log2);
+                       dim3(DEC_THREADS), 0, st, q, kv, scratch, out, H, KV, scale_log2, AttnMask{nullptr, nullptr, 0});
   } else {
     DLI_ONCE_PER_DEVICE(cudaFuncSetAttribute(decode_attn_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        dec_smem_bytes<HD, G>()));  // > 48 KB dynamic shared memory: opt-in per device
@@ -536,6 +539,38 @@ int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const Kv
   DLI_DEC_CASE(64, 1); DLI_DEC_CASE(64, 2); DLI_DEC_CASE(64, 4); DLI_DEC_CASE(64, 8);
 #undef DLI_DEC_CASE
   return fail(DLI_ERR_UNSUPPORTED, "dli_decode_attention: head_dim %d with GQA group %d is not instantiated", hd, G);
+}
+
+// Decode attention with padded keys (dli_decode_attention_masked): the register-staged kernel with a validity check per
+// key; a padded batch is the rare path, the tensor-core GQA and bulk-copy kernels stay mask-free.
+template <int HD, int G>
+static int launch_dec_masked(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV, int splits,
+                             float* scratch, const AttnMask& mask, cudaStream_t st) {
+  const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
+  int rc = launch_kernel("decode_attn_direct_kernel<masked>", decode_attn_direct_kernel<HD, G>, dim3(splits, KV, batch),
+                         dim3(DEC_THREADS), 0, st, q, kv, scratch, out, H, KV, scale_log2, mask);
+  if (rc || splits == 1) return rc;
+  return launch_kernel("decode_combine_kernel", decode_combine_kernel<HD>, dim3(H, batch), dim3(HD), 0, st,
+                       (const float*)scratch, out, H, splits);
+}
+
+int launch_decode_attention_masked(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV,
+                                   int hd, const AttnMask& mask, float* scratch, size_t scratch_bytes, cudaStream_t st) {
+  DLI_REQUIRE(q && out && scratch, "dli_decode_attention_masked: null pointer");
+  DLI_REQUIRE(batch > 0 && H > 0 && KV > 0 && H % KV == 0, "dli_decode_attention_masked: batch=%d H=%d KV=%d", batch, H, KV);
+  DLI_REQUIRE(!mask.key_valid || mask.key_stride >= kv.max_ctx, "dli_decode_attention_masked: key_valid rows of %d entries < context %d",
+              mask.key_stride, kv.max_ctx);
+  const int G = H / KV;
+  const int splits = decode_splits(batch, KV, kv.max_ctx, 2 * sm_count());
+  const size_t need = (size_t)batch * H * splits * (hd + 2) * sizeof(float);
+  if (scratch_bytes < need)
+    return fail(DLI_ERR_WORKSPACE, "dli_decode_attention_masked: scratch %zu bytes < %zu needed", scratch_bytes, need);
+#define DLI_DEC_CASE(HD_, G_) \
+  if (hd == HD_ && G == G_) return launch_dec_masked<HD_, G_>(q, out, kv, batch, H, KV, splits, scratch, mask, st)
+  DLI_DEC_CASE(128, 1); DLI_DEC_CASE(128, 2); DLI_DEC_CASE(128, 4); DLI_DEC_CASE(128, 8);
+  DLI_DEC_CASE(64, 1); DLI_DEC_CASE(64, 2); DLI_DEC_CASE(64, 4); DLI_DEC_CASE(64, 8);
+#undef DLI_DEC_CASE
+  return fail(DLI_ERR_UNSUPPORTED, "dli_decode_attention_masked: head_dim %d with GQA group %d is not instantiated", hd, G);
 }
 
 // -------------------------------------------------------------------------------------------------------

@@ -32,10 +32,18 @@ __device__ __forceinline__ uint32_t swz(int r, int c) {
   return (uint32_t)(r * HD * 2 + ((c ^ (r & 7)) << 4));
 }
 
-template <int HD, int NWARPS, int NBUF>
+// MASKED instantiation (dli_prefill_attention_masked): visibility comes from a per-query key limit and / or a
+// per-sequence key validity map instead of the causal flag alone.  Hidden scores take a large FINITE negative value, as
+// the reference's additive finfo.min mask does (model.py:106-135): a row with no visible key at all (a left-padding
+// query) then comes out as the uniform average of V over the whole context, exactly like the reference's softmax of a
+// row of equal entries; rows with at least one visible key give hidden keys probability 0.
+constexpr float PF_MASKED = -3.0e38f;
+
+template <int HD, int NWARPS, int NBUF, bool MASKED = false>
 __global__ void __launch_bounds__(NWARPS * 32) prefill_attn_kernel(const __nv_bfloat16* __restrict__ q,
                                                                    __nv_bfloat16* __restrict__ out, KvView kv, int q_len,
-                                                                   int H, int KV, int causal, float scale_log2) {
+                                                                   int H, int KV, int causal, float scale_log2,
+                                                                   AttnMask mask) {
   constexpr int CPR = HD / 8;          // 16-byte chunks per row
   constexpr int BM = NWARPS * 16;      // queries per CTA
   constexpr int NT = NWARPS * 32;
@@ -54,7 +62,7 @@ __global__ void __launch_bounds__(NWARPS * 32) prefill_attn_kernel(const __nv_bf
   const int32_t* bt = kv.block_table + (long long)b * kv.max_pages;
 
   int kv_end = T;
-  if (causal) kv_end = min(T, past + m0 + BM);
+  if (causal && !MASKED) kv_end = min(T, past + m0 + BM);
   const int n_tiles = (kv_end + PF_BN - 1) / PF_BN;
 
   auto load_kv = [&](int tile) {  // K/V rows of keys [tile*64, +64) -> buffer tile&1 (zeros past T)
@@ -117,7 +125,7 @@ __global__ void __launch_bounds__(NWARPS * 32) prefill_attn_kernel(const __nv_bf
     }
     const uint32_t sK = sK0 + (tile % NBUF) * KV_TILE_BYTES, sV = sV0 + (tile % NBUF) * KV_TILE_BYTES;
 
-    if (!causal || j0 <= warp_last_pos) {  // warp-uniform: tiles entirely above this warp's diagonal are skipped
+    if (MASKED || !causal || j0 <= warp_last_pos) {  // warp-uniform: tiles entirely above this warp's diagonal are skipped
       // ---- S = Q K^T (16 x 64 per warp) ----
       float s[PF_BN / 8][4];
 #pragma unroll
@@ -136,7 +144,15 @@ __global__ void __launch_bounds__(NWARPS * 32) prefill_attn_kernel(const __nv_bf
       }
 
       // ---- mask (only on tiles that touch the diagonal or the end of the context) + online softmax ----
-      const bool need_mask = (j0 + PF_BN > T) || (causal && j0 + PF_BN - 1 > past + m0 + warp * 16);
+      const bool need_mask = MASKED || (j0 + PF_BN > T) || (causal && j0 + PF_BN - 1 > past + m0 + warp * 16);
+      int lim[2] = {T, T};
+      if (MASKED && mask.key_limit) {
+#pragma unroll
+        for (int r2 = 0; r2 < 2; ++r2) {
+          const int qi = m0 + warp * 16 + g + r2 * 8;
+          lim[r2] = qi < q_len ? mask.key_limit[qi] : 0;
+        }
+      }
       float mx[2] = {-INFINITY, -INFINITY};
 #pragma unroll
       for (int n = 0; n < PF_BN / 8; ++n) {
@@ -146,7 +162,12 @@ __global__ void __launch_bounds__(NWARPS * 32) prefill_attn_kernel(const __nv_bf
           if (need_mask) {
             const int j = j0 + n * 8 + 2 * t4 + (e & 1);
             const int pos = pos0 + (e >> 1) * 8;
-            if (!(j < T && (!causal || j <= pos))) v = -INFINITY;
+            if (MASKED) {
+              if (j >= T) v = -INFINITY;
+              else if ((mask.key_limit ? j >= lim[e >> 1] : (causal && j > pos)) ||
+                       (mask.key_valid && mask.key_valid[(long long)b * mask.key_stride + j] == 0))
+                v = PF_MASKED;
+            } else if (!(j < T && (!causal || j <= pos))) v = -INFINITY;
           }
           s[n][e] = v;
           mx[e >> 1] = fmaxf(mx[e >> 1], v);
@@ -225,7 +246,31 @@ static int launch_pf(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& k
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
   dim3 grid((q_len + BM - 1) / BM, H, batch);
   return launch_kernel("prefill_attn_kernel", prefill_attn_kernel<HD, NWARPS, NBUF>, grid, dim3(NWARPS * 32), smem, st, q, out, kv,
-                       q_len, H, KV, causal ? 1 : 0, scale_log2);
+                       q_len, H, KV, causal ? 1 : 0, scale_log2, AttnMask{nullptr, nullptr, 0});
+}
+
+template <int HD>
+static int launch_pf_masked(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H, int KV,
+                            bool causal, const AttnMask& mask, cudaStream_t st) {
+  constexpr int NWARPS = 4, NBUF = 1, BM = NWARPS * 16;
+  const size_t smem = (size_t)(BM + 2 * NBUF * PF_BN) * HD * 2;
+  DLI_ONCE_PER_DEVICE(cudaFuncSetAttribute(prefill_attn_kernel<HD, NWARPS, NBUF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const float scale_log2 = 1.4426950408889634f / sqrtf((float)HD);
+  dim3 grid((q_len + BM - 1) / BM, H, batch);
+  return launch_kernel("prefill_attn_kernel<masked>", prefill_attn_kernel<HD, NWARPS, NBUF, true>, grid, dim3(NWARPS * 32), smem, st,
+                       q, out, kv, q_len, H, KV, causal ? 1 : 0, scale_log2, mask);
+}
+
+int launch_prefill_attention_masked(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H,
+                                    int KV, int hd, bool causal, const AttnMask& mask, cudaStream_t st) {
+  DLI_REQUIRE(q && out, "dli_prefill_attention_masked: null pointer");
+  DLI_REQUIRE(batch > 0 && q_len > 0 && H > 0 && KV > 0 && H % KV == 0, "dli_prefill_attention_masked: batch=%d q_len=%d H=%d KV=%d",
+              batch, q_len, H, KV);
+  DLI_REQUIRE(!mask.key_valid || mask.key_stride >= kv.max_ctx, "dli_prefill_attention_masked: key_valid rows of %d entries < context %d",
+              mask.key_stride, kv.max_ctx);
+  if (hd == 128) return launch_pf_masked<128>(q, out, kv, batch, q_len, H, KV, causal, mask, st);
+  if (hd == 64) return launch_pf_masked<64>(q, out, kv, batch, q_len, H, KV, causal, mask, st);
+  return fail(DLI_ERR_UNSUPPORTED, "dli_prefill_attention_masked: head_dim %d is not instantiated (64, 128)", hd);
 }
 
 int launch_prefill_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H,

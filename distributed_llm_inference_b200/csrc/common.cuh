@@ -163,6 +163,17 @@ struct ExitArgs {
   uint32_t* state;        // nullable: no counter, no signal
 };
 
+// Attention masks beyond the causal flag (dli_attn_mask in include/dli_b200.h), passed by value to the kernels.
+struct AttnMask {
+  const int32_t* key_limit;   // device [q_len] or nullptr: query l sees cache slots j < key_limit[l]
+  const uint8_t* key_valid;   // device [batch, key_stride] or nullptr: 0 = padded key, visible to no query
+  int key_stride;
+};
+int launch_prefill_attention_masked(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int q_len, int H,
+                                    int KV, int hd, bool causal, const AttnMask& mask, cudaStream_t st);
+int launch_decode_attention_masked(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV,
+                                   int hd, const AttnMask& mask, float* scratch, size_t scratch_bytes, cudaStream_t st);
+
 // ---- other launchers ----------------------------------------------------------------------------------
 int launch_rmsnorm_entry(const void* x, const __nv_bfloat16* w, __nv_bfloat16* y, float* resid_out, int rows, int h, float eps,
                          const EntryArgs& ea, cudaStream_t st);

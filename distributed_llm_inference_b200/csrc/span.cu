@@ -355,7 +355,7 @@ size_t dli_span_workspace_bytes(const dli_span* span, int max_tokens, int max_ba
 static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, int causal, const void* hidden_in,
                              void* hidden_out, const float* cos, const float* sin, void* all_hidden, void* workspace,
                              size_t workspace_bytes, dli_stream_t stream, const StepState& step,
-                             const dli_stage_io* io = nullptr);
+                             const dli_stage_io* io = nullptr, const dli_attn_mask* mask = nullptr);
 
 int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, int causal, const void* hidden_in,
                      void* hidden_out, const float* cos, const float* sin, void* all_hidden, void* workspace,
@@ -363,6 +363,39 @@ int dli_span_forward(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, i
   const StepState none{nullptr, nullptr, nullptr, 0, false};
   return span_forward_impl(s, kv, batch, q_len, causal, hidden_in, hidden_out, cos, sin, all_hidden, workspace,
                            workspace_bytes, stream, none);
+}
+
+int dli_span_forward_masked(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, int causal, const dli_attn_mask* mask,
+                            const void* hidden_in, void* hidden_out, const float* cos, const float* sin, void* all_hidden,
+                            void* workspace, size_t workspace_bytes, dli_stream_t stream) {
+  DLI_REQUIRE(mask && (mask->key_limit || mask->key_valid), "dli_span_forward_masked: empty mask (use dli_span_forward)");
+  const StepState none{nullptr, nullptr, nullptr, 0, false};
+  return span_forward_impl(s, kv, batch, q_len, causal, hidden_in, hidden_out, cos, sin, all_hidden, workspace,
+                           workspace_bytes, stream, none, nullptr, mask);
+}
+
+int dli_prefill_attention_masked(const void* q_bf16, void* out_bf16, const dli_kv_desc* kv, int layer, int batch, int q_len,
+                                 int n_heads, int n_kv_heads, int head_dim, int causal, const dli_attn_mask* mask,
+                                 dli_stream_t stream) {
+  DLI_REQUIRE(mask, "dli_prefill_attention_masked: null mask");
+  KvView v;
+  int rc = kv_view(kv, layer, &v);
+  if (rc) return rc;
+  return launch_prefill_attention_masked((const __nv_bfloat16*)q_bf16, (__nv_bfloat16*)out_bf16, v, batch, q_len, n_heads,
+                                         n_kv_heads, head_dim, causal != 0, AttnMask{mask->key_limit, mask->key_valid, mask->key_stride},
+                                         (cudaStream_t)stream);
+}
+
+int dli_decode_attention_masked(const void* q_bf16, void* out_bf16, const dli_kv_desc* kv, int layer, int batch, int n_heads,
+                                int n_kv_heads, int head_dim, const dli_attn_mask* mask, float* scratch, size_t scratch_bytes,
+                                dli_stream_t stream) {
+  DLI_REQUIRE(mask, "dli_decode_attention_masked: null mask");
+  KvView v;
+  int rc = kv_view(kv, layer, &v);
+  if (rc) return rc;
+  return launch_decode_attention_masked((const __nv_bfloat16*)q_bf16, (__nv_bfloat16*)out_bf16, v, batch, n_heads, n_kv_heads,
+                                        head_dim, AttnMask{nullptr, mask->key_valid, mask->key_stride}, scratch, scratch_bytes,
+                                        (cudaStream_t)stream);
 }
 
 int dli_span_decode_step(dli_span* s, const dli_kv_desc* kv, int batch, const void* hidden_in, void* hidden_out,
@@ -419,7 +452,8 @@ int dli_lm_head_argmax(const void* hidden, int hidden_is_f32, const void* final_
 
 static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int q_len, int causal, const void* hidden_in,
                              void* hidden_out, const float* cos, const float* sin, void* all_hidden, void* workspace,
-                             size_t workspace_bytes, dli_stream_t stream, const StepState& step, const dli_stage_io* io) {
+                             size_t workspace_bytes, dli_stream_t stream, const StepState& step, const dli_stage_io* io,
+                             const dli_attn_mask* mask) {
   reset_launch_count();
   DLI_REQUIRE(s && kv && cos && sin && workspace && (io || (hidden_in && hidden_out)), "dli_span_forward: null pointer");
   DLI_REQUIRE(batch > 0 && q_len > 0, "dli_span_forward: batch=%d q_len=%d", batch, q_len);
@@ -481,7 +515,7 @@ static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int 
     //            the buffer behind itself) or, when the context is not split, the attention kernel does that work
     //            itself (rope_inline.cuh) -- one launch less per layer.
     const bool fused_rope = !skinny && s->n_qkv % 256 == 0 && gemm_persistent_enabled();
-    const bool fused_dec_rope = !fused_rope && q_len == 1 && skinny &&
+    const bool fused_dec_rope = !fused_rope && q_len == 1 && skinny && !mask &&
                                 decode_attention_fuses_rope(view, batch, d.n_heads, d.n_kv_heads, d.head_dim);
     if (fused_rope) {
       RopeArgs ra{cos, sin, w.qbuf, view, q_len, d.n_heads, d.n_kv_heads, d.head_dim};
@@ -498,7 +532,15 @@ static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int 
       }
     }
     // attention core (modules.py:87-105)
-    if (q_len == 1) {
+    if (mask) {  // padded keys / per-query key limits (model.py:103-135 beyond the causal flag): the generic kernels
+      const AttnMask am{mask->key_limit, mask->key_valid, mask->key_stride};
+      if (q_len == 1)
+        DLI_STEP(DLI_PROF_ATTENTION, launch_decode_attention_masked(attn_in, w.attn, view, batch, d.n_heads, d.n_kv_heads,
+                                                                    d.head_dim, am, w.dec_scratch, w.dec_scratch_bytes, st));
+      else
+        DLI_STEP(DLI_PROF_ATTENTION, launch_prefill_attention_masked(attn_in, w.attn, view, batch, q_len, d.n_heads,
+                                                                     d.n_kv_heads, d.head_dim, causal != 0, am, st));
+    } else if (q_len == 1) {
       const DecRope dr{w.qkv_acc, cos, sin, s->n_qkv, step.pos};
       DLI_STEP(DLI_PROF_ATTENTION,
                launch_decode_attention(attn_in, w.attn, view, batch, d.n_heads, d.n_kv_heads, d.head_dim, w.dec_scratch,

@@ -14,11 +14,11 @@ Same constructor signature ``(window_length, num_sink_tokens)`` (cache.py:11), s
   * the constructor works (the reference's raises, cache.py:12 / SURVEY D1);
   * layers are indexed by their LOCAL position in the span (SURVEY D3);
   * attention-sink eviction (cache.py:111-133) runs as one in-place kernel over all layers of the span
-    (``evict`` -> ``dli_kv_evict``) for single-token steps; a multi-token chunk that would overflow the window
-    raises ``NotImplementedError`` (the reference's mask is then position-dependent in a way the kernels'
-    ``causal`` flag does not express);
+    (``evict`` -> ``dli_kv_evict``), for single tokens and for multi-token chunks alike (the chunk must leave room for
+    at least one kept token: ``n < window - sinks``);
   * ``update()`` (the per-layer tensor API of cache.py:64-135) is provided for callers that hold K/V
-    tensors themselves; the span forward does not use it — its fused kernel appends in place.
+    tensors themselves, eviction and cos/sin history included; the span forward does not use it — its fused
+    kernels append in place.
 """
 from __future__ import annotations
 
@@ -29,7 +29,7 @@ import torch
 
 class _Generation:
     __slots__ = ("batch", "length", "pages", "block_table", "seq_lens", "max_pages", "seen_tokens", "first_pos",
-                 "evictions")
+                 "evictions", "cos_hist", "sin_hist")
 
     def __init__(self, batch: int, max_pages: int, device):
         self.batch = batch
@@ -37,6 +37,8 @@ class _Generation:
         self.seen_tokens = 0                 # cache.py:86-87
         self.first_pos = 0                   # absolute position of the generation's first token (cos/sin history)
         self.evictions = 0
+        self.cos_hist = None                 # update(): cos/sin rows of the generation's first `window` positions
+        self.sin_hist = None                 # (cache.py:91-101); LlamaBlock.forward takes them from its rotary table
         self.pages: List[List[int]] = [[] for _ in range(batch)]
         self.max_pages = max_pages
         self.block_table = torch.zeros(batch, max_pages, dtype=torch.int32, device=device)
@@ -197,8 +199,26 @@ class PartialLlamaSinkCache:
         B, KV, n, hd = key_states.shape
         if self._k is None:
             raise RuntimeError("cache is not bound to a span yet (call bind(n_layers, n_kv_heads, head_dim, device))")
-        if self.needs_eviction(gid, n):
-            raise NotImplementedError("the tensor-level update() does not evict; use LlamaBlock.forward or evict()")
+        sin, cos = cache_kwargs.get("sin"), cache_kwargs.get("cos")
+        n_layers = self._shape[0]
+        g = self._gens.get(gid)
+        if layer_idx == 0:
+            if cos is not None and sin is not None:          # cache.py:91-101: history until `window` rows
+                g0 = self.open(gid, B, n)
+                c2, s2 = (cos, sin) if cos.dim() == 2 else (cos[0], sin[0])
+                c2, s2 = c2.to(self._k.device, torch.float32), s2.to(self._k.device, torch.float32)
+                if cos.dim() == 2 or g0.cos_hist is None:
+                    g0.cos_hist, g0.sin_hist = c2.contiguous(), s2.contiguous()
+                elif g0.cos_hist.shape[0] < self.window_length:
+                    g0.cos_hist = torch.cat([g0.cos_hist, c2], dim=0)
+                    g0.sin_hist = torch.cat([g0.sin_hist, s2], dim=0)
+            if self.needs_eviction(gid, n):                  # cache.py:111-133, all layers of the span in one launch
+                g = self._gens[gid]
+                W = self.window_length
+                if g.cos_hist is None or g.cos_hist.shape[0] < W:
+                    raise ValueError("eviction needs the cos/sin history of the first `window_length` positions: pass "
+                                     "cos and sin in cache_kwargs on every update of layer 0 (cache.py:91-101)")
+                self.evict(gid, n, g.cos_hist[:W].contiguous(), g.sin_hist[:W].contiguous())
         g = self.reserve(gid, B, (self._gens[gid].length if gid in self._gens else 0) + n)
         pt = self.page_tokens
         pos = torch.arange(g.length, g.length + n, device=self._k.device)
@@ -212,7 +232,7 @@ class PartialLlamaSinkCache:
         pg, sl = table[:, allpos // pt], (allpos % pt)[None, :].expand(B, total)
         k_all = self._k[layer_idx][pg, :, sl].transpose(1, 2)
         v_all = self._v[layer_idx][pg, :, sl].transpose(1, 2)
-        if layer_idx == self._shape[0] - 1:
+        if layer_idx == n_layers - 1:
             self.advance(gid, n)
         return k_all, v_all
 

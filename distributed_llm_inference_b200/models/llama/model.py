@@ -207,17 +207,32 @@ class LlamaBlock(nn.Module):
         return {name: (float(ms[i]), int(cnt[i])) for i, name in enumerate(ffi.PROF_CLASSES)}
 
     # ------------------------------------------------------------------ forward
-    def _causal_flag(self, attention_mask, q_len: int, past: int) -> int:
-        """model.py:78-144 reduced to one bit for the cases without padding."""
+    def _mask_plan(self, attention_mask, q_len: int, past: int, batch: int, device):
+        """model.py:78-144 reduced to ``(causal, key_valid)``: one bit plus, for a 2-D mask that really contains zeros, a
+        ``[B, past + q_len]`` uint8 validity map of the keys (model.py:128-135).  An all-ones mask is the same as none."""
         impl = getattr(self.config, "_attn_implementation", None) or "sdpa"
+        key_valid = None
         if attention_mask is not None:
-            if attention_mask.dim() != 2 or not bool(torch.all(attention_mask == 1)):
-                raise NotImplementedError("padding / custom 4-D attention masks are not supported by the B200 span")
+            if attention_mask.dim() != 2:
+                raise NotImplementedError("custom 4-D attention masks are not supported by the B200 span")
+            if not bool(torch.all(attention_mask == 1)):            # one host read per call that passes a mask
+                if impl == "flash_attention_2":
+                    raise NotImplementedError("flash_attention_2 with a padding mask: the reference indexes the 2-D mask with "
+                                              "four indices and raises (model.py:86-89 -> modules.py:92-94)")
+                if attention_mask.shape[0] != batch or attention_mask.shape[1] < past + q_len:
+                    raise ValueError(f"attention_mask must be [{batch}, >= {past + q_len}], got {tuple(attention_mask.shape)}")
+                key_valid = (attention_mask[:, :past + q_len] != 0).to(device=device, dtype=torch.uint8).contiguous()
         if impl == "flash_attention_2":
-            return 0                                   # model.py:86-89: mask None -> modules.py:92-94 adds nothing
-        if impl == "sdpa" and (q_len == 1 or past == 0):
-            return 0                                   # model.py:94-101 (_ignore_causal_mask_sdpa) -> None (SURVEY D5)
-        return 1                                       # model.py:103-127
+            return 0, None                             # model.py:86-89: mask None -> modules.py:92-94 adds nothing
+        if impl == "sdpa" and key_valid is None and (q_len == 1 or past == 0):
+            return 0, None                             # model.py:94-101 (_ignore_causal_mask_sdpa) -> None (SURVEY D5)
+        return 1, key_valid                            # model.py:103-135
+
+    def _causal_flag(self, attention_mask, q_len: int, past: int) -> int:
+        impl = getattr(self.config, "_attn_implementation", None) or "sdpa"
+        if impl == "flash_attention_2" or (impl == "sdpa" and attention_mask is None and (q_len == 1 or past == 0)):
+            return 0
+        return 1
 
     @torch.no_grad()
     def forward(
@@ -270,8 +285,6 @@ class LlamaBlock(nn.Module):
         if position_ids.dim() != 2 or position_ids.shape[0] != 1 or position_ids.shape[1] != L:
             raise ValueError("position_ids must be [1, q_len]: the reference's apply_rotary_pos_emb broadcasts one "
                              "position vector over the batch (modules.py:17-20)")
-        causal = self._causal_flag(attention_mask, L, past)
-
         # positions of a generation are contiguous (the reference's sink cache assumes the same for its cos/sin history,
         # cache.py:91-101), so the host knows an upper bound without reading the device tensor: the table is grown to
         # cover it and the gather index is clamped, so an out-of-range id can never fault on the device
@@ -286,12 +299,7 @@ class LlamaBlock(nn.Module):
         idx = position_ids[0].to(device).clamp(0, table.shape[1] - 1)
         cs = torch.index_select(table, 1, idx)                                      # [2, L, hd] fp32 (model.py:55)
 
-        if gen is None:
-            pass
-        elif cache.needs_eviction(gid, L):              # cache.py:107-133: the window is full
-            if L != 1:
-                raise NotImplementedError("a multi-token chunk that overflows window_length is not supported by the "
-                                          "B200 span (the reference's mask becomes position-dependent there)")
+        if gen is not None and cache.needs_eviction(gid, L):   # cache.py:107-133: the window is full
             p0, W = gen.first_pos, cache.window_length
             table = self._rope_table(device, p0 + W)
             cache.evict(gid, L, table[0, p0:p0 + W], table[1, p0:p0 + W])
@@ -300,6 +308,14 @@ class LlamaBlock(nn.Module):
         if first_call:
             gen.first_pos = first_pos
         max_ctx = past + L
+        causal, key_valid = self._mask_plan(attention_mask, L, past, B, device)
+        # The reference's causal rule compares a query's ABSOLUTE cache_position with a key's SLOT in the cache
+        # (model.py:110).  The two coincide -- and the kernels' causal flag applies -- as long as the generation started at
+        # position 0 and nothing was evicted; otherwise (a chunk that crosses the sink window, cache.py:111-133 with
+        # n > 1, or a generation that starts at a later position) the rule becomes a per-query key limit.
+        key_limit = None
+        if causal and L > 1 and first_pos + seen != past:
+            key_limit = (cache_position.to(device) + 1).clamp(max=max_ctx).to(torch.int32).contiguous()
         x = hidden_states.contiguous()
         out = torch.empty_like(x)
         all_h = torch.empty(len(self.layers) + 1, B, L, h, dtype=x.dtype, device=device) if output_hidden_states else None
@@ -307,9 +323,18 @@ class LlamaBlock(nn.Module):
         with torch.cuda.device(device):                  # kernels launch on the tensors' device, whatever is current
             ws = self._workspace(B * L, B, max_ctx, device)
             try:
-                ffi.check(ffi.lib.dli_span_forward(
-                    self._span, C.byref(kv), B, L, causal, x.data_ptr(), out.data_ptr(), cs[0].data_ptr(), cs[1].data_ptr(),
-                    all_h.data_ptr() if all_h is not None else None, ws.data_ptr(), ws.numel(), ffi.current_stream(device)))
+                if key_valid is not None or key_limit is not None:
+                    am = ffi.AttnMask(None if key_limit is None else key_limit.data_ptr(),
+                                      None if key_valid is None else key_valid.data_ptr(),
+                                      0 if key_valid is None else key_valid.shape[1])
+                    ffi.check(ffi.lib.dli_span_forward_masked(
+                        self._span, C.byref(kv), B, L, causal, C.byref(am), x.data_ptr(), out.data_ptr(), cs[0].data_ptr(),
+                        cs[1].data_ptr(), all_h.data_ptr() if all_h is not None else None, ws.data_ptr(), ws.numel(),
+                        ffi.current_stream(device)))
+                else:
+                    ffi.check(ffi.lib.dli_span_forward(
+                        self._span, C.byref(kv), B, L, causal, x.data_ptr(), out.data_ptr(), cs[0].data_ptr(), cs[1].data_ptr(),
+                        all_h.data_ptr() if all_h is not None else None, ws.data_ptr(), ws.numel(), ffi.current_stream(device)))
             except ffi.DliError:
                 self._ws = None                          # a chain that stopped half-way leaves partial sums behind: the
                 raise                                    # next call gets a freshly zeroed workspace (include/dli_b200.h)

@@ -152,6 +152,30 @@ int dli_prefill_attention(const void* q_bf16, void* out_bf16, const dli_kv_desc*
                           int batch, int q_len, int n_heads, int n_kv_heads, int head_dim, int causal,
                           dli_stream_t stream);
 
+/* Masks beyond the causal flag (LlamaBlock._update_causal_mask, model.py:103-135):
+ *   key_limit  device int32 [q_len] or NULL: query l sees cache slots j < key_limit[l].  Replaces the causal rule; needed
+ *              when a multi-token chunk crosses the attention-sink window, where the reference compares the ABSOLUTE
+ *              cache_position of a query with the SLOT index of a key in the evicted cache (model.py:110 after
+ *              cache.py:111-133), i.e. key_limit[l] = min(window, cache_position[l] + 1).
+ *   key_valid  device uint8 [batch, key_stride] or NULL: 0 marks a padded key (attention_mask == 0, model.py:128-135),
+ *              visible to no query of that sequence; key_stride >= kv->max_ctx.
+ * Hidden scores take a large finite negative value like the reference's additive finfo.min, so a prefill row with no
+ * visible key (a left-padding query) is the uniform average of V over the context, as in the reference.  At decode a
+ * hidden key has probability 0 (the step's own key is always valid).  These calls take the generic kernels (mma.sync
+ * prefill, register-staged decode): padded batches and window-crossing chunks are the rare path. */
+typedef struct dli_attn_mask {
+  const int32_t* key_limit;
+  const uint8_t* key_valid;
+  int32_t key_stride;
+} dli_attn_mask;
+
+int dli_prefill_attention_masked(const void* q_bf16, void* out_bf16, const dli_kv_desc* kv, int layer, int batch,
+                                 int q_len, int n_heads, int n_kv_heads, int head_dim, int causal,
+                                 const dli_attn_mask* mask, dli_stream_t stream);
+int dli_decode_attention_masked(const void* q_bf16, void* out_bf16, const dli_kv_desc* kv, int layer, int batch,
+                                int n_heads, int n_kv_heads, int head_dim, const dli_attn_mask* mask, float* scratch,
+                                size_t scratch_bytes, dli_stream_t stream);
+
 /* Attention-sink eviction for every layer of a span, in place on the pages (call BEFORE the forward that appends
  * the n_new tokens, when cur_len + n_new >= window): the cache becomes [first `sinks` tokens | last
  * (window - sinks - n_new) tokens with keys re-rotated back by n_new positions]; afterwards the caller sets
@@ -215,6 +239,13 @@ size_t dli_span_workspace_bytes(const dli_span* span, int max_tokens, int max_ba
 int dli_span_forward(dli_span* span, const dli_kv_desc* kv, int batch, int q_len, int causal,
                      const void* hidden_in, void* hidden_out, const float* cos, const float* sin,
                      void* all_hidden, void* workspace, size_t workspace_bytes, dli_stream_t stream);
+
+/* dli_span_forward with a mask beyond the causal flag (see dli_attn_mask): padded batches (attention_mask with zeros,
+ * model.py:128-135) and multi-token chunks that cross the sink window (cache.py:107-133 with n > 1). */
+int dli_span_forward_masked(dli_span* span, const dli_kv_desc* kv, int batch, int q_len, int causal,
+                            const dli_attn_mask* mask, const void* hidden_in, void* hidden_out, const float* cos,
+                            const float* sin, void* all_hidden, void* workspace, size_t workspace_bytes,
+                            dli_stream_t stream);
 
 /* One decode step (q_len == 1) whose bookkeeping lives on the device, for replay in a CUDA graph: the same kernels
  * as dli_span_forward(..., q_len = 1, ...), but

@@ -24,6 +24,9 @@ class SpanCase:
     rope: str
     norm_jitter: float = 0.1
     first_layer: int = 0          # global index of the first layer (weights seed 1234 + idx)
+    chunks: Tuple[int, ...] = ()  # if given: after the prefill, chunks of these many tokens instead of n_decode single ones
+    pad: Tuple[int, ...] = ()     # if given: per sequence, how many prompt positions are padding (attention_mask == 0)
+    pad_side: str = "left"
 
 
 SPAN_CASES: Tuple[SpanCase, ...] = (
@@ -39,6 +42,16 @@ SPAN_CASES: Tuple[SpanCase, ...] = (
     SpanCase("gqa_evict_literal", "test_gqa", 3, 2, 9, 11, 12, 2, "eager", "literal"),
     # first chunk longer than the window (D14) then trimmed at the next update
     SpanCase("gqa_overlong_first", "test_gqa", 2, 1, 8, 4, 6, 2, "eager", "float"),
+    # multi-token chunks that cross the window (cache.py:107-133 with n > 1; the causal rule of model.py:110 then
+    # compares absolute positions with slots of the evicted cache)
+    SpanCase("gqa_evict_chunk_float", "test_gqa", 3, 2, 9, 0, 12, 2, "eager", "float", chunks=(4, 3, 1, 5, 2)),
+    SpanCase("gqa_evict_chunk_literal", "test_gqa", 3, 2, 9, 0, 12, 2, "eager", "literal", chunks=(2, 6, 1, 3)),
+    SpanCase("hd128_evict_chunk_sdpa", "test_hd128", 2, 1, 20, 0, 24, 4, "sdpa", "float", chunks=(7, 1, 9, 2)),
+    # 2-D padding masks (model.py:128-135): left padding (fully masked pad rows come out as uniform averages), right
+    # padding, and a long left-padded prompt that takes the token-major GEMM path
+    SpanCase("gqa_padded_left", "test_gqa", 3, 3, 9, 6, 4096, 4, "eager", "float", pad=(0, 3, 5)),
+    SpanCase("gqa_padded_right_sdpa", "test_gqa", 2, 2, 12, 4, 4096, 4, "sdpa", "float", pad=(0, 4), pad_side="right"),
+    SpanCase("hd128_padded_left_long", "test_hd128", 2, 2, 150, 3, 4096, 4, "eager", "float", pad=(0, 37), first_layer=1),
 )
 
 

@@ -34,9 +34,10 @@ def ref_make_span(shp, weights, attn_implementation, rope):
     blk = ref_shim.make_block(cfg, len(weights), rope=rope)
     ref_shim.load_layer_weights(blk, weights)
 
-    def span(generation_id, hidden, past_key_value=None, cache_position=None, output_hidden_states=False):
+    def span(generation_id, hidden, past_key_value=None, cache_position=None, output_hidden_states=False,
+             attention_mask=None):
         return ref_shim.block_forward(blk, generation_id, hidden, past_key_value, cache_position,
-                                      output_hidden_states)
+                                      output_hidden_states, attention_mask=attention_mask)
 
     return span
 
@@ -46,7 +47,10 @@ def main():
     torch.set_grad_enabled(False)
     meta = dict(torch=torch.__version__, reference="Dylan102938/distributed-llm-inference @ /root/reference",
                 dtype="float32")
+    names = set(sys.argv[2:])                                # optional: only these span cases
     for case in (SPAN_CASES if only in ("all", "span") else ()):
+        if names and case.name not in names:
+            continue
         out = run_span_case(case, ref_make_span, ref_shim.make_cache)
         path = os.path.join(HERE, f"span_{case.name}.npz")
         np.savez_compressed(path, prefill=out["prefill"], decode=out["decode"],

@@ -36,6 +36,20 @@ def span_case_weights(case: SpanCase, dtype, device="cpu"):
     return [{k: v.to(device) for k, v in w.items()} for w in ws]
 
 
+def case_mask(case: SpanCase, length: int, device="cpu"):
+    """2-D attention mask ``[B, length]`` of the case (1 = token, 0 = padding inside the prompt), or None."""
+    if not case.pad:
+        return None
+    m = torch.ones(case.batch, length, dtype=torch.long)
+    for b, n in enumerate(case.pad):
+        if n:
+            if case.pad_side == "left":
+                m[b, :n] = 0
+            else:
+                m[b, case.prefill - n:case.prefill] = 0
+    return m.to(device)
+
+
 def run_span_case(case: SpanCase, make_span: Callable, make_cache: Callable, dtype=torch.float32,
                   device="cpu") -> Dict[str, np.ndarray]:
     shp, x0, steps = span_case_inputs(case, dtype, device)
@@ -43,13 +57,27 @@ def run_span_case(case: SpanCase, make_span: Callable, make_cache: Callable, dty
     span = make_span(shp, weights, case.attn_implementation, case.rope)
     cache = make_cache(case.window, case.sinks)
     out: Dict[str, np.ndarray] = {}
+    mk = {} if not case.pad else None          # keyword only when the case has a mask (older factories take none)
     with torch.no_grad():
-        y = span("g0", x0, past_key_value=cache, cache_position=None)[0]
+        kw = {} if mk is not None else {"attention_mask": case_mask(case, case.prefill, device)}
+        y = span("g0", x0, past_key_value=cache, cache_position=None, **kw)[0]
         out["prefill"] = y.float().cpu().numpy()
         dec: List[np.ndarray] = []
+        if case.chunks:
+            pos = case.prefill
+            for i, n in enumerate(case.chunks):
+                xt = syn.make_hidden(shp, case.batch, n, seed=1000 + i, dtype=dtype, device=device)
+                cp = torch.arange(pos, pos + n, device=x0.device)
+                kw = {} if mk is not None else {"attention_mask": case_mask(case, pos + n, device)}
+                y = span("g0", xt, past_key_value=cache, cache_position=cp, **kw)[0]
+                dec.append(y.float().cpu().numpy())
+                pos += n
+            out["decode"] = np.concatenate(dec, axis=1)          # [B, sum(chunks), h]
+            return out
         for i, xt in enumerate(steps):
             cp = torch.tensor([case.prefill + i], device=x0.device)
-            y = span("g0", xt, past_key_value=cache, cache_position=cp)[0]
+            kw = {} if mk is not None else {"attention_mask": case_mask(case, case.prefill + i + 1, device)}
+            y = span("g0", xt, past_key_value=cache, cache_position=cp, **kw)[0]
             dec.append(y.float().cpu().numpy())
         out["decode"] = np.stack(dec, axis=0) if dec else np.zeros((0,), np.float32)
     return out

@@ -53,13 +53,40 @@ def test_span_matches_reference_fixture(case):
     _check(case.name + "/decode", out["decode"], gold["decode"])
 
 
-def test_multi_token_chunk_over_the_window_is_refused_loudly():
+def test_chunk_that_leaves_no_room_in_the_window_is_refused_loudly():
+    """A chunk of n >= window - sinks tokens would keep nothing of the past (the reference's slice arithmetic then
+    keeps the wrong end of the cache, cache.py:113): refused, not guessed.  Smaller chunks that cross the window are
+    the ``*_evict_chunk_*`` fixtures above."""
     shp = syn.SHAPES["test_gqa"]
     blk = gpu_make_span(shp, syn.make_span_weights(shp, [0]), "eager", "float")
     cache = gpu_make_cache(12, 2)
     blk("g", syn.make_hidden(shp, 1, 9).to(DEV), past_key_value=cache)
     with pytest.raises(NotImplementedError):
-        blk("g", syn.make_hidden(shp, 1, 4).to(DEV), past_key_value=cache, cache_position=torch.arange(9, 13, device=DEV))
+        blk("g", syn.make_hidden(shp, 1, 10).to(DEV), past_key_value=cache, cache_position=torch.arange(9, 19, device=DEV))
+
+
+def test_tensor_level_cache_update_evicts_like_the_oracle():
+    """PartialLlamaSinkCache.update (the per-layer tensor API of cache.py:64-135) with eviction: single tokens and a
+    multi-token chunk against the oracle's cache on the same rotated keys, cos/sin history taken from cache_kwargs."""
+    torch.manual_seed(0)
+    B, KV, hd, W, s = 2, 2, 64, 12, 2
+    gc, oc = gpu_make_cache(W, s), so.SinkCacheOracle(W, s)
+    gc.bind(2, KV, hd, DEV)
+    pos = 0
+    for n in (7, 1, 3, 1, 4, 1, 1):
+        pid = torch.arange(pos, pos + n)[None]
+        cos, sin = so.rope_tables(pid, hd, 10000.0, "float", torch.float32)
+        for layer in range(2):
+            k = torch.randn(B, KV, n, hd).to(torch.bfloat16)
+            v = torch.randn(B, KV, n, hd).to(torch.bfloat16)
+            kw = {"generation_id": "g", "cos": cos, "sin": sin}
+            rk, rv = oc.update(k.float(), v.float(), layer, dict(kw))
+            gk, gv = gc.update(k.to(DEV), v.to(DEV), layer, {"generation_id": "g", "cos": cos.to(DEV), "sin": sin.to(DEV)})
+            assert gk.shape == rk.shape and gv.shape == rv.shape, (n, layer, gk.shape, rk.shape)
+            torch.testing.assert_close(gk.float().cpu(), rk, rtol=2e-2, atol=2e-2)     # kept keys are re-rotated and
+            torch.testing.assert_close(gv.float().cpu(), rv, rtol=0, atol=0)           # re-rounded to bf16 per eviction
+        pos += n
+        assert gc.get_seq_length(0, "g") == oc.get_seq_length(0, "g")
 
 
 def test_span_matches_oracle_live_two_generations_and_hidden_states():
