@@ -115,7 +115,7 @@ def test_paged_cache_limits_are_loud():
     assert c.needs_eviction("g", 2) and not c.needs_eviction("g", 1)    # cache.py:107: append while n + len < window
     with pytest.raises(ValueError, match="evict first"):
         c.reserve("g", 1, 11)
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(ValueError, match="cos/sin history"):      # update() evicts, and eviction re-rotates keys
         c.update(torch.zeros(1, 1, 2, 8), torch.zeros(1, 1, 2, 8), 0, {"generation_id": "g"})
     c2 = PartialLlamaSinkCache(4096, 2, page_tokens=4, capacity_tokens=8)
     c2.bind(1, 1, 8, "cpu", dtype=torch.float32)
