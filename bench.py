@@ -389,7 +389,7 @@ def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layer
 
     blk = build_span(shape, layer_ids, dev, max_positions=max(8192, total_ctx + 64))
     cache = PartialLlamaSinkCache(1 << 20, 4, page_tokens=page_tokens,
-                                  capacity_tokens=n_mb * batch * (total_ctx + 16) + batch * 64 +
+                                  capacity_tokens=n_mb * batch * (total_ctx + 16) + batch * 192 +
                                   (n_mb if world > 1 else 1) * batch * (prompt + 16) + (prompt + 128))
     client_w = None
     if want_e2e:   # client tensors of the token ring (embedding on stage 0, final norm + head on the last stage)
@@ -495,16 +495,18 @@ def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layer
     round_graph = False
     if world > 1 and stage.handoff == "peer_store" and not args.no_round_graph:
         round_graph = stage.capture_round(gids)     # steady-state rounds: one graph launch per round
-    # every stage's step timed ALONE (no hand-off, nothing to wait for), while the other GPUs idle: a pipeline with as
-    # many micro-batches as stages runs at the pace of its slowest stage, so this is the bound the round time is read against
+    # every stage's step timed WITHOUT hand-off (nothing to wait for), all stages at the same time, each on its own GPU:
+    # a pipeline with as many micro-batches as stages runs at the pace of its slowest stage, so this is the bound the
+    # round time is read against.  The ~0.3 s of back-to-back steps also bring every GPU to its steady clocks (the GPUs
+    # idle through the set-up; a few warm-up rounds of a few ms each do not do that).
     solo = None
-    if world > 1 and not args.no_graph:
+    if not args.no_graph:
         ctx.barrier()
         xs_solo = syn.make_hidden(shape, batch, prompt, seed=77, device=dev)
         blk("solo", xs_solo, past_key_value=cache)
         del xs_solo
-        gs = blk.graphed_decode("solo", cache, prompt + 24)
-        for _ in range(4):
+        gs = blk.graphed_decode("solo", cache, prompt + 120)
+        for _ in range(100):
             gs.step()
         torch.cuda.synchronize()
         e0.record()
@@ -514,7 +516,10 @@ def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layer
         torch.cuda.synchronize()
         mine = torch.tensor([e0.elapsed_time(e1) / 12], device=dev)
         allms = [torch.zeros_like(mine) for _ in range(world)]
-        dist.all_gather(allms, mine)
+        if world > 1:
+            dist.all_gather(allms, mine)
+        else:
+            allms = [mine]
         solo = [round(t.item(), 4) for t in allms]
         del gs
         cache.close("solo")
@@ -559,12 +564,12 @@ def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layer
         "prefill_first_call_tokens_per_sec": round(n_mb * batch * prompt / (prefill_ms * 1e-3), 1),
         "prefill": prefill, "chunk": chunk,
     }
-    if solo is not None:
+    if solo is not None and world > 1:
         res["stage_step_alone_ms"] = solo
         res["pipeline_vs_slowest_stage"] = round(max(solo) / (ms_per_step / n_mb), 4)
-        res["stage_step_alone_note"] = ("each stage's decode step replayed alone (same layers, batch and context, no hand-off) "
-                                        "while the other GPUs idle, per rank; pipeline_vs_slowest_stage = max of these / "
-                                        "the pipeline's time per stage-step")
+        res["stage_step_alone_note"] = ("each stage's decode step replayed without hand-off (same layers, batch and context), all "
+                                        "ranks at the same time, per rank; pipeline_vs_slowest_stage = max of these / the "
+                                        "pipeline's time per stage-step")
     if world > 1:   # whole-pipeline prefill: all stages' FLOPs over the max-over-ranks time, against N x the peak
         fl = n_mb * prefill_flops(shape, n_total, batch, prompt)
         n_chunks = -(-prompt // chunk)
