@@ -315,16 +315,16 @@ __device__ __forceinline__ void flag_wait(const uint32_t* flag, uint32_t need, u
       return;
     }
     __nanosleep(ns);
-    if (ns < 256) ns *= 2;
+    if (ns < 128) ns *= 2;
   }
 }
 // Last kernel of a stage step, called by ALL threads of every CTA after their output stores: fence them system-wide,
 // take a ticket, and let the last CTA to arrive bump the step counter and release the consumer's flag.
 __device__ __forceinline__ void step_exit(const ExitArgs& xa) {
   if (!xa.state) return;
-  __threadfence_system();
-  __syncthreads();
+  __syncthreads();  // every thread's output stores are ordered before thread 0's fence (the pattern of a grid-wide sync)
   if (threadIdx.x == 0) {
+    __threadfence_system();  // cumulative: covers what the CTA's other threads stored before the barrier
     const unsigned total = gridDim.x * gridDim.y * gridDim.z;
     const unsigned ticket = atomicAdd(xa.state + 1, 1u);
     if (ticket == total - 1) {

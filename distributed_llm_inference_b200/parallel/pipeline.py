@@ -62,8 +62,10 @@ class PipelineStage:
         self.handoff = "nccl" if world > 1 else "local"
         self.handoff_error = None
         self.round_error = None
-        self.chain_steps = False    # True: chain the steps of different micro-batches with programmatic dependent launch
-                                    # (measured on 2 GPUs: no gain over the stream barrier in front of each step)
+        # chain the steps of different micro-batches with programmatic dependent launch (the next step's entry kernel and
+        # its first GEMM's weight ring are resident while the current step drains) instead of a stream barrier in front of
+        # every step: 8 stages x 4 layers of the 7B shape, 3.311 -> 3.282 ms per round; no difference at 2 stages
+        self.chain_steps = True
         self.trace = None           # set to [] to collect (start, end) CUDA-event pairs per micro-batch (per-step graphs)
 
     # back-compat views used by bench.py / tests: the hidden ring's graphs

@@ -4,8 +4,7 @@ Reference: distributed_llm_inference/server/worker.py:9-23 is a stub (``__init__
 ``run`` is ``pass``); its signature ``(model, block_index_start, block_index_end, ...)`` and the comment
 ``self.blocks[...] = load_block()`` say what it was meant to do.  This version does exactly that: load the span
 ``[block_index_start, block_index_end)`` from a local checkpoint directory, put it on the GPU, give it a paged
-sink cache and wrap it in the backend whose pool a server loop calls.  ``Server.run`` (server/server.py:4-24) is a
-comment-only loop (health check / rebalance / restart); it has no behaviour to mirror and is not provided.
+sink cache and wrap it in the backend whose pool the server loop (server/server.py) calls.
 """
 from __future__ import annotations
 
@@ -41,6 +40,6 @@ class InferenceWorker:
         return self.backend.forward(hidden_states, generation_id=generation_id, cache_position=cache_position)[0]
 
     def run(self):
-        """A server loop would pull tasks from ``self.backend.get_pools()``; transport (hivemind in the reference's
-        imports) is outside this repository."""
+        """-> the backend's inference pool; ``Server.run`` (server/server.py) takes tasks from its queue and submits them
+        here one at a time.  Transport between machines (hivemind in the reference's imports) is outside this repository."""
         return self.backend.get_pools()

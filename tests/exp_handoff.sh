@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533"
 COMMON="bench.py --gpus $N --steps 32 --warmup 6 --cpu-budget 0 --no-parity --no-configs --no-e2e"
 i=0
-for extra in "--micro-batches 1" "" "--chain" "--no-round-graph" "--chain --no-round-graph" "--nccl-handoff"; do
+for extra in "--micro-batches 1" "" "--no-chain" "--no-round-graph" "--no-chain --no-round-graph" "--nccl-handoff"; do
   i=$((i+1))
   timeout 300 $TR $COMMON $extra > gpurun_out/handoff_$i.json 2> gpurun_out/handoff_$i.err || tail -5 gpurun_out/handoff_$i.err
   python - <<PY

@@ -270,3 +270,54 @@ def test_two_spans_on_two_devices_in_one_process():
         h = spans[1]("g", h.to("cuda:1"), past_key_value=caches[1], cache_position=cp.to("cuda:1"))[0]
         _check(f"two-device step {step}", h.float().cpu().numpy(), ref.numpy())
         pos += L
+
+
+def test_server_hosts_a_loaded_span(tmp_path):
+    """``Server.run`` loads layers [1, 3) of a local checkpoint into an ``InferenceWorker`` on the GPU and
+    serves two interleaved generations (session id out of band of the tensors); outputs against the oracle."""
+    import threading
+
+    from distributed_llm_inference_b200.server.server import Server
+
+    shp = syn.SHAPES["test_hd128"]
+    W = syn.make_span_weights(shp, [0, 1, 2], norm_jitter=0.1)
+    syn.write_checkpoint(str(tmp_path), shp, dict(zip(range(3), W)))
+    srv = Server(str(tmp_path), 1, 3, rope="float", attn_implementation="eager", capacity_tokens=4096)
+    t = threading.Thread(target=srv.run, daemon=True)
+    t.start()
+    assert srv.ready.wait(120)
+    assert [b["block_index"] for b in srv.worker.blocks] == [1, 2]
+    osp = oracle_make_span(shp, W[1:], "eager", "float")
+    oc = so.SinkCacheOracle(4096, 4)
+    lens = {"a": 0, "b": 0}
+    for step, (gid, B, L) in enumerate([("a", 2, 40), ("b", 1, 7), ("a", 2, 1), ("b", 1, 1), ("a", 2, 1)]):
+        x = syn.make_hidden(shp, B, L, seed=90 + step)
+        cp = torch.arange(lens[gid], lens[gid] + L)
+        ref = osp.forward(gid, x.float(), past_key_value=oc, cache_position=cp)[0]
+        got = srv.submit(gid, x.to(DEV), cp.to(DEV)).result(60)
+        _check(f"served step {step}", got.float().cpu().numpy(), ref.numpy())
+        lens[gid] += L
+    with pytest.raises(TypeError):
+        srv.submit("a", torch.zeros(1, 1, shp.hidden_size, device=DEV)).result(60)      # fp32: the caller's error
+    assert srv.restarts == 0
+    srv.shutdown()
+    t.join(30)
+    assert not t.is_alive()
+
+
+def test_make_inference_graphed_callable_replays():
+    """utils/cuda.py (reference utils/cuda.py:6-77): forward-only graph capture of a callable; replay with new inputs
+    copied into the static buffers gives what the callable gives eagerly."""
+    from distributed_llm_inference_b200.utils.cuda import make_inference_graphed_callable
+
+    w = torch.randn(64, 64, device=DEV)
+
+    def f(x, y):
+        return torch.relu(x @ w) + y
+
+    a, b = torch.randn(8, 64, device=DEV), torch.randn(8, 64, device=DEV)
+    g = make_inference_graphed_callable(f, (a, b))
+    for seed in range(3):
+        torch.manual_seed(seed)
+        x, y = torch.randn(8, 64, device=DEV), torch.randn(8, 64, device=DEV)
+        torch.testing.assert_close(g(x, y), f(x, y))
