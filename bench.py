@@ -121,14 +121,19 @@ class ClockSampler(threading.Thread):
                 "samples": len(s)}
 
 
-def decode_step_bytes(shape: syn.LlamaShape, n_layers: int, batch: int, ctx: int, head: bool = False) -> dict:
+def decode_step_bytes(shape: syn.LlamaShape, n_layers: int, batch: int, ctx: int, head: bool = False, w8: bool = False) -> dict:
     """ALGORITHMIC bytes of one decode stage-step: weights read once, K and V read once,
     K/V appended, span input + output; with ``head`` also the [vocab, h] head read once and the logits written and read."""
     h, i = shape.hidden_size, shape.intermediate_size
     H, KV, hd = shape.num_attention_heads, shape.num_key_value_heads, shape.head_dim
     per_gemm = {"gemm_qkv": 2 * h * (H + 2 * KV) * hd, "gemm_o": 2 * H * hd * h, "gemm_gate_up": 2 * 2 * h * i,
                 "gemm_down": 2 * i * h}
-    weights = n_layers * (sum(per_gemm.values()) + 2 * 2 * h)
+    if w8:   # int8 weights + one fp32 scale per output row
+        rows = (H + 2 * KV) * hd + h + 2 * i + h
+        per_gemm = {k: v // 2 for k, v in per_gemm.items()}
+        weights = n_layers * (sum(per_gemm.values()) + 4 * rows + 2 * 2 * h)
+    else:
+        weights = n_layers * (sum(per_gemm.values()) + 2 * 2 * h)
     kv_read = n_layers * batch * ctx * 2 * KV * hd * 2
     kv_write = n_layers * batch * 2 * KV * hd * 2
     io = 2 * batch * h * 2
@@ -369,7 +374,7 @@ def free_cuda():
 
 
 def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layers_total, K: int, W: int,
-                 prefill_chunk=None, full: bool = False, want_e2e: bool = False, page_tokens: int = 16):
+                 prefill_chunk=None, full: bool = False, want_e2e: bool = False, page_tokens: int = 16, w8: bool = False):
     """One decode measurement of ``model`` cut into ``ctx.world`` stages: prefill (timed), warm-up, K timed rounds of
     ``n_mb`` micro-batches x ``batch`` sequences over the hidden-state ring.  ``full``: also the instrumented per-class
     pass, the dominant-kernel roofline, batch-1 latency, warm prefill (one GPU).  ``want_e2e``: the token ring
@@ -388,6 +393,9 @@ def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layer
     hbm_peak, tc_peak, peak_kind = measured_peaks()
 
     blk = build_span(shape, layer_ids, dev, max_positions=max(8192, total_ctx + 64))
+    if w8:
+        blk.quantize_w8()                     # row-wise int8 weights (convert_to_optimized_block(quantize=True))
+        free_cuda()
     cache = PartialLlamaSinkCache(1 << 20, 4, page_tokens=page_tokens,
                                   capacity_tokens=n_mb * batch * (total_ctx + 16) + batch * 192 +
                                   (n_mb if world > 1 else 1) * batch * (prompt + 16) + (prompt + 128))
@@ -547,10 +555,10 @@ def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layer
     tokens_per_step = batch * n_mb
     value = tokens_per_step / (ms_per_step * 1e-3)
     ctx_mid = prompt + W + K // 2
-    sb = decode_step_bytes(shape, len(layer_ids), batch, ctx_mid)
+    sb = decode_step_bytes(shape, len(layer_ids), batch, ctx_mid, w8=w8)
     stage_gbs = sb["total"] / (ms_per_step / n_mb * 1e-3) / 1e9
     res = {
-        "model": shape.name, "layers_total": n_total, "layers_per_stage": len(layer_ids), "batch": batch, "micro_batches": n_mb,
+        "model": shape.name, "weights": "int8 rows + fp32 scales, bf16 activations" if w8 else "bf16", "layers_total": n_total, "layers_per_stage": len(layer_ids), "batch": batch, "micro_batches": n_mb,
         "prompt": prompt, "value": round(value, 1), "ms_per_step": round(ms_per_step, 4),
         "ms_per_stage_step": round(ms_per_step / n_mb, 4), "p50_ms_per_token": round(lat[len(lat) // 2] / n_mb, 4),
         "tokens_per_step": tokens_per_step, "steps": K, "launches": int(launches), "clocks": clocks,
@@ -873,8 +881,16 @@ def run_ours(args):
     if world > 1 and not args.no_parity:
         parity = pipeline_parity(ctx)
     n_mb = args.micro_batches or world   # micro-batches in flight (default: the pipeline depth)
-    main = run_workload(ctx, MODEL, BATCH, PROMPT, n_mb, args.layers, K, W, prefill_chunk=args.prefill_chunk, full=True,
-                        want_e2e=not args.no_e2e, page_tokens=args.page_tokens)
+    main = run_workload(ctx, MODEL, BATCH, PROMPT, n_mb, args.layers, K, W, prefill_chunk=args.prefill_chunk, full=not args.w8,
+                        want_e2e=not args.no_e2e, page_tokens=args.page_tokens, w8=args.w8)
+    w8_rec = None
+    if world == 1 and not args.w8 and not args.no_w8:
+        # the same workload with the weights stored as row-wise int8 (the reference's optimised mode keeps its weights
+        # in that format, utils/model.py:93-123): a second, clearly labelled record -- the headline stays bf16
+        r8 = run_workload(ctx, MODEL, BATCH, PROMPT, n_mb, args.layers, min(K, 32), 3, w8=True)
+        w8_rec = {k: r8[k] for k in ("weights", "value", "ms_per_step", "p50_ms_per_token", "stage_roofline", "launches",
+                                     "prefill_first_call_tokens_per_sec")}
+        w8_rec["vs_bf16"] = round(r8["value"] / main["value"], 3)
     configs = None
     if world > 1 and not args.no_configs and MODEL == "7b" and not args.layers:
         configs = {}
@@ -922,6 +938,7 @@ def run_ours(args):
             "cpu_baseline": cpu, "decode_batch1": main.get("decode_batch1"),
             "stage_step_alone_ms": main.get("stage_step_alone_ms"),
             "pipeline_vs_slowest_stage": main.get("pipeline_vs_slowest_stage"),
+            "decode_int8_weights": w8_rec,
             "pipeline_parity": parity, "configs": configs,
         }
         print(json.dumps(line), flush=True)
@@ -981,6 +998,8 @@ def main():
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the pipeline_parity record")
     ap.add_argument("--no-configs", action="store_true", help="N > 1: skip the BASELINE configs 3-5 records")
     ap.add_argument("--no-e2e", action="store_true", help="skip the token-ring e2e measurement")
+    ap.add_argument("--w8", action="store_true", help="run the main workload with row-wise int8 weights (experiments)")
+    ap.add_argument("--no-w8", action="store_true", help="one GPU: skip the decode_int8_weights record")
     ap.add_argument("--no-chain", action="store_true", help="experiments: a stream barrier in front of every stage step instead "
                                                             "of chaining the micro-batches' steps with programmatic dependent launch")
     args = ap.parse_args()

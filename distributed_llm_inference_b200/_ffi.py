@@ -28,6 +28,8 @@ EXPORTS = (
     "dli_span_profile_read", "dli_decode_attention_static", "dli_kv_evict", "dli_span_decode_step",
     "dli_stage_decode_step", "dli_flag_wait", "dli_lm_head_argmax",
     "dli_span_forward_masked", "dli_prefill_attention_masked", "dli_decode_attention_masked",
+    "dli_quantize_rows_w8", "dli_dequantize_rows_w8", "dli_gemm_w8", "dli_span_bind_weights_w8",
+    "dli_span_dequant_scratch_bytes", "dli_span_set_dequant_scratch",
 )
 
 
@@ -50,6 +52,12 @@ class SpanDesc(C.Structure):
 
 class LayerWeights(C.Structure):
     _fields_ = [("wqkv", C.c_void_p), ("wo", C.c_void_p), ("wgu", C.c_void_p), ("wdown", C.c_void_p),
+                ("g_in", C.c_void_p), ("g_post", C.c_void_p)]
+
+
+class LayerWeightsW8(C.Structure):
+    _fields_ = [("wqkv", C.c_void_p), ("sqkv", C.c_void_p), ("wo", C.c_void_p), ("so", C.c_void_p),
+                ("wgu", C.c_void_p), ("sgu", C.c_void_p), ("wdown", C.c_void_p), ("sdown", C.c_void_p),
                 ("g_in", C.c_void_p), ("g_post", C.c_void_p)]
 
 
@@ -97,6 +105,12 @@ def _load() -> C.CDLL:
         "dli_span_decode_step": (C.c_int, [vp, C.POINTER(KvDesc), i32, vp, vp, vp, vp, vp, i32, vp, sz, vp]),
         "dli_stage_decode_step": (C.c_int, [vp, C.POINTER(KvDesc), i32, C.POINTER(StageIo), vp, vp, vp, i32, vp, sz, vp]),
         "dli_flag_wait": (C.c_int, [vp, C.c_uint32, vp, i32, vp]),
+        "dli_quantize_rows_w8": (C.c_int, [vp, i64, i64, vp, vp, vp]),
+        "dli_dequantize_rows_w8": (C.c_int, [vp, vp, i64, i64, vp, vp]),
+        "dli_gemm_w8": (C.c_int, [vp, i64, vp, vp, vp, i64, i32, i32, i32, i32, vp]),
+        "dli_span_bind_weights_w8": (C.c_int, [vp, i32, C.POINTER(LayerWeightsW8)]),
+        "dli_span_dequant_scratch_bytes": (sz, [vp]),
+        "dli_span_set_dequant_scratch": (C.c_int, [vp, vp, sz]),
         "dli_span_forward_masked": (C.c_int, [vp, C.POINTER(KvDesc), i32, i32, i32, C.POINTER(AttnMask), vp, vp, vp, vp, vp, vp, sz, vp]),
         "dli_prefill_attention_masked": (C.c_int, [vp, vp, C.POINTER(KvDesc), i32, i32, i32, i32, i32, i32, i32, C.POINTER(AttnMask), vp]),
         "dli_decode_attention_masked": (C.c_int, [vp, vp, C.POINTER(KvDesc), i32, i32, i32, i32, i32, C.POINTER(AttnMask), vp, sz, vp]),

@@ -132,6 +132,14 @@ int launch_gemm_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const CUte
                         long long ldo, int m, int n, int epilogue, cudaStream_t st, const RopeArgs* rope = nullptr);
 int launch_gemm(const void* x, long long ldx, const void* w, void* out, long long ldo, int m, int n, int k,
                 int epilogue, cudaStream_t st);
+// weight-only int8 (gemm_w8.cu): decode GEMM on row-wise quantised weights, (de)quantisation kernels
+int make_tmap_u8(CUtensorMap* map, const void* base, long long rows, long long cols, int box_rows);
+int launch_gemm_w8_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const CUtensorMap& tmap_w, const float* scale, void* out,
+                           long long ldo, int m, int n, int epilogue, cudaStream_t st);
+int launch_gemm_w8(const void* x, long long ldx, const void* q, const float* scale, void* out, long long ldo, int m, int n,
+                   int k, int epilogue, cudaStream_t st);
+int launch_quantize_rows_w8(const void* w_bf16, long long n, long long k, void* q_u8, float* scale, cudaStream_t st);
+int launch_dequantize_rows_w8(const void* q_u8, const float* scale, long long n, long long k, void* w_bf16, cudaStream_t st);
 
 // Decode step whose position lives on the device (dli_span_decode_step): which table row to use, and what the span's
 // last kernel advances afterwards.

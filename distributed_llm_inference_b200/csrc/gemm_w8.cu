@@ -1,0 +1,446 @@
+// Weight-only int8 decode GEMM:  out[m, n] (+)= scale[n] * sum_k x[m, k] * (q[n, k] - 128)      (m <= 128)
+//
+// The reference's only "optimised" mode turns every nn.Linear into bitsandbytes Linear8bitLt with
+// has_fp16_weights=False (utils/model.py:93-123): weights are stored as row-wise absmax int8 (one fp32 scale per output
+// row).  Decode is bound by the bytes of the weights, so storing them in 8 bits halves the step's HBM traffic.  This
+// kernel keeps that weight format (biased uint8 = int8 + 128, scale = absmax / 127) and the 16-bit activations of the
+// bf16 path: the int8 tile that TMA lands in shared memory is widened to bf16 -- exactly, every integer in
+// [-128, 127] is a bf16 -- by the four epilogue warps, which are idle during the main loop, into the 128B-swizzled
+// K-major layout tcgen05.mma reads; the MMA is the bf16 one (fp32 accumulators in TMEM) and the row scale is applied
+// to the accumulator in the epilogue.  There is no activation quantisation and therefore no outlier decomposition.
+//
+// Same shape as the bf16 weight-streaming kernel (gemm_tcgen05.cu, swap-AB: 128 weight rows are the MMA-M operand,
+// the batch is MMA-N; split-K over gridDim.z; TMA producer warp, MMA warp, 4 more warps), with one more hop per stage:
+//   raw_full[s]  TMA (int8 weights + bf16 activations) -> converter warps
+//   full[s]      converter warps (bf16 weights written, fence.proxy.async) -> MMA warp
+//   empty[s]     tcgen05.commit -> TMA producer
+#include "common.cuh"
+#include "tc_ptx.cuh"
+
+#include <algorithm>
+
+namespace dli {
+
+constexpr int W8_THREADS = 192;
+constexpr int W8_RAW_BYTES = BM * BK;      // 128 rows x 64 int8
+constexpr int W8_A_BYTES = BM * BK * 2;    // the same tile as bf16
+constexpr int W8_MAX_STAGES = 6;
+
+struct W8Params {
+  void* out;
+  long long ldo;
+  int m_tokens, n_features;
+  int k_blocks, kb_per_split;
+  int stages;
+  int up_row_offset;   // SILU epilogue: row of q / scale where up_proj starts (= n_features)
+  const float* scale;  // [rows of q]
+};
+
+__device__ __forceinline__ float w8_silu(float x) { return x / (1.0f + __expf(-x)); }
+
+// four biased bytes of `w` -> two bf16x2 words (exact)
+__device__ __forceinline__ void w8_widen4(uint32_t w, uint32_t& lo, uint32_t& hi) {
+  const float f0 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650)) - 8388736.0f;  // 2^23 + 128
+  const float f1 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7651)) - 8388736.0f;
+  const float f2 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7652)) - 8388736.0f;
+  const float f3 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7653)) - 8388736.0f;
+  lo = pack_bf16(f0, f1);
+  hi = pack_bf16(f2, f3);
+}
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(W8_THREADS, 2)
+gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant__ CUtensorMap tma_x, const W8Params p) {
+  constexpr int B_TILE_BYTES = BN * BK * 2;
+  constexpr int STAGE_BYTES = W8_A_BYTES + B_TILE_BYTES + W8_RAW_BYTES;
+  constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
+  constexpr bool SILU = EPI == DLI_EPI_SILU_MUL_BF16;
+
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t bars[3 * W8_MAX_STAGES + 1];
+  __shared__ uint32_t tmem_base_slot;
+
+  const uint32_t tiles = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int stages = p.stages;
+  const uint32_t raw_full0 = smem_u32(&bars[0]), full0 = smem_u32(&bars[W8_MAX_STAGES]),
+                 empty0 = smem_u32(&bars[2 * W8_MAX_STAGES]), tmem_full = smem_u32(&bars[3 * W8_MAX_STAGES]);
+
+  const int kb0 = blockIdx.z * p.kb_per_split;
+  const int kb1 = min(kb0 + p.kb_per_split, p.k_blocks);
+  const int a_row0 = blockIdx.x * (SILU ? BM / 2 : BM);
+  const int b_row0 = blockIdx.y * BN;
+
+  pdl_trigger();
+  if (threadIdx.x == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_w) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_x) : "memory");
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(raw_full0 + 8 * s, 1);
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, 1);
+    }
+    mbar_init(tmem_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)),
+                 "r"((uint32_t)TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_d = tmem_base_slot;
+
+  if (kb1 > kb0) {
+    if (warp == 0) {
+      // ===== TMA producer: int8 weight tiles (before the dependency wait: weights never depend on the predecessor)
+      //       and the activation tiles (after it) =====
+      auto load_weights = [&](int s, int kb) {
+        const uint32_t raw = tiles + s * STAGE_BYTES + W8_A_BYTES + B_TILE_BYTES;
+        if (SILU) {  // 64 gate rows + 64 up rows of the same 64 features
+          tma_load_2d(raw, &tma_w, raw_full0 + 8 * s, kb * BK, a_row0);
+          tma_load_2d(raw + W8_RAW_BYTES / 2, &tma_w, raw_full0 + 8 * s, kb * BK, p.up_row_offset + a_row0);
+        } else {
+          tma_load_2d(raw, &tma_w, raw_full0 + 8 * s, kb * BK, a_row0);
+        }
+      };
+      auto load_acts = [&](int s, int kb) {
+        tma_load_2d(tiles + s * STAGE_BYTES + W8_A_BYTES, &tma_x, raw_full0 + 8 * s, kb * BK, b_row0);
+      };
+      const int n_pre = min(stages, kb1 - kb0);
+      if (elect_one()) {
+        for (int i = 0; i < n_pre; ++i) {
+          mbar_expect_tx(raw_full0 + 8 * i, W8_RAW_BYTES + B_TILE_BYTES);
+          load_weights(i, kb0 + i);
+        }
+      }
+      __syncwarp();
+      pdl_wait();
+      if (elect_one()) {
+        for (int i = 0; i < n_pre; ++i) load_acts(i, kb0 + i);
+      }
+      __syncwarp();
+      int s = n_pre == stages ? 0 : n_pre;
+      uint32_t ph = n_pre == stages ? 1 : 0;
+      for (int kb = kb0 + n_pre; kb < kb1; ++kb) {
+        mbar_wait(empty0 + 8 * s, ph ^ 1);
+        if (elect_one()) {
+          mbar_expect_tx(raw_full0 + 8 * s, W8_RAW_BYTES + B_TILE_BYTES);
+          load_weights(s, kb);
+          load_acts(s, kb);
+        }
+        __syncwarp();
+        if (++s == stages) { s = 0; ph ^= 1; }
+      }
+    } else if (warp == 1) {
+      // ===== MMA issuer =====
+      constexpr uint32_t idesc = umma_idesc_bf16(BN);
+      int s = 0;
+      uint32_t ph = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(full0 + 8 * s, ph);
+        tcgen05_fence_after();
+        if (elect_one()) {
+          const uint32_t a_src = tiles + s * STAGE_BYTES;
+          const uint64_t adesc = umma_desc_sw128(a_src), bdesc = umma_desc_sw128(a_src + W8_A_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          umma_commit(empty0 + 8 * s);
+          if (kb + 1 == kb1) umma_commit(tmem_full);
+        }
+        __syncwarp();
+        if (++s == stages) { s = 0; ph ^= 1; }
+      }
+    } else {
+      // ===== converters (main loop), then epilogue =====
+      const int e = threadIdx.x - 64;  // 0..127
+      {
+        int s = 0;
+        uint32_t ph = 0;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(raw_full0 + 8 * s, ph);
+          const uint32_t a_dst = tiles + s * STAGE_BYTES;
+          const uint32_t raw = a_dst + W8_A_BYTES + B_TILE_BYTES;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int id = i * 128 + e;           // 16-byte chunk of the raw tile: consecutive threads, consecutive chunks
+            const int r = id >> 2, c = id & 3;    // row, chunk of 16 int8
+            uint32_t w0, w1, w2, w3;
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "r"(raw + r * BK + c * 16));
+            uint32_t o[8];
+            w8_widen4(w0, o[0], o[1]);
+            w8_widen4(w1, o[2], o[3]);
+            w8_widen4(w2, o[4], o[5]);
+            w8_widen4(w3, o[6], o[7]);
+            // bf16 row r: 8 chunks of 8 elements, 128B swizzle: chunk index XOR (row mod 8); 8-row groups 1024 B apart
+            const uint32_t row_base = a_dst + (r >> 3) * 1024 + (r & 7) * 128;
+            const uint32_t d0 = row_base + (((2 * c) ^ (r & 7)) << 4), d1 = row_base + (((2 * c + 1) ^ (r & 7)) << 4);
+            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(d0), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(d1), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7]) : "memory");
+          }
+          fence_proxy_async_smem();                       // generic-proxy stores -> visible to the tensor core's reads
+          asm volatile("bar.sync 1, 128;" ::: "memory");  // the four converter warps only
+          if (e == 0) mbar_arrive(full0 + 8 * s);
+          if (++s == stages) { s = 0; ph ^= 1; }
+        }
+      }
+      pdl_wait();  // the output buffers belong to the predecessor until it has completed
+      mbar_wait(tmem_full, 0, 50);
+      tcgen05_fence_after();
+      const int q = warp & 3;
+      const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16);
+      uint32_t v[16];
+      // lane = feature, column = token: transposed through the (now idle) operand ring so that global traffic is
+      // 128-bit and coalesced along the feature axis
+      float* stage_f = reinterpret_cast<float*>(smem_raw + (tiles - smem_u32(smem_raw)));  // [BN tokens][128 lanes]
+      const int lane_row = q * 32 + lane;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 16) {
+        tmem_ld16(taddr + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) stage_f[(c0 + j) * BM + lane_row] = __uint_as_float(v[j]);
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (SILU) {
+        for (int idx = e; idx < BN * 16; idx += 128) {
+          const int t = idx >> 4, f = (idx & 15) * 4;
+          const int tok = b_row0 + t, feat = a_row0 + f;
+          if (tok < p.m_tokens && feat < p.n_features) {
+            const float4 g4 = *reinterpret_cast<const float4*>(stage_f + t * BM + f);
+            const float4 u4 = *reinterpret_cast<const float4*>(stage_f + t * BM + 64 + f);
+            float gs[4], us[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const bool ok = feat + j < p.n_features;
+              gs[j] = ok ? p.scale[feat + j] : 0.f;
+              us[j] = ok ? p.scale[p.up_row_offset + feat + j] : 0.f;
+            }
+            const float gg[4] = {g4.x * gs[0], g4.y * gs[1], g4.z * gs[2], g4.w * gs[3]};
+            const float uu[4] = {u4.x * us[0], u4.y * us[1], u4.z * us[2], u4.w * us[3]};
+            __nv_bfloat16* o = (__nv_bfloat16*)p.out + (long long)tok * p.ldo + feat;
+            if (feat + 4 <= p.n_features) {
+              *reinterpret_cast<uint2*>(o) = make_uint2(pack_bf16(w8_silu(gg[0]) * uu[0], w8_silu(gg[1]) * uu[1]),
+                                                        pack_bf16(w8_silu(gg[2]) * uu[2], w8_silu(gg[3]) * uu[3]));
+            } else {
+              for (int j = 0; j < 4 && feat + j < p.n_features; ++j) o[j] = __float2bfloat16_rn(w8_silu(gg[j]) * uu[j]);
+            }
+          }
+        }
+      } else {
+        for (int idx = e; idx < BN * 32; idx += 128) {
+          const int t = idx >> 5, f = (idx & 31) * 4;
+          const int tok = b_row0 + t, feat = a_row0 + f;
+          if (tok < p.m_tokens && feat < p.n_features) {
+            const float4 a4 = *reinterpret_cast<const float4*>(stage_f + t * BM + f);
+            float aa[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) aa[j] *= (feat + j < p.n_features) ? p.scale[feat + j] : 0.f;
+            const bool full = feat + 4 <= p.n_features;
+            if (EPI == DLI_EPI_STORE_BF16) {
+              __nv_bfloat16* o = (__nv_bfloat16*)p.out + (long long)tok * p.ldo + feat;
+              if (full) *reinterpret_cast<uint2*>(o) = make_uint2(pack_bf16(aa[0], aa[1]), pack_bf16(aa[2], aa[3]));
+              else for (int j = 0; j < 4 && feat + j < p.n_features; ++j) o[j] = __float2bfloat16_rn(aa[j]);
+            } else {
+              float* o = (float*)p.out + (long long)tok * p.ldo + feat;
+              if (full && EPI == DLI_EPI_ADD_F32) {
+                asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o), "f"(aa[0]), "f"(aa[1]), "f"(aa[2]), "f"(aa[3])
+                             : "memory");
+              } else if (full) {
+                *reinterpret_cast<float4*>(o) = make_float4(aa[0], aa[1], aa[2], aa[3]);
+              } else {
+                for (int j = 0; j < 4 && feat + j < p.n_features; ++j) {
+                  if (EPI == DLI_EPI_ADD_F32) atomicAdd(o + j, aa[j]);
+                  else o[j] = aa[j];
+                }
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TMEM_COLS) : "memory");
+  }
+}
+
+// ---- host side ----------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFnW8)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// 2-D uint8 tensor [rows, cols]; box = [box_rows, 64 bytes], no swizzle (the converter warps read it with plain loads)
+int make_tmap_u8(CUtensorMap* map, const void* base, long long rows, long long cols, int box_rows) {
+  static EncodeTiledFnW8 fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFnW8>(ptr);
+  }
+  if (!fn) return fail(DLI_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (cols % 16) != 0)
+    return fail(DLI_ERR_ARG, "int8 TMA operand needs a 16-byte aligned base and a row length that is a multiple of 16");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(DLI_ERR_CUDA, "cuTensorMapEncodeTiled (uint8) failed with CUresult %d", (int)r);
+  return DLI_OK;
+}
+
+template <int BN, int EPI>
+static int launch_w8_variant(const CUtensorMap& tw, const CUtensorMap& tx, const W8Params& p, dim3 grid, cudaStream_t st) {
+  constexpr int STAGE_BYTES = W8_A_BYTES + BN * BK * 2 + W8_RAW_BYTES;
+  const size_t smem = (size_t)p.stages * STAGE_BYTES + 1024;
+  auto kern = gemm_w8_kernel<BN, EPI>;
+  DLI_ONCE_PER_DEVICE(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+  return launch_kernel("gemm_w8_kernel", kern, grid, dim3(W8_THREADS), smem, st, tw, tx, p);
+}
+
+template <int BN>
+static int launch_w8_epi(int epi, const CUtensorMap& tw, const CUtensorMap& tx, const W8Params& p, dim3 grid, cudaStream_t st) {
+  switch (epi) {
+    case DLI_EPI_STORE_F32: return launch_w8_variant<BN, DLI_EPI_STORE_F32>(tw, tx, p, grid, st);
+    case DLI_EPI_ADD_F32: return launch_w8_variant<BN, DLI_EPI_ADD_F32>(tw, tx, p, grid, st);
+    case DLI_EPI_STORE_BF16: return launch_w8_variant<BN, DLI_EPI_STORE_BF16>(tw, tx, p, grid, st);
+    case DLI_EPI_SILU_MUL_BF16: return launch_w8_variant<BN, DLI_EPI_SILU_MUL_BF16>(tw, tx, p, grid, st);
+    default: return fail(DLI_ERR_ARG, "unknown epilogue %d", epi);
+  }
+}
+
+// tmap_w: uint8 map of the quantised matrix with box rows = 128 (64 for the gate|up epilogue); tmap_x: bf16 activations
+// with box rows = plan.bn.  The plan is plan_gemm's (same tiles and split-K); only the stage count differs.
+int launch_gemm_w8_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const CUtensorMap& tmap_w, const float* scale, void* out,
+                           long long ldo, int m, int n, int epilogue, cudaStream_t st) {
+  if (!g.swap) return fail(DLI_ERR_UNSUPPORTED, "the int8-weight GEMM is the decode kernel: m = %d > 128", m);
+  W8Params p{};
+  p.out = out;
+  p.ldo = ldo;
+  p.m_tokens = m;
+  p.n_features = n;
+  p.k_blocks = g.k_blocks;
+  p.kb_per_split = g.kb_per_split;
+  const int stage_bytes = W8_A_BYTES + g.bn * BK * 2 + W8_RAW_BYTES;
+  p.stages = std::max(2, std::min(std::min(W8_MAX_STAGES, (112 * 1024 - 2048) / stage_bytes), g.kb_per_split));
+  p.up_row_offset = n;
+  p.scale = scale;
+  dim3 grid(g.grid_x, g.grid_y, g.splits);
+  switch (g.bn) {
+    case 16: return launch_w8_epi<16>(epilogue, tmap_w, tmap_x, p, grid, st);
+    case 32: return launch_w8_epi<32>(epilogue, tmap_w, tmap_x, p, grid, st);
+    case 64: return launch_w8_epi<64>(epilogue, tmap_w, tmap_x, p, grid, st);
+    default: return launch_w8_epi<128>(epilogue, tmap_w, tmap_x, p, grid, st);
+  }
+}
+
+int launch_gemm_w8(const void* x, long long ldx, const void* q, const float* scale, void* out, long long ldo, int m, int n,
+                   int k, int epilogue, cudaStream_t st) {
+  DLI_REQUIRE(x && q && scale && out, "dli_gemm_w8: null pointer");
+  DLI_REQUIRE(m > 0 && m <= 128 && n > 0 && k > 0, "dli_gemm_w8: m=%d n=%d k=%d (decode kernel: m <= 128)", m, n, k);
+  DLI_REQUIRE(k % 16 == 0 && ldx % 8 == 0, "dli_gemm_w8: k must be a multiple of 16 and ldx of 8 (k=%d ldx=%lld)", k, ldx);
+  DLI_REQUIRE(epilogue >= 0 && epilogue <= DLI_EPI_SILU_MUL_BF16, "dli_gemm_w8: unknown epilogue %d", epilogue);
+  int epi = epilogue;
+  GemmPlan g = plan_gemm(m, n, k, epi);
+  if (epi == DLI_EPI_STORE_F32) {  // split-K partials meet in L2: clear the destination, then add
+    DLI_CUDA_OK(cudaMemset2DAsync(out, (size_t)ldo * 4, 0, (size_t)n * 4, (size_t)m, st));
+    count_launch();
+    epi = DLI_EPI_ADD_F32;
+    g = plan_gemm(m, n, k, epi);
+  }
+  const long long w_rows = epilogue == DLI_EPI_SILU_MUL_BF16 ? 2LL * n : n;
+  CUtensorMap tx, tw;
+  int rc = make_tmap_bf16(&tx, x, m, k, ldx, g.b_box_rows);
+  if (rc) return rc;
+  if ((rc = make_tmap_u8(&tw, q, w_rows, k, g.a_box_rows))) return rc;
+  return launch_gemm_w8_planned(g, tx, tw, scale, out, ldo, m, n, epi, st);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Row-wise absmax int8 quantisation (the weight format of bitsandbytes Linear8bitLt with has_fp16_weights=False,
+// utils/model.py:102-108): scale[r] = max_k |w[r, k]| / 127, q[r, k] = round(w[r, k] / scale[r]) stored as q + 128.
+// One CTA per row; and the inverse, for the prefill path, which runs the bf16 tensor-core GEMMs on a dequantised copy.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) quantize_rows_w8_kernel(const __nv_bfloat16* __restrict__ w, long long k,
+                                                               uint8_t* __restrict__ q, float* __restrict__ scale) {
+  __shared__ float red[8];
+  const long long row = blockIdx.x;
+  const __nv_bfloat16* src = w + row * k;
+  float mx = 0.f;
+  for (long long i = threadIdx.x * 8LL; i < k; i += 256 * 8) {
+    const uint4 a = *reinterpret_cast<const uint4*>(src + i);
+    const uint32_t u[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) mx = fmaxf(mx, fmaxf(fabsf(bf16_lo(u[j])), fabsf(bf16_hi(u[j]))));
+  }
+  mx = warp_max(mx);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+  __syncthreads();
+  mx = red[0];
+#pragma unroll
+  for (int i = 1; i < 8; ++i) mx = fmaxf(mx, red[i]);
+  const float s = mx / 127.0f, inv = mx > 0.f ? 127.0f / mx : 0.f;
+  if (threadIdx.x == 0) scale[row] = s;
+  uint8_t* dst = q + row * k;
+  for (long long i = threadIdx.x * 8LL; i < k; i += 256 * 8) {
+    const uint4 a = *reinterpret_cast<const uint4*>(src + i);
+    const uint32_t u[4] = {a.x, a.y, a.z, a.w};
+    uint32_t o[2] = {0, 0};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int q0 = max(-127, min(127, __float2int_rn(bf16_lo(u[j]) * inv))) + 128;
+      const int q1 = max(-127, min(127, __float2int_rn(bf16_hi(u[j]) * inv))) + 128;
+      o[j >> 1] |= ((uint32_t)q0 | ((uint32_t)q1 << 8)) << (16 * (j & 1));
+    }
+    *reinterpret_cast<uint2*>(dst + i) = make_uint2(o[0], o[1]);
+  }
+}
+
+__global__ void __launch_bounds__(256) dequantize_rows_w8_kernel(const uint8_t* __restrict__ q, const float* __restrict__ scale,
+                                                                 long long k, __nv_bfloat16* __restrict__ w) {
+  pdl_trigger();
+  pdl_wait();
+  const long long row = blockIdx.x;
+  const float s = scale[row];
+  const uint8_t* src = q + row * k;
+  __nv_bfloat16* dst = w + row * k;
+  for (long long i = (blockIdx.y * 256LL + threadIdx.x) * 8; i < k; i += (long long)gridDim.y * 256 * 8) {
+    const uint2 a = *reinterpret_cast<const uint2*>(src + i);
+    const uint32_t u[2] = {a.x, a.y};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t b = u[j >> 1] >> (16 * (j & 1));
+      o[j] = pack_bf16(((int)(b & 0xff) - 128) * s, ((int)((b >> 8) & 0xff) - 128) * s);
+    }
+    *reinterpret_cast<uint4*>(dst + i) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+int launch_quantize_rows_w8(const void* w_bf16, long long n, long long k, void* q_u8, float* scale, cudaStream_t st) {
+  DLI_REQUIRE(w_bf16 && q_u8 && scale && n > 0 && k > 0 && k % 16 == 0, "dli_quantize_rows_w8: null pointer or k %% 16 != 0");
+  quantize_rows_w8_kernel<<<(unsigned)n, 256, 0, st>>>((const __nv_bfloat16*)w_bf16, k, (uint8_t*)q_u8, scale);
+  DLI_CHECK_LAUNCH("quantize_rows_w8_kernel");
+  return DLI_OK;
+}
+
+int launch_dequantize_rows_w8(const void* q_u8, const float* scale, long long n, long long k, void* w_bf16, cudaStream_t st) {
+  DLI_REQUIRE(w_bf16 && q_u8 && scale && n > 0 && k > 0 && k % 16 == 0, "dli_dequantize_rows_w8: null pointer or k %% 16 != 0");
+  const int ny = (int)std::max<long long>(1, std::min<long long>(4, k / 2048));
+  return launch_kernel("dequantize_rows_w8_kernel", dequantize_rows_w8_kernel, dim3((unsigned)n, ny), dim3(256), 0, st,
+                       (const uint8_t*)q_u8, scale, k, (__nv_bfloat16*)w_bf16);
+}
+
+}  // namespace dli

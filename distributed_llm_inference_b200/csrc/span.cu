@@ -5,6 +5,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <new>
 #include <vector>
 
@@ -86,10 +87,22 @@ int kv_view(const dli_kv_desc* kv, int layer, KvView* out) {
 struct WeightMaps {
   CUtensorMap box64, box128, box256;
 };
+struct W8Maps {
+  CUtensorMap box64, box128;  // uint8 maps of a quantised matrix
+  const void* q = nullptr;
+  const float* scale = nullptr;
+  long long rows = 0, cols = 0;
+};
 struct Layer {
   dli_layer_weights w{};
   bool bound = false;
+  bool w8 = false;            // weights bound through dli_span_bind_weights_w8 (row-wise int8 + fp32 scales)
   WeightMaps qkv, o, gu, down;
+  W8Maps qkv8, o8, gu8, down8;
+};
+struct ScratchMaps {          // bf16 maps over the dequantisation scratch for one matrix shape (prefill of a w8 span)
+  long long rows, cols;
+  WeightMaps m;
 };
 struct ProfMark {
   cudaEvent_t ev;
@@ -108,6 +121,9 @@ struct dli_span {
   int n_qkv;  // (H + 2 KV) * hd
   std::vector<dli::Layer> layers;
   std::vector<dli::ActMapKey> act_maps;  // activation-side TMA descriptors, keyed by (pointer, shape, box)
+  void* dq_scratch = nullptr;            // caller-allocated bf16 scratch a w8 span dequantises into at prefill
+  size_t dq_scratch_bytes = 0;
+  std::vector<dli::ScratchMaps> dq_maps;
   const void* head_ptr = nullptr;        // lm_head matrix the maps below describe (dli_stage_decode_step)
   int head_vocab = 0;
   dli::WeightMaps head;
@@ -192,7 +208,41 @@ static int prof_mark(dli_span* s, int cls, cudaStream_t st) {
 
 // one linear layer of the span: out (+)= x[m, k] . w[n, k]^T through the planned tcgen05 kernel
 static int span_gemm(dli_span* s, const void* x, const WeightMaps& wm, void* out, long long ldo, int m, int n, int k,
-                     int epilogue, cudaStream_t st, const RopeArgs* rope = nullptr) {
+                     int epilogue, cudaStream_t st, const RopeArgs* rope = nullptr, const W8Maps* w8 = nullptr);
+
+// a quantised matrix at prefill: widen it into the scratch, then the bf16 tensor-core GEMM on the copy
+static int span_gemm_dequant(dli_span* s, const void* x, const W8Maps& w8, void* out, long long ldo, int m, int n, int k,
+                             int epilogue, cudaStream_t st, const RopeArgs* rope) {
+  const size_t need = (size_t)w8.rows * w8.cols * 2;
+  if (!s->dq_scratch || s->dq_scratch_bytes < need)
+    return fail(DLI_ERR_WORKSPACE, "int8-weight span: chunks of more than 128 tokens need a dequantisation scratch of %zu bytes "
+                                   "(dli_span_set_dequant_scratch)", need);
+  int rc = launch_dequantize_rows_w8(w8.q, w8.scale, w8.rows, w8.cols, s->dq_scratch, st);
+  if (rc) return rc;
+  ScratchMaps* sm = nullptr;
+  for (auto& e : s->dq_maps)
+    if (e.rows == w8.rows && e.cols == w8.cols) sm = &e;
+  if (!sm) {
+    ScratchMaps e{w8.rows, w8.cols, {}};
+    if ((rc = make_tmap_bf16(&e.m.box128, s->dq_scratch, w8.rows, w8.cols, w8.cols, 128))) return rc;
+    if ((rc = make_tmap_bf16(&e.m.box64, s->dq_scratch, w8.rows, w8.cols, w8.cols, 64))) return rc;
+    if ((rc = make_tmap_bf16(&e.m.box256, s->dq_scratch, w8.rows, w8.cols, w8.cols, 256))) return rc;
+    s->dq_maps.push_back(e);
+    sm = &s->dq_maps.back();
+  }
+  return span_gemm(s, x, sm->m, out, ldo, m, n, k, epilogue, st, rope, nullptr);
+}
+
+static int span_gemm(dli_span* s, const void* x, const WeightMaps& wm, void* out, long long ldo, int m, int n, int k,
+                     int epilogue, cudaStream_t st, const RopeArgs* rope, const W8Maps* w8) {
+  if (w8 && w8->q) {
+    if (m > 128 || epilogue == DLI_EPI_QKV_ROPE_INTERNAL) return span_gemm_dequant(s, x, *w8, out, ldo, m, n, k, epilogue, st, rope);
+    const GemmPlan g8 = plan_gemm(m, n, k, epilogue);
+    const CUtensorMap* tx8 = nullptr;
+    int rc8 = act_map(s, x, m, k, g8.b_box_rows, &tx8);
+    if (rc8) return rc8;
+    return launch_gemm_w8_planned(g8, *tx8, g8.a_box_rows == 64 ? w8->box64 : w8->box128, w8->scale, out, ldo, m, n, epilogue, st);
+  }
   const GemmPlan g = plan_gemm(m, n, k, epilogue);
   const int x_box = g.swap ? g.b_box_rows : g.a_box_rows;
   const int w_box = g.swap ? g.a_box_rows : g.b_box_rows;
@@ -345,6 +395,64 @@ int dli_span_bind_weights(dli_span* s, int layer, const dli_layer_weights* w) {
   L.w = *w;
   L.bound = true;
   return DLI_OK;
+}
+
+int dli_span_bind_weights_w8(dli_span* s, int layer, const dli_layer_weights_w8* w) {
+  DLI_REQUIRE(s && w, "dli_span_bind_weights_w8: null pointer");
+  DLI_REQUIRE(layer >= 0 && layer < s->d.n_layers, "dli_span_bind_weights_w8: layer %d out of range", layer);
+  DLI_REQUIRE(w->wqkv && w->wo && w->wgu && w->wdown && w->sqkv && w->so && w->sgu && w->sdown && w->g_in && w->g_post,
+              "dli_span_bind_weights_w8: null weight or scale pointer");
+  Layer& L = s->layers[layer];
+  const dli_span_desc& d = s->d;
+  const int qdim = d.n_heads * d.head_dim;
+  struct { const void* p; const float* sc; long long rows, cols; W8Maps* m; } items[4] = {
+      {w->wqkv, w->sqkv, s->n_qkv, d.hidden_size, &L.qkv8},
+      {w->wo, w->so, d.hidden_size, qdim, &L.o8},
+      {w->wgu, w->sgu, 2LL * d.intermediate_size, d.hidden_size, &L.gu8},
+      {w->wdown, w->sdown, d.hidden_size, d.intermediate_size, &L.down8}};
+  for (auto& it : items) {
+    int rc = make_tmap_u8(&it.m->box128, it.p, it.rows, it.cols, 128);
+    if (rc) return rc;
+    if ((rc = make_tmap_u8(&it.m->box64, it.p, it.rows, it.cols, 64))) return rc;
+    it.m->q = it.p;
+    it.m->scale = it.sc;
+    it.m->rows = it.rows;
+    it.m->cols = it.cols;
+  }
+  L.w = dli_layer_weights{nullptr, nullptr, nullptr, nullptr, w->g_in, w->g_post};
+  L.w8 = true;
+  L.bound = true;
+  return DLI_OK;
+}
+
+int dli_span_set_dequant_scratch(dli_span* s, void* scratch_bf16, size_t bytes) {
+  DLI_REQUIRE(s, "dli_span_set_dequant_scratch: null span");
+  DLI_REQUIRE(!scratch_bf16 || (reinterpret_cast<uintptr_t>(scratch_bf16) & 255) == 0, "dli_span_set_dequant_scratch: 256-byte alignment");
+  s->dq_scratch = scratch_bf16;
+  s->dq_scratch_bytes = scratch_bf16 ? bytes : 0;
+  s->dq_maps.clear();
+  return DLI_OK;
+}
+
+size_t dli_span_dequant_scratch_bytes(const dli_span* s) {
+  if (!s) return 0;
+  const dli_span_desc& d = s->d;
+  const size_t a = (size_t)s->n_qkv * d.hidden_size, b = (size_t)d.hidden_size * d.n_heads * d.head_dim,
+               c = (size_t)2 * d.intermediate_size * d.hidden_size;
+  return 2 * std::max(a, std::max(b, c));
+}
+
+int dli_gemm_w8(const void* x_bf16, int64_t ldx, const void* q_u8, const float* scale, void* out, int64_t ldo, int m, int n,
+                int k, int epilogue, dli_stream_t stream) {
+  return launch_gemm_w8(x_bf16, ldx, q_u8, scale, out, ldo, m, n, k, epilogue, (cudaStream_t)stream);
+}
+
+int dli_quantize_rows_w8(const void* w_bf16, int64_t n, int64_t k, void* q_u8, float* scale, dli_stream_t stream) {
+  return launch_quantize_rows_w8(w_bf16, n, k, q_u8, scale, (cudaStream_t)stream);
+}
+
+int dli_dequantize_rows_w8(const void* q_u8, const float* scale, int64_t n, int64_t k, void* w_bf16, dli_stream_t stream) {
+  return launch_dequantize_rows_w8(q_u8, scale, n, k, w_bf16, (cudaStream_t)stream);
 }
 
 size_t dli_span_workspace_bytes(const dli_span* span, int max_tokens, int max_batch, int max_ctx) {
@@ -519,11 +627,11 @@ static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int 
                                 decode_attention_fuses_rope(view, batch, d.n_heads, d.n_kv_heads, d.head_dim);
     if (fused_rope) {
       RopeArgs ra{cos, sin, w.qbuf, view, q_len, d.n_heads, d.n_kv_heads, d.head_dim};
-      DLI_STEP(DLI_PROF_GEMM_QKV, span_gemm(s, w.xn, L.qkv, nullptr, 0, M, s->n_qkv, h, DLI_EPI_QKV_ROPE_INTERNAL, st, &ra));
+      DLI_STEP(DLI_PROF_GEMM_QKV, span_gemm(s, w.xn, L.qkv, nullptr, 0, M, s->n_qkv, h, DLI_EPI_QKV_ROPE_INTERNAL, st, &ra, L.w8 ? &L.qkv8 : nullptr));
     } else {
       float* qkv = skinny ? w.qkv_acc : w.qkv;
       DLI_STEP(DLI_PROF_GEMM_QKV, span_gemm(s, w.xn, L.qkv, qkv, s->n_qkv, M, s->n_qkv, h,
-                                            skinny ? DLI_EPI_ADD_F32 : DLI_EPI_STORE_F32, st));
+                                            skinny ? DLI_EPI_ADD_F32 : DLI_EPI_STORE_F32, st, nullptr, L.w8 ? &L.qkv8 : nullptr));
       DLI_MARK(DLI_PROF_ROPE_APPEND);
       if (!fused_dec_rope && !DLI_SKIPPED(DLI_PROF_ROPE_APPEND)) {
         rc = launch_rope_kv_append(qkv, skinny, cos, sin, w.qbuf, view, batch, q_len, d.n_heads, d.n_kv_heads, d.head_dim,
@@ -550,14 +658,14 @@ static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int 
                                                             d.head_dim, causal != 0, st));
     }
     // o_proj + residual (modules.py:112,173)
-    DLI_STEP(DLI_PROF_GEMM_O, span_gemm(s, w.attn, L.o, w.resid, h, M, h, qdim, DLI_EPI_ADD_F32, st));
+    DLI_STEP(DLI_PROF_GEMM_O, span_gemm(s, w.attn, L.o, w.resid, h, M, h, qdim, DLI_EPI_ADD_F32, st, nullptr, L.w8 ? &L.o8 : nullptr));
     // post_attention_layernorm of h + h (modules.py:179)
     DLI_STEP(DLI_PROF_RMSNORM, launch_rmsnorm(w.resid, true, (const __nv_bfloat16*)L.w.g_post, w.xn, nullptr, nullptr, M, h,
                                               d.eps_post, d.post_prescale, st));
     // MLP (modules.py:181,182): gate|up with silu(gate) * up as the GEMM epilogue on both paths (64 gate + 64 up weight
     // rows per CTA at decode, 128 + 128 accumulator columns per CTA pair at prefill), then down + residual
-    DLI_STEP(DLI_PROF_GEMM_GATE_UP, span_gemm(s, w.xn, L.gu, w.act, inter, M, inter, h, DLI_EPI_SILU_MUL_BF16, st));
-    DLI_STEP(DLI_PROF_GEMM_DOWN, span_gemm(s, w.act, L.down, w.resid, h, M, h, inter, DLI_EPI_ADD_F32, st));
+    DLI_STEP(DLI_PROF_GEMM_GATE_UP, span_gemm(s, w.xn, L.gu, w.act, inter, M, inter, h, DLI_EPI_SILU_MUL_BF16, st, nullptr, L.w8 ? &L.gu8 : nullptr));
+    DLI_STEP(DLI_PROF_GEMM_DOWN, span_gemm(s, w.act, L.down, w.resid, h, M, h, inter, DLI_EPI_ADD_F32, st, nullptr, L.w8 ? &L.down8 : nullptr));
   }
 #undef DLI_STEP
   DLI_MARK(DLI_PROF_CAST);

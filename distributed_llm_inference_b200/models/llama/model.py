@@ -108,6 +108,7 @@ class LlamaBlock(nn.Module):
         self._ws: Optional[torch.Tensor] = None
         self._ws_key = (0, 0, 0)
         self._scratch_cache: Optional[PartialLlamaSinkCache] = None
+        self._dq: Optional[torch.Tensor] = None
         self.last_launch_count = 0
 
     # ------------------------------------------------------------------ native span object
@@ -120,9 +121,17 @@ class LlamaBlock(nn.Module):
         ffi = self._ffi()
         for layer in self.layers:
             layer.fuse()
-        ptrs = tuple(p.data_ptr() for layer in self.layers for p in
-                     (layer._wqkv, layer.self_attn.o_proj.weight, layer._wgu, layer.mlp.down_proj.weight,
-                      layer.input_layernorm.weight, layer.post_attention_layernorm.weight))
+        w8 = [layer.w8 is not None for layer in self.layers]
+        if any(w8) and not all(w8):
+            raise ValueError("either every layer of a span is quantised (quantize_w8) or none")
+        if all(w8):
+            ptrs = tuple(t.data_ptr() for layer in self.layers
+                         for t in (*layer.w8["qkv"], *layer.w8["o"], *layer.w8["gu"], *layer.w8["down"],
+                                   layer.input_layernorm.weight, layer.post_attention_layernorm.weight))
+        else:
+            ptrs = tuple(p.data_ptr() for layer in self.layers for p in
+                         (layer._wqkv, layer.self_attn.o_proj.weight, layer._wgu, layer.mlp.down_proj.weight,
+                          layer.input_layernorm.weight, layer.post_attention_layernorm.weight))
         if self._span is not None and ptrs == self._bound_ptrs:
             return
         cfg = self.config
@@ -133,13 +142,32 @@ class LlamaBlock(nn.Module):
             out = C.c_void_p()
             ffi.check(ffi.lib.dli_span_create(C.byref(desc), C.byref(out)))
             self._span = out
+        per = len(ptrs) // len(self.layers)
         for j, layer in enumerate(self.layers):
-            for p in layer.parameters():
+            for p in (layer.input_layernorm.weight, layer.post_attention_layernorm.weight):
                 if p.device != device or p.dtype != torch.bfloat16:
                     raise ValueError(f"layer {j}: parameters must be bf16 on {device} (got {p.dtype} on {p.device})")
-            w = ffi.LayerWeights(*ptrs[6 * j: 6 * j + 6])
-            ffi.check(ffi.lib.dli_span_bind_weights(self._span, j, C.byref(w)))
+            if all(w8):
+                w = ffi.LayerWeightsW8(*ptrs[per * j: per * (j + 1)])
+                ffi.check(ffi.lib.dli_span_bind_weights_w8(self._span, j, C.byref(w)))
+            else:
+                for p in layer.parameters():
+                    if p.device != device or p.dtype != torch.bfloat16:
+                        raise ValueError(f"layer {j}: parameters must be bf16 on {device} (got {p.dtype} on {p.device})")
+                w = ffi.LayerWeights(*ptrs[per * j: per * (j + 1)])
+                ffi.check(ffi.lib.dli_span_bind_weights(self._span, j, C.byref(w)))
+        if all(w8):   # prefill of a quantised span widens one matrix at a time into this scratch
+            nbytes = ffi.lib.dli_span_dequant_scratch_bytes(self._span)
+            if self._dq is None or self._dq.numel() < nbytes or self._dq.device != device:
+                self._dq = torch.empty(nbytes, dtype=torch.uint8, device=device)
+            ffi.check(ffi.lib.dli_span_set_dequant_scratch(self._span, self._dq.data_ptr(), self._dq.numel()))
         self._bound_ptrs = ptrs
+
+    def quantize_w8(self) -> "LlamaBlock":
+        """Row-wise int8 weights for every layer of the span (see ``OptimizedLlamaDecoderLayer.quantize_w8``)."""
+        for layer in self.layers:
+            layer.quantize_w8()
+        return self
 
     def __del__(self):
         try:

@@ -82,6 +82,39 @@ class OptimizedLlamaDecoderLayer(nn.Module):
         self.post_attention_layernorm = _Weight(config.hidden_size, dtype=dtype, ones=True)  # eps 1e-6: modules.py:125
         self._wqkv: Optional[torch.Tensor] = None
         self._wgu: Optional[torch.Tensor] = None
+        self.w8 = None      # after quantize_w8(): {"qkv": (uint8 [n, k], fp32 [n]), "o": ..., "gu": ..., "down": ...}
+
+    @torch.no_grad()
+    def quantize_w8(self) -> None:
+        """Replace the seven linear weights by row-wise absmax int8 + one fp32 scale per output row -- the weight format
+        of the reference's optimised mode (bitsandbytes ``Linear8bitLt(has_fp16_weights=False)``, utils/model.py:102-108)
+        -- computed on the GPU by ``dli_quantize_rows_w8``; the bf16 copies are released (the ``*.weight`` parameters
+        become empty).  Decode then streams half the weight bytes (``dli_gemm_w8``)."""
+        from distributed_llm_inference_b200 import _ffi
+
+        if self.w8 is not None:
+            return
+        self.fuse()
+        a, m = self.self_attn, self.mlp
+        if not self._wqkv.is_cuda:
+            raise RuntimeError("quantize_w8 runs on the GPU: move the block to CUDA first")
+        out = {}
+        with torch.cuda.device(self._wqkv.device):
+            for name, w in (("qkv", self._wqkv), ("o", a.o_proj.weight.data), ("gu", self._wgu), ("down", m.down_proj.weight.data)):
+                w = w.contiguous()
+                n, k = w.shape
+                q = torch.empty(n, k, dtype=torch.uint8, device=w.device)
+                sc = torch.empty(n, dtype=torch.float32, device=w.device)
+                _ffi.check(_ffi.lib.dli_quantize_rows_w8(w.data_ptr(), n, k, q.data_ptr(), sc.data_ptr(),
+                                                         _ffi.current_stream(w.device)))
+                out[name] = (q, sc)
+            torch.cuda.synchronize(self._wqkv.device)
+        self.w8 = out
+        empty = torch.empty(0, dtype=self._wqkv.dtype, device=self._wqkv.device)
+        for p in (a.q_proj.weight, a.k_proj.weight, a.v_proj.weight, a.o_proj.weight, m.gate_proj.weight, m.up_proj.weight,
+                  m.down_proj.weight):
+            p.data = empty
+        self._wqkv = self._wgu = None
 
     def _is_fused(self) -> bool:
         a, m = self.self_attn, self.mlp
@@ -99,7 +132,7 @@ class OptimizedLlamaDecoderLayer(nn.Module):
 
     @torch.no_grad()
     def fuse(self) -> None:
-        if self._is_fused():
+        if self.w8 is not None or self._is_fused():
             return
         a, m = self.self_attn, self.mlp
         wqkv = torch.cat([a.q_proj.weight.data, a.k_proj.weight.data, a.v_proj.weight.data], dim=0).contiguous()

@@ -7,8 +7,8 @@ puts them on the CPU.  Here the same contract works offline: ``model_name`` is a
 shards that hold the span's layers are opened; tensors are cast to bf16 (the span kernels' dtype; the reference's
 fp16 cast is a dtype choice) and copied into the ``LlamaBlock``'s parameters, whose names are the
 reference's (``layers.{j}.self_attn.q_proj.weight`` ...).  ``convert_to_optimized_block`` (bitsandbytes int8,
-utils/model.py:93-123) has no counterpart: the B200 span is already the optimised path; it just moves the block
-to the GPU.
+utils/model.py:93-123) moves the block to the GPU and optionally stores the weights as row-wise int8 (weight-only:
+activations stay bf16).
 """
 from __future__ import annotations
 
@@ -90,9 +90,17 @@ def load_block(model_name: str, layer_ids: List[int], use_quantized: bool = Fals
 
 
 def convert_to_optimized_block(block: LlamaBlock, quantize: bool = False, threshold: float = 5.0) -> LlamaBlock:
-    """utils/model.py:116-123 without the int8 conversion: the block's forward already runs the sm_100a kernels."""
-    if quantize:
-        raise NotImplementedError("int8 (bitsandbytes) weights are outside the bf16 span kernels")
+    """utils/model.py:116-123: move the block to the GPU and, with ``quantize=True``, store every linear weight as
+    row-wise absmax int8 + one fp32 scale per output row -- the weight format of the reference's
+    ``Linear8bitLt(has_fp16_weights=False)`` (utils/model.py:102-108).  The reference converts regardless of the flag
+     and also quantises the ACTIVATIONS vector-wise to int8, with the columns that hold a value above
+    ``threshold`` kept in fp16 (LLM.int8); here activations stay bf16, so there is nothing for ``threshold`` to
+    protect and it is unused -- the result is closer to the unquantised model than the reference's, not identical to
+    it.  ``quantize=False`` keeps the bf16 span (the north star's dtype)."""
     if not torch.cuda.is_available():
-        raise NotImplementedError("the B200 span needs a CUDA device")
-    return block.to(torch.device("cuda"))
+        raise NotImplementedError("the B200 span needs a CUDA device" if not quantize else
+                                  "Quantization is only supported on CUDA devices")      # utils/model.py:117-118
+    block = block.to(torch.device("cuda"))
+    if quantize:
+        block.quantize_w8()
+    return block

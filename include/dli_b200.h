@@ -221,6 +221,36 @@ int dli_span_create(const dli_span_desc* desc, dli_span** out);
 int dli_span_destroy(dli_span* span);
 int dli_span_bind_weights(dli_span* span, int layer, const dli_layer_weights* w);
 
+/* ------------------------------------------------------------------------------------------------
+ * Weight-only int8 (the weight format of the reference's optimised mode: convert_to_optimized_block turns every
+ * nn.Linear into bitsandbytes Linear8bitLt(has_fp16_weights=False), utils/model.py:93-123, i.e. row-wise absmax int8
+ * with one fp32 scale per output row).  q[r, k] = round(w[r, k] / scale[r]) + 128 as uint8, scale[r] = max|w[r, :]| / 127.
+ * Activations stay bf16: the decode GEMM widens the int8 tile to bf16 in shared memory (exact) and scales the fp32
+ * accumulator by scale[r] -- half the weight bytes per decode step, no activation quantisation, no outlier columns.
+ * Chunks of more than 128 tokens (prefill) dequantise one matrix at a time into a caller-allocated bf16 scratch and
+ * run the bf16 GEMMs on it.
+ * ---------------------------------------------------------------------------------------------- */
+int dli_quantize_rows_w8(const void* w_bf16, int64_t n, int64_t k, void* q_u8, float* scale, dli_stream_t stream);
+int dli_dequantize_rows_w8(const void* q_u8, const float* scale, int64_t n, int64_t k, void* w_bf16, dli_stream_t stream);
+/* out[m, n] (+)= scale[n] * sum_k x[m, k] * (q[n, k] - 128), m <= 128, k % 16 == 0; epilogues as dli_gemm (for
+ * DLI_EPI_SILU_MUL_BF16, q and scale hold 2n rows: gate then up). */
+int dli_gemm_w8(const void* x_bf16, int64_t ldx, const void* q_u8, const float* scale, void* out, int64_t ldo, int m,
+                int n, int k, int epilogue, dli_stream_t stream);
+
+typedef struct dli_layer_weights_w8 {
+  const void* wqkv;  const float* sqkv;   /* uint8 [(H + 2*KV) * hd, h], fp32 [(H + 2*KV) * hd] */
+  const void* wo;    const float* so;     /* [h, H * hd], [h]                                    */
+  const void* wgu;   const float* sgu;    /* [2 * i, h], [2 * i]                                 */
+  const void* wdown; const float* sdown;  /* [h, i], [h]                                         */
+  const void* g_in;                       /* bf16 [h] input_layernorm.weight                     */
+  const void* g_post;                     /* bf16 [h] post_attention_layernorm.weight            */
+} dli_layer_weights_w8;
+int dli_span_bind_weights_w8(dli_span* span, int layer, const dli_layer_weights_w8* w);
+/* bf16 scratch for the prefill path of a span with int8 weights: at least dli_span_dequant_scratch_bytes(span) bytes,
+ * 256-byte aligned, caller-allocated, borrowed until replaced or the span is destroyed. */
+size_t dli_span_dequant_scratch_bytes(const dli_span* span);
+int dli_span_set_dequant_scratch(dli_span* span, void* scratch_bf16, size_t bytes);
+
 /* Bytes of caller-allocated device workspace dli_span_forward needs for chunks of up to max_tokens
  * (= batch * q_len) tokens, batch <= max_batch, context <= max_ctx. */
 size_t dli_span_workspace_bytes(const dli_span* span, int max_tokens, int max_batch, int max_ctx);
