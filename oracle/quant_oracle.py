@@ -27,7 +27,8 @@ def quantize_rowwise(w: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
     cvt.rni), zero rows mapping to scale 0."""
     w = w.float()
     absmax = w.abs().amax(dim=1)
-    inv = torch.where(absmax > 0, 127.0 / absmax, torch.zeros_like(absmax))
+    # tensor / tensor: a correctly rounded fp32 division (scalar / tensor is reciprocal-then-multiply in torch)
+    inv = torch.where(absmax > 0, torch.full_like(absmax, 127.0) / absmax, torch.zeros_like(absmax))
     q = torch.round(w * inv[:, None]).clamp_(-127, 127).to(torch.int8)
     return q, absmax / 127.0
 
