@@ -230,6 +230,9 @@ static int span_gemm_dequant(dli_span* s, const void* x, const W8Maps& w8, void*
     s->dq_maps.push_back(e);
     sm = &s->dq_maps.back();
   }
+  // the GEMM kernels request their weight tiles BEFORE the dependency wait (weights never change) -- not true of a
+  // scratch the previous launch has just filled: this one GEMM starts only when the dequantisation has completed
+  pdl_barrier_next_launch();
   return span_gemm(s, x, sm->m, out, ldo, m, n, k, epilogue, st, rope, nullptr);
 }
 
