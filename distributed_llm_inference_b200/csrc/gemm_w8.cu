@@ -5,26 +5,48 @@
 // row).  Decode is bound by the bytes of the weights, so storing them in 8 bits halves the step's HBM traffic.  This
 // kernel keeps that weight format (biased uint8 = int8 + 128, scale = absmax / 127) and the 16-bit activations of the
 // bf16 path: the int8 tile that TMA lands in shared memory is widened to bf16 -- exactly, every integer in
-// [-128, 127] is a bf16 -- by the four epilogue warps, which are idle during the main loop, into the 128B-swizzled
-// K-major layout tcgen05.mma reads; the MMA is the bf16 one (fp32 accumulators in TMEM) and the row scale is applied
-// to the accumulator in the epilogue.  There is no activation quantisation and therefore no outlier decomposition.
+// [-128, 127] is a bf16 -- by eight more warps of the CTA and handed to the tensor core THROUGH TENSOR MEMORY: each
+// converter thread owns one weight row (= one TMEM lane), reads its 32 int8 from shared memory, and tcgen05.st's the
+// 16 bf16 pairs into the A-operand slot; the MMA is the TS form of the bf16 one (A from TMEM, activations from shared
+// memory, fp32 accumulators in TMEM) and the row scale is applied to the accumulator in the epilogue.  There is no
+// activation quantisation and therefore no outlier decomposition.
 //
 // Same shape as the bf16 weight-streaming kernel (gemm_tcgen05.cu, swap-AB: 128 weight rows are the MMA-M operand,
-// the batch is MMA-N; split-K over gridDim.z; TMA producer warp, MMA warp, 4 more warps), with one more hop per stage:
-//   raw_full[s]  TMA (int8 weights + bf16 activations) -> converter warps
-//   full[s]      converter warps (bf16 weights written, fence.proxy.async) -> MMA warp
-//   empty[s]     tcgen05.commit -> TMA producer
+// the batch is MMA-N; split-K over gridDim.z; TMA producer warp, MMA warp), with one more hop per k-block:
+//   raw_full[r]   TMA (int8 weights + bf16 activations of k-block kb into raw stage r = kb mod R) -> converter warps
+//   a_full[c]     converter warps (bf16 weights in TMEM slot c = kb mod 3, tcgen05.wait::st) -> MMA warp
+//   a_empty[c]    tcgen05.commit -> converter warps;   raw_empty[r]  tcgen05.commit -> TMA producer (the activation
+//                 tile the MMA reads lives in the raw stage)
+// First cut (kept in git history): widened tiles written back to shared memory for an SS-mode MMA.  That needs a
+// fence.proxy.async per k-block, which in a main loop with a deep ring of TMA loads in flight cost ~1000 cycles per
+// k-block (per-phase counters, tests/exp_w8_timing.py) -- the kernel streamed int8 no faster than the bf16 kernel
+// streams bf16.  Tensor memory needs no proxy fence.  The raw tile uses the 64-byte TMA swizzle so that 32 lanes reading
+// 32 different 64-byte rows hit all shared-memory banks.
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
 #include <algorithm>
+#include <stdlib.h>
 
 namespace dli {
 
-constexpr int W8_THREADS = 192;
+constexpr int W8_CONVERTERS = 256;                 // 8 warps widen the int8 tile (and write the output afterwards)
+constexpr int W8_THREADS = 64 + W8_CONVERTERS;     // + TMA producer warp + MMA warp
 constexpr int W8_RAW_BYTES = BM * BK;      // 128 rows x 64 int8
 constexpr int W8_A_BYTES = BM * BK * 2;    // the same tile as bf16
-constexpr int W8_MAX_STAGES = 6;
+constexpr int W8_MAX_STAGES = 10;  // raw ring: int8 weight tile + activation tile per stage (what is in flight from HBM)
+constexpr int W8_A_SLOTS = 3;      // widened bf16 weight tiles (32 TMEM columns each) between converters and MMA warp
+constexpr int W8_A_COLS = BK / 2;  // 64 bf16 = 32 columns of bf16 pairs
+
+// D[tmem] (+)= A[tmem] * B[smem]: A = 128 lanes x 16 bf16 (8 columns of bf16 pairs), B K-major in shared memory
+__device__ __forceinline__ void w8_umma_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 
 struct W8Params {
   void* out;
@@ -34,6 +56,7 @@ struct W8Params {
   int stages;
   int up_row_offset;   // SILU epilogue: row of q / scale where up_proj starts (= n_features)
   const float* scale;  // [rows of q]
+  long long* dbg;      // W8_TIMING builds: per-phase cycle counters of CTA 0 (experiments)
 };
 
 __device__ __forceinline__ float w8_silu(float x) { return x / (1.0f + __expf(-x)); }
@@ -44,27 +67,30 @@ __device__ __forceinline__ void w8_widen4(uint32_t w, uint32_t& lo, uint32_t& hi
   const float f1 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7651)) - 8388736.0f;
   const float f2 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7652)) - 8388736.0f;
   const float f3 = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7653)) - 8388736.0f;
-  lo = pack_bf16(f0, f1);
-  hi = pack_bf16(f2, f3);
+  // integers of at most 8 significant bits: the bf16 is the upper half of the fp32, no rounding -> byte permutes
+  lo = __byte_perm(__float_as_uint(f0), __float_as_uint(f1), 0x7632);
+  hi = __byte_perm(__float_as_uint(f2), __float_as_uint(f3), 0x7632);
 }
 
 template <int BN, int EPI>
 __global__ void __launch_bounds__(W8_THREADS, 2)
 gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant__ CUtensorMap tma_x, const W8Params p) {
   constexpr int B_TILE_BYTES = BN * BK * 2;
-  constexpr int STAGE_BYTES = W8_A_BYTES + B_TILE_BYTES + W8_RAW_BYTES;
-  constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
+  constexpr int STAGE_BYTES = B_TILE_BYTES + W8_RAW_BYTES;   // raw stage: activation tile (1024-aligned), then int8 weights
+  constexpr int ACC_COLS = BN < 32 ? 32 : BN;
+  constexpr int TMEM_COLS = ACC_COLS + W8_A_SLOTS * W8_A_COLS <= 128 ? 128 : 256;   // power of two
   constexpr bool SILU = EPI == DLI_EPI_SILU_MUL_BF16;
 
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t bars[3 * W8_MAX_STAGES + 1];
+  __shared__ uint64_t bars[2 * W8_MAX_STAGES + 2 * W8_A_SLOTS + 1];
   __shared__ uint32_t tmem_base_slot;
 
-  const uint32_t tiles = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t tiles = (smem_u32(smem_raw) + 1023u) & ~1023u;      // the raw ring
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int stages = p.stages;
-  const uint32_t raw_full0 = smem_u32(&bars[0]), full0 = smem_u32(&bars[W8_MAX_STAGES]),
-                 empty0 = smem_u32(&bars[2 * W8_MAX_STAGES]), tmem_full = smem_u32(&bars[3 * W8_MAX_STAGES]);
+  const uint32_t raw_full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[W8_MAX_STAGES]),
+                 a_full0 = smem_u32(&bars[2 * W8_MAX_STAGES]), a_empty0 = smem_u32(&bars[2 * W8_MAX_STAGES + W8_A_SLOTS]),
+                 tmem_full = smem_u32(&bars[2 * W8_MAX_STAGES + 2 * W8_A_SLOTS]);
 
   const int kb0 = blockIdx.z * p.kb_per_split;
   const int kb1 = min(kb0 + p.kb_per_split, p.k_blocks);
@@ -77,8 +103,11 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_x) : "memory");
     for (int s = 0; s < stages; ++s) {
       mbar_init(raw_full0 + 8 * s, 1);
-      mbar_init(full0 + 8 * s, 1);
       mbar_init(empty0 + 8 * s, 1);
+    }
+    for (int c = 0; c < W8_A_SLOTS; ++c) {
+      mbar_init(a_full0 + 8 * c, W8_CONVERTERS / 32);   // one arrival per converter warp
+      mbar_init(a_empty0 + 8 * c, 1);
     }
     mbar_init(tmem_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -99,7 +128,7 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
       // ===== TMA producer: int8 weight tiles (before the dependency wait: weights never depend on the predecessor)
       //       and the activation tiles (after it) =====
       auto load_weights = [&](int s, int kb) {
-        const uint32_t raw = tiles + s * STAGE_BYTES + W8_A_BYTES + B_TILE_BYTES;
+        const uint32_t raw = tiles + s * STAGE_BYTES + B_TILE_BYTES;
         if (SILU) {  // 64 gate rows + 64 up rows of the same 64 features
           tma_load_2d(raw, &tma_w, raw_full0 + 8 * s, kb * BK, a_row0);
           tma_load_2d(raw + W8_RAW_BYTES / 2, &tma_w, raw_full0 + 8 * s, kb * BK, p.up_row_offset + a_row0);
@@ -108,7 +137,7 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
         }
       };
       auto load_acts = [&](int s, int kb) {
-        tma_load_2d(tiles + s * STAGE_BYTES + W8_A_BYTES, &tma_x, raw_full0 + 8 * s, kb * BK, b_row0);
+        tma_load_2d(tiles + s * STAGE_BYTES, &tma_x, raw_full0 + 8 * s, kb * BK, b_row0);
       };
       const int n_pre = min(stages, kb1 - kb0);
       if (elect_one()) {
@@ -138,76 +167,98 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
     } else if (warp == 1) {
       // ===== MMA issuer =====
       constexpr uint32_t idesc = umma_idesc_bf16(BN);
-      int s = 0;
-      uint32_t ph = 0;
+      int s = 0, c = 0;
+      uint32_t cph = 0;
       for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(full0 + 8 * s, ph);
+        mbar_wait(a_full0 + 8 * c, cph);   // the converters passed raw_full[s] before arriving: the activation tile is there too
         tcgen05_fence_after();
         if (elect_one()) {
-          const uint32_t a_src = tiles + s * STAGE_BYTES;
-          const uint64_t adesc = umma_desc_sw128(a_src), bdesc = umma_desc_sw128(a_src + W8_A_BYTES);
+          const uint32_t tmem_a = tmem_d + ACC_COLS + c * W8_A_COLS;
+          const uint64_t bdesc = umma_desc_sw128(tiles + s * STAGE_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k)
-            umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-          umma_commit(empty0 + 8 * s);
+            w8_umma_ts(tmem_d, tmem_a + 8 * k, bdesc + 2 * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          umma_commit(a_empty0 + 8 * c);   // the TMEM slot may be overwritten
+          umma_commit(empty0 + 8 * s);     // the raw stage (its activation tile) may be refilled
           if (kb + 1 == kb1) umma_commit(tmem_full);
         }
         __syncwarp();
-        if (++s == stages) { s = 0; ph ^= 1; }
+        if (++s == stages) s = 0;
+        if (++c == W8_A_SLOTS) { c = 0; cph ^= 1; }
       }
     } else {
       // ===== converters (main loop), then epilogue =====
-      const int e = threadIdx.x - 64;  // 0..127
+      const int e = threadIdx.x - 64;  // 0..255
+      const int q = warp & 3;                // TMEM lane quarter this warp may access: weight rows 32 q .. 32 q + 31
+      const int half = (warp - 2) >> 2;      // two warps share a quarter: k 0..31 and k 32..63 of the k-block
       {
-        int s = 0;
-        uint32_t ph = 0;
+        // this thread's row of the raw tile ([128 rows][64 B], 64-byte TMA swizzle: chunk ^= (row >> 1) & 3)
+        const int r = q * 32 + lane;
+        const uint32_t src0 = B_TILE_BYTES + r * BK + (((2 * half) ^ ((r >> 1) & 3)) << 4);
+        const uint32_t src1 = B_TILE_BYTES + r * BK + (((2 * half + 1) ^ ((r >> 1) & 3)) << 4);
+        const uint32_t t_lane = tmem_d + ((uint32_t)(q * 32) << 16) + ACC_COLS + half * 16;
+        int s = 0, c = 0;
+        uint32_t ph = 0, cph = 0;
+#ifdef W8_TIMING
+        long long t_raw = 0, t_slot = 0, t_conv = 0, t_sync = 0, t0 = clock64(), t1;
+#define W8_T(acc) do { t1 = clock64(); acc += t1 - t0; t0 = t1; } while (0)
+#else
+#define W8_T(acc) ((void)0)
+#endif
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(raw_full0 + 8 * s, ph);
-          const uint32_t a_dst = tiles + s * STAGE_BYTES;
-          const uint32_t raw = a_dst + W8_A_BYTES + B_TILE_BYTES;
+          W8_T(t_raw);
+          const uint32_t raw_stage = tiles + s * STAGE_BYTES;
+          uint32_t w[8];
+          asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(raw_stage + src0));
+          asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "r"(raw_stage + src1));
+          uint32_t o[16];
+#ifndef W8_EXP_NOCONVERT   // experiment build: skip the widening (garbage results) to time the rest alone
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int id = i * 128 + e;           // 16-byte chunk of the raw tile: consecutive threads, consecutive chunks
-            const int r = id >> 2, c = id & 3;    // row, chunk of 16 int8
-            uint32_t w0, w1, w2, w3;
-            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "r"(raw + r * BK + c * 16));
-            uint32_t o[8];
-            w8_widen4(w0, o[0], o[1]);
-            w8_widen4(w1, o[2], o[3]);
-            w8_widen4(w2, o[4], o[5]);
-            w8_widen4(w3, o[6], o[7]);
-            // bf16 row r: 8 chunks of 8 elements, 128B swizzle: chunk index XOR (row mod 8); 8-row groups 1024 B apart
-            const uint32_t row_base = a_dst + (r >> 3) * 1024 + (r & 7) * 128;
-            const uint32_t d0 = row_base + (((2 * c) ^ (r & 7)) << 4), d1 = row_base + (((2 * c + 1) ^ (r & 7)) << 4);
-            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(d0), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
-            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(d1), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7]) : "memory");
-          }
-          fence_proxy_async_smem();                       // generic-proxy stores -> visible to the tensor core's reads
-          asm volatile("bar.sync 1, 128;" ::: "memory");  // the four converter warps only
-          if (e == 0) mbar_arrive(full0 + 8 * s);
+          for (int i = 0; i < 8; ++i) w8_widen4(w[i], o[2 * i], o[2 * i + 1]);
+#else
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { o[2 * i] = w[i]; o[2 * i + 1] = w[i]; }
+#endif
+          mbar_wait(a_empty0 + 8 * c, cph ^ 1);   // the MMAs that last read this TMEM slot have completed
+          tcgen05_fence_after();
+          W8_T(t_slot);
+          tmem_st16(t_lane + c * W8_A_COLS, o);
+          tmem_st_wait();
+          W8_T(t_conv);
+          tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(a_full0 + 8 * c);    // the slot is full when all eight warps have arrived
+          W8_T(t_sync);
           if (++s == stages) { s = 0; ph ^= 1; }
+          if (++c == W8_A_SLOTS) { c = 0; cph ^= 1; }
         }
+#ifdef W8_TIMING
+        if (p.dbg && blockIdx.x == 7 && blockIdx.y == 0 && blockIdx.z == 0 && (e == 0 || e == 224)) {
+          long long* d = p.dbg + (e ? 8 : 0);
+          d[0] = t_raw; d[1] = t_slot; d[2] = t_conv; d[3] = t_sync; d[4] = kb1 - kb0;
+        }
+#endif
       }
       pdl_wait();  // the output buffers belong to the predecessor until it has completed
       mbar_wait(tmem_full, 0, 50);
       tcgen05_fence_after();
-      const int q = warp & 3;
-      const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16);
+      const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16);   // the two warps of a quarter split the accumulator columns
       uint32_t v[16];
       // lane = feature, column = token: transposed through the (now idle) operand ring so that global traffic is
       // 128-bit and coalesced along the feature axis
-      float* stage_f = reinterpret_cast<float*>(smem_raw + (tiles - smem_u32(smem_raw)));  // [BN tokens][128 lanes]
+      float* stage_f = reinterpret_cast<float*>(smem_raw + (tiles - smem_u32(smem_raw)));  // [BN tokens][128 lanes] over the idle raw ring
       const int lane_row = q * 32 + lane;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 16) {
+      for (int c0 = half * 16; c0 < BN; c0 += 32) {
         tmem_ld16(taddr + c0, v);
         tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 16; ++j) stage_f[(c0 + j) * BM + lane_row] = __uint_as_float(v[j]);
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       if (SILU) {
-        for (int idx = e; idx < BN * 16; idx += 128) {
+        for (int idx = e; idx < BN * 16; idx += W8_CONVERTERS) {
           const int t = idx >> 4, f = (idx & 15) * 4;
           const int tok = b_row0 + t, feat = a_row0 + f;
           if (tok < p.m_tokens && feat < p.n_features) {
@@ -232,7 +283,7 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
           }
         }
       } else {
-        for (int idx = e; idx < BN * 32; idx += 128) {
+        for (int idx = e; idx < BN * 32; idx += W8_CONVERTERS) {
           const int t = idx >> 5, f = (idx & 31) * 4;
           const int tok = b_row0 + t, feat = a_row0 + f;
           if (tok < p.m_tokens && feat < p.n_features) {
@@ -277,7 +328,7 @@ typedef CUresult (*EncodeTiledFnW8)(CUtensorMap*, CUtensorMapDataType, cuuint32_
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-// 2-D uint8 tensor [rows, cols]; box = [box_rows, 64 bytes], no swizzle (the converter warps read it with plain loads)
+// 2-D uint8 tensor [rows, cols]; box = [box_rows, 64 bytes], 64-byte swizzle (the converter warps read one row per lane)
 int make_tmap_u8(CUtensorMap* map, const void* base, long long rows, long long cols, int box_rows) {
   static EncodeTiledFnW8 fn = nullptr;
   if (!fn) {
@@ -295,7 +346,7 @@ int make_tmap_u8(CUtensorMap* map, const void* base, long long rows, long long c
   cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(DLI_ERR_CUDA, "cuTensorMapEncodeTiled (uint8) failed with CUresult %d", (int)r);
   return DLI_OK;
@@ -303,7 +354,7 @@ int make_tmap_u8(CUtensorMap* map, const void* base, long long rows, long long c
 
 template <int BN, int EPI>
 static int launch_w8_variant(const CUtensorMap& tw, const CUtensorMap& tx, const W8Params& p, dim3 grid, cudaStream_t st) {
-  constexpr int STAGE_BYTES = W8_A_BYTES + BN * BK * 2 + W8_RAW_BYTES;
+  constexpr int STAGE_BYTES = BN * BK * 2 + W8_RAW_BYTES;
   const size_t smem = (size_t)p.stages * STAGE_BYTES + 1024;
   auto kern = gemm_w8_kernel<BN, EPI>;
   DLI_ONCE_PER_DEVICE(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
@@ -333,10 +384,17 @@ int launch_gemm_w8_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const C
   p.n_features = n;
   p.k_blocks = g.k_blocks;
   p.kb_per_split = g.kb_per_split;
-  const int stage_bytes = W8_A_BYTES + g.bn * BK * 2 + W8_RAW_BYTES;
-  p.stages = std::max(2, std::min(std::min(W8_MAX_STAGES, (112 * 1024 - 2048) / stage_bytes), g.kb_per_split));
+  const int stage_bytes = g.bn * BK * 2 + W8_RAW_BYTES;
+  // two CTAs per SM: raw ring <= ~111 KB; the epilogue's transposition buffer (bn x 512 B) overlays it
+  int stages = std::min(W8_MAX_STAGES, (112 * 1024 - 2048) / stage_bytes);
+  while (stages * stage_bytes < g.bn * 512) ++stages;
+  p.stages = std::max(2, stages);
   p.up_row_offset = n;
   p.scale = scale;
+  p.dbg = nullptr;
+#ifdef W8_TIMING
+  if (const char* e = getenv("DLI_W8_DBG_PTR")) p.dbg = reinterpret_cast<long long*>(strtoull(e, nullptr, 16));
+#endif
   dim3 grid(g.grid_x, g.grid_y, g.splits);
   switch (g.bn) {
     case 16: return launch_w8_epi<16>(epilogue, tmap_w, tmap_x, p, grid, st);

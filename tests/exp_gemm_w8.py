@@ -1,0 +1,44 @@
+"""Experiment (not a test): weight-streaming rate of the int8-weight decode GEMM (dli_gemm_w8) next to the bf16 one."""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+from distributed_llm_inference_b200 import _ffi
+from tests import gpu_ops as ops
+
+dev = "cuda"
+M = int(os.environ.get("EXP_M", "16"))
+shapes = [(12288, 4096), (4096, 4096), (4096, 11008)]
+only_w8 = bool(os.environ.get("EXP_ONLY_W8"))
+for (n, k) in shapes:
+    nbuf = max(2, int(400e6 // (n * k)) + 1)
+    x = torch.randn(M, k, device=dev, dtype=torch.bfloat16)
+    out = torch.zeros(M, n, device=dev, dtype=torch.float32)
+    qs = [torch.randint(0, 256, (n, k), device=dev, dtype=torch.uint8) for _ in range(nbuf)]
+    sc = torch.rand(n, device=dev) * 1e-3
+
+    def run_w8():
+        for q in qs:
+            _ffi.check(_ffi.lib.dli_gemm_w8(x.data_ptr(), k, q.data_ptr(), sc.data_ptr(), out.data_ptr(), n, M, n, k,
+                                            _ffi.EPI_ADD_F32, ops.stream()))
+
+    def timeit(fn, reps=6):
+        fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) * 1e3 / (reps * nbuf)
+
+    us8 = timeit(run_w8)
+    line = f"m={M} n={n:6d} k={k:6d} int8 {n*k/1e6:6.1f} MB {us8:7.2f} us {n*k/us8/1e3:7.1f} GB/s"
+    if not only_w8:
+        ws = [torch.randn(n, k, device=dev, dtype=torch.bfloat16) for _ in range(nbuf)]
+        us16 = timeit(lambda: [ops.gemm(x, w, _ffi.EPI_ADD_F32, out=out) for w in ws])
+        line += f" | bf16 {us16:7.2f} us {n*k*2/us16/1e3:7.1f} GB/s | speed-up {us16/us8:.2f}"
+        del ws
+    print(line, flush=True)
+    del qs
