@@ -14,14 +14,16 @@
 // Same shape as the bf16 weight-streaming kernel (gemm_tcgen05.cu, swap-AB: 128 weight rows are the MMA-M operand,
 // the batch is MMA-N; split-K over gridDim.z; TMA producer warp, MMA warp), with one more hop per k-block:
 //   raw_full[r]   TMA (int8 weights + bf16 activations of k-block kb into raw stage r = kb mod R) -> converter warps
-//   a_full[c]     converter warps (bf16 weights in TMEM slot c = kb mod 3, tcgen05.wait::st) -> MMA warp
+//   a_full[c]     converter warps (bf16 weights in TMEM slot c = kb mod 4, tcgen05.wait::st) -> MMA warp
 //   a_empty[c]    tcgen05.commit -> converter warps;   raw_empty[r]  tcgen05.commit -> TMA producer (the activation
 //                 tile the MMA reads lives in the raw stage)
 // First cut (kept in git history): widened tiles written back to shared memory for an SS-mode MMA.  That needs a
 // fence.proxy.async per k-block, which in a main loop with a deep ring of TMA loads in flight cost ~1000 cycles per
 // k-block (per-phase counters, tests/exp_w8_timing.py) -- the kernel streamed int8 no faster than the bf16 kernel
-// streams bf16.  Tensor memory needs no proxy fence.  The raw tile uses the 64-byte TMA swizzle so that 32 lanes reading
-// 32 different 64-byte rows hit all shared-memory banks.
+// streams bf16.  Tensor memory needs no proxy fence.  The raw tile uses the 128-byte TMA swizzle so that 32 lanes reading
+// 32 different rows hit all shared-memory banks.  A raw stage covers two k-blocks (128 int8 per row): with 64-byte rows the
+// kernel was bound by the NUMBER of row requests TMA issues, not by bytes (converters waited ~1470 cycles per k-block for
+// data while the widening took 200), i.e. it streamed int8 rows no faster than the bf16 kernel streams bf16 rows.
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
@@ -32,10 +34,10 @@ namespace dli {
 
 constexpr int W8_CONVERTERS = 256;                 // 8 warps widen the int8 tile (and write the output afterwards)
 constexpr int W8_THREADS = 64 + W8_CONVERTERS;     // + TMA producer warp + MMA warp
-constexpr int W8_RAW_BYTES = BM * BK;      // 128 rows x 64 int8
-constexpr int W8_A_BYTES = BM * BK * 2;    // the same tile as bf16
-constexpr int W8_MAX_STAGES = 10;  // raw ring: int8 weight tile + activation tile per stage (what is in flight from HBM)
-constexpr int W8_A_SLOTS = 3;      // widened bf16 weight tiles (32 TMEM columns each) between converters and MMA warp
+constexpr int W8_RAW_K = 2 * BK;           // a raw stage holds TWO k-blocks: 128-byte rows, like the bf16 kernel's TMA rows
+constexpr int W8_RAW_BYTES = BM * W8_RAW_K;  // 128 rows x 128 int8
+constexpr int W8_MAX_STAGES = 5;   // raw ring: int8 weight tile + two activation tiles per stage (what is in flight from HBM)
+constexpr int W8_A_SLOTS = 4;      // widened bf16 weight tiles (32 TMEM columns each) between converters and MMA warp
 constexpr int W8_A_COLS = BK / 2;  // 64 bf16 = 32 columns of bf16 pairs
 
 // D[tmem] (+)= A[tmem] * B[smem]: A = 128 lanes x 16 bf16 (8 columns of bf16 pairs), B K-major in shared memory
@@ -76,9 +78,9 @@ template <int BN, int EPI>
 __global__ void __launch_bounds__(W8_THREADS, 2)
 gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant__ CUtensorMap tma_x, const W8Params p) {
   constexpr int B_TILE_BYTES = BN * BK * 2;
-  constexpr int STAGE_BYTES = B_TILE_BYTES + W8_RAW_BYTES;   // raw stage: activation tile (1024-aligned), then int8 weights
+  constexpr int STAGE_BYTES = 2 * B_TILE_BYTES + W8_RAW_BYTES;   // raw stage: two activation tiles (1024-aligned), then int8 weights
   constexpr int ACC_COLS = BN < 32 ? 32 : BN;
-  constexpr int TMEM_COLS = ACC_COLS + W8_A_SLOTS * W8_A_COLS <= 128 ? 128 : 256;   // power of two
+  constexpr int TMEM_COLS = 256;   // accumulator + 4 x 32 columns of widened weights, rounded up to a power of two
   constexpr bool SILU = EPI == DLI_EPI_SILU_MUL_BF16;
 
   extern __shared__ uint8_t smem_raw[];
@@ -92,8 +94,9 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
                  a_full0 = smem_u32(&bars[2 * W8_MAX_STAGES]), a_empty0 = smem_u32(&bars[2 * W8_MAX_STAGES + W8_A_SLOTS]),
                  tmem_full = smem_u32(&bars[2 * W8_MAX_STAGES + 2 * W8_A_SLOTS]);
 
-  const int kb0 = blockIdx.z * p.kb_per_split;
+  const int kb0 = blockIdx.z * p.kb_per_split;   // kb_per_split is even: a raw stage is a PAIR of k-blocks
   const int kb1 = min(kb0 + p.kb_per_split, p.k_blocks);
+  const int kp0 = kb0 >> 1, kp1 = (kb1 + 1) >> 1;   // an odd tail reads zeros (TMA out-of-bounds fill) against zero activations
   const int a_row0 = blockIdx.x * (SILU ? BM / 2 : BM);
   const int b_row0 = blockIdx.y * BN;
 
@@ -127,39 +130,40 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
     if (warp == 0) {
       // ===== TMA producer: int8 weight tiles (before the dependency wait: weights never depend on the predecessor)
       //       and the activation tiles (after it) =====
-      auto load_weights = [&](int s, int kb) {
-        const uint32_t raw = tiles + s * STAGE_BYTES + B_TILE_BYTES;
+      auto load_weights = [&](int s, int kp) {
+        const uint32_t raw = tiles + s * STAGE_BYTES + 2 * B_TILE_BYTES;
         if (SILU) {  // 64 gate rows + 64 up rows of the same 64 features
-          tma_load_2d(raw, &tma_w, raw_full0 + 8 * s, kb * BK, a_row0);
-          tma_load_2d(raw + W8_RAW_BYTES / 2, &tma_w, raw_full0 + 8 * s, kb * BK, p.up_row_offset + a_row0);
+          tma_load_2d(raw, &tma_w, raw_full0 + 8 * s, kp * W8_RAW_K, a_row0);
+          tma_load_2d(raw + W8_RAW_BYTES / 2, &tma_w, raw_full0 + 8 * s, kp * W8_RAW_K, p.up_row_offset + a_row0);
         } else {
-          tma_load_2d(raw, &tma_w, raw_full0 + 8 * s, kb * BK, a_row0);
+          tma_load_2d(raw, &tma_w, raw_full0 + 8 * s, kp * W8_RAW_K, a_row0);
         }
       };
-      auto load_acts = [&](int s, int kb) {
-        tma_load_2d(tiles + s * STAGE_BYTES, &tma_x, raw_full0 + 8 * s, kb * BK, b_row0);
+      auto load_acts = [&](int s, int kp) {
+        tma_load_2d(tiles + s * STAGE_BYTES, &tma_x, raw_full0 + 8 * s, (2 * kp) * BK, b_row0);
+        tma_load_2d(tiles + s * STAGE_BYTES + B_TILE_BYTES, &tma_x, raw_full0 + 8 * s, (2 * kp + 1) * BK, b_row0);
       };
-      const int n_pre = min(stages, kb1 - kb0);
+      const int n_pre = min(stages, kp1 - kp0);
       if (elect_one()) {
         for (int i = 0; i < n_pre; ++i) {
-          mbar_expect_tx(raw_full0 + 8 * i, W8_RAW_BYTES + B_TILE_BYTES);
-          load_weights(i, kb0 + i);
+          mbar_expect_tx(raw_full0 + 8 * i, W8_RAW_BYTES + 2 * B_TILE_BYTES);
+          load_weights(i, kp0 + i);
         }
       }
       __syncwarp();
       pdl_wait();
       if (elect_one()) {
-        for (int i = 0; i < n_pre; ++i) load_acts(i, kb0 + i);
+        for (int i = 0; i < n_pre; ++i) load_acts(i, kp0 + i);
       }
       __syncwarp();
       int s = n_pre == stages ? 0 : n_pre;
       uint32_t ph = n_pre == stages ? 1 : 0;
-      for (int kb = kb0 + n_pre; kb < kb1; ++kb) {
+      for (int kp = kp0 + n_pre; kp < kp1; ++kp) {
         mbar_wait(empty0 + 8 * s, ph ^ 1);
         if (elect_one()) {
-          mbar_expect_tx(raw_full0 + 8 * s, W8_RAW_BYTES + B_TILE_BYTES);
-          load_weights(s, kb);
-          load_acts(s, kb);
+          mbar_expect_tx(raw_full0 + 8 * s, W8_RAW_BYTES + 2 * B_TILE_BYTES);
+          load_weights(s, kp);
+          load_acts(s, kp);
         }
         __syncwarp();
         if (++s == stages) { s = 0; ph ^= 1; }
@@ -169,22 +173,27 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
       constexpr uint32_t idesc = umma_idesc_bf16(BN);
       int s = 0, c = 0;
       uint32_t cph = 0;
-      for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(a_full0 + 8 * c, cph);   // the converters passed raw_full[s] before arriving: the activation tile is there too
-        tcgen05_fence_after();
-        if (elect_one()) {
-          const uint32_t tmem_a = tmem_d + ACC_COLS + c * W8_A_COLS;
-          const uint64_t bdesc = umma_desc_sw128(tiles + s * STAGE_BYTES);
+      for (int kp = kp0; kp < kp1; ++kp) {
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k)
-            w8_umma_ts(tmem_d, tmem_a + 8 * k, bdesc + 2 * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-          umma_commit(a_empty0 + 8 * c);   // the TMEM slot may be overwritten
-          umma_commit(empty0 + 8 * s);     // the raw stage (its activation tile) may be refilled
-          if (kb + 1 == kb1) umma_commit(tmem_full);
+        for (int j = 0; j < 2; ++j) {        // the two k-blocks of the raw stage
+          mbar_wait(a_full0 + 8 * c, cph);   // the converters passed raw_full[s] before arriving: the activation tiles are there too
+          tcgen05_fence_after();
+          if (elect_one()) {
+            const uint32_t tmem_a = tmem_d + ACC_COLS + c * W8_A_COLS;
+            const uint64_t bdesc = umma_desc_sw128(tiles + s * STAGE_BYTES + j * B_TILE_BYTES);
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              w8_umma_ts(tmem_d, tmem_a + 8 * k, bdesc + 2 * k, idesc, (kp > kp0 || j > 0 || k > 0) ? 1u : 0u);
+            umma_commit(a_empty0 + 8 * c);   // the TMEM slot may be overwritten
+            if (j == 1) {
+              umma_commit(empty0 + 8 * s);   // the raw stage (its activation tiles) may be refilled
+              if (kp + 1 == kp1) umma_commit(tmem_full);
+            }
+          }
+          __syncwarp();
+          if (++c == W8_A_SLOTS) { c = 0; cph ^= 1; }
         }
-        __syncwarp();
         if (++s == stages) s = 0;
-        if (++c == W8_A_SLOTS) { c = 0; cph ^= 1; }
       }
     } else {
       // ===== converters (main loop), then epilogue =====
@@ -192,10 +201,15 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
       const int q = warp & 3;                // TMEM lane quarter this warp may access: weight rows 32 q .. 32 q + 31
       const int half = (warp - 2) >> 2;      // two warps share a quarter: k 0..31 and k 32..63 of the k-block
       {
-        // this thread's row of the raw tile ([128 rows][64 B], 64-byte TMA swizzle: chunk ^= (row >> 1) & 3)
+        // this thread's row of the raw tile ([128 rows][128 B], 128-byte TMA swizzle: 16-byte chunk ^= row & 7): of each of
+        // the stage's two k-blocks j it widens int8 32 half .. 32 half + 31, i.e. chunks 4 j + 2 half and 4 j + 2 half + 1
         const int r = q * 32 + lane;
-        const uint32_t src0 = B_TILE_BYTES + r * BK + (((2 * half) ^ ((r >> 1) & 3)) << 4);
-        const uint32_t src1 = B_TILE_BYTES + r * BK + (((2 * half + 1) ^ ((r >> 1) & 3)) << 4);
+        uint32_t src[2][2];
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+          for (int i = 0; i < 2; ++i)
+            src[j][i] = 2 * B_TILE_BYTES + r * W8_RAW_K + (((4 * j + 2 * half + i) ^ (r & 7)) << 4);
         const uint32_t t_lane = tmem_d + ((uint32_t)(q * 32) << 16) + ACC_COLS + half * 16;
         int s = 0, c = 0;
         uint32_t ph = 0, cph = 0;
@@ -205,38 +219,45 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
 #else
 #define W8_T(acc) ((void)0)
 #endif
-        for (int kb = kb0; kb < kb1; ++kb) {
+        for (int kp = kp0; kp < kp1; ++kp) {
           mbar_wait(raw_full0 + 8 * s, ph);
           W8_T(t_raw);
           const uint32_t raw_stage = tiles + s * STAGE_BYTES;
-          uint32_t w[8];
-          asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(raw_stage + src0));
-          asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "r"(raw_stage + src1));
-          uint32_t o[16];
+          uint32_t w[2][8];
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]) : "r"(raw_stage + src[j][0]));
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7]) : "r"(raw_stage + src[j][1]));
+          }
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            uint32_t o[16];
 #ifndef W8_EXP_NOCONVERT   // experiment build: skip the widening (garbage results) to time the rest alone
 #pragma unroll
-          for (int i = 0; i < 8; ++i) w8_widen4(w[i], o[2 * i], o[2 * i + 1]);
+            for (int i = 0; i < 8; ++i) w8_widen4(w[j][i], o[2 * i], o[2 * i + 1]);
 #else
 #pragma unroll
-          for (int i = 0; i < 8; ++i) { o[2 * i] = w[i]; o[2 * i + 1] = w[i]; }
+            for (int i = 0; i < 8; ++i) { o[2 * i] = w[j][i]; o[2 * i + 1] = w[j][i]; }
 #endif
-          mbar_wait(a_empty0 + 8 * c, cph ^ 1);   // the MMAs that last read this TMEM slot have completed
-          tcgen05_fence_after();
-          W8_T(t_slot);
-          tmem_st16(t_lane + c * W8_A_COLS, o);
-          tmem_st_wait();
-          W8_T(t_conv);
-          tcgen05_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(a_full0 + 8 * c);    // the slot is full when all eight warps have arrived
-          W8_T(t_sync);
+            W8_T(t_conv);
+            mbar_wait(a_empty0 + 8 * c, cph ^ 1);   // the MMAs that last read this TMEM slot have completed
+            tcgen05_fence_after();
+            W8_T(t_slot);
+            tmem_st16(t_lane + c * W8_A_COLS, o);
+            tmem_st_wait();
+            W8_T(t_conv);
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(a_full0 + 8 * c);    // the slot is full when all eight warps have arrived
+            W8_T(t_sync);
+            if (++c == W8_A_SLOTS) { c = 0; cph ^= 1; }
+          }
           if (++s == stages) { s = 0; ph ^= 1; }
-          if (++c == W8_A_SLOTS) { c = 0; cph ^= 1; }
         }
 #ifdef W8_TIMING
         if (p.dbg && blockIdx.x == 7 && blockIdx.y == 0 && blockIdx.z == 0 && (e == 0 || e == 224)) {
           long long* d = p.dbg + (e ? 8 : 0);
-          d[0] = t_raw; d[1] = t_slot; d[2] = t_conv; d[3] = t_sync; d[4] = kb1 - kb0;
+          d[0] = t_raw; d[1] = t_slot; d[2] = t_conv; d[3] = t_sync; d[4] = kb1 - kb0;   // per k-block figures = sums / this
         }
 #endif
       }
@@ -328,7 +349,7 @@ typedef CUresult (*EncodeTiledFnW8)(CUtensorMap*, CUtensorMapDataType, cuuint32_
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-// 2-D uint8 tensor [rows, cols]; box = [box_rows, 64 bytes], 64-byte swizzle (the converter warps read one row per lane)
+// 2-D uint8 tensor [rows, cols]; box = [box_rows, 128 bytes], 128-byte swizzle (the converter warps read one row per lane)
 int make_tmap_u8(CUtensorMap* map, const void* base, long long rows, long long cols, int box_rows) {
   static EncodeTiledFnW8 fn = nullptr;
   if (!fn) {
@@ -343,10 +364,10 @@ int make_tmap_u8(CUtensorMap* map, const void* base, long long rows, long long c
     return fail(DLI_ERR_ARG, "int8 TMA operand needs a 16-byte aligned base and a row length that is a multiple of 16");
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)cols};
-  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t box[2] = {(cuuint32_t)W8_RAW_K, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(DLI_ERR_CUDA, "cuTensorMapEncodeTiled (uint8) failed with CUresult %d", (int)r);
   return DLI_OK;
@@ -354,7 +375,7 @@ int make_tmap_u8(CUtensorMap* map, const void* base, long long rows, long long c
 
 template <int BN, int EPI>
 static int launch_w8_variant(const CUtensorMap& tw, const CUtensorMap& tx, const W8Params& p, dim3 grid, cudaStream_t st) {
-  constexpr int STAGE_BYTES = BN * BK * 2 + W8_RAW_BYTES;
+  constexpr int STAGE_BYTES = 2 * BN * BK * 2 + W8_RAW_BYTES;
   const size_t smem = (size_t)p.stages * STAGE_BYTES + 1024;
   auto kern = gemm_w8_kernel<BN, EPI>;
   DLI_ONCE_PER_DEVICE(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
@@ -383,8 +404,9 @@ int launch_gemm_w8_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const C
   p.m_tokens = m;
   p.n_features = n;
   p.k_blocks = g.k_blocks;
-  p.kb_per_split = g.kb_per_split;
-  const int stage_bytes = g.bn * BK * 2 + W8_RAW_BYTES;
+  p.kb_per_split = (g.kb_per_split + 1) & ~1;   // whole pairs of k-blocks per split
+  const int splits = (g.k_blocks + p.kb_per_split - 1) / p.kb_per_split;
+  const int stage_bytes = 2 * g.bn * BK * 2 + W8_RAW_BYTES;
   // two CTAs per SM: raw ring <= ~111 KB; the epilogue's transposition buffer (bn x 512 B) overlays it
   int stages = std::min(W8_MAX_STAGES, (112 * 1024 - 2048) / stage_bytes);
   while (stages * stage_bytes < g.bn * 512) ++stages;
@@ -395,7 +417,7 @@ int launch_gemm_w8_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const C
 #ifdef W8_TIMING
   if (const char* e = getenv("DLI_W8_DBG_PTR")) p.dbg = reinterpret_cast<long long*>(strtoull(e, nullptr, 16));
 #endif
-  dim3 grid(g.grid_x, g.grid_y, g.splits);
+  dim3 grid(g.grid_x, g.grid_y, splits);
   switch (g.bn) {
     case 16: return launch_w8_epi<16>(epilogue, tmap_w, tmap_x, p, grid, st);
     case 32: return launch_w8_epi<32>(epilogue, tmap_w, tmap_x, p, grid, st);
