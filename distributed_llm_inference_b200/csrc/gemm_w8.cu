@@ -32,8 +32,10 @@
 
 namespace dli {
 
-constexpr int W8_CONVERTERS = 256;                 // 8 warps widen the int8 tile (and write the output afterwards)
-constexpr int W8_THREADS = 64 + W8_CONVERTERS;     // + TMA producer warp + MMA warp
+// NCW = 8 or 16 converter warps widen the int8 tiles (and write the output afterwards), + TMA producer warp + MMA warp.
+// A CTA walks its k-blocks one after the other and the widening of a k-block is a dependent chain per thread, so a grid
+// with few, long CTAs (gate|up: one CTA per 64 features, never split, all of K) is bound by that chain: it gets 16 warps,
+// each thread a quarter of a row per k-block instead of half.
 constexpr int W8_RAW_K = 2 * BK;           // a raw stage holds TWO k-blocks: 128-byte rows, like the bf16 kernel's TMA rows
 constexpr int W8_RAW_BYTES = BM * W8_RAW_K;  // 128 rows x 128 int8
 constexpr int W8_MAX_STAGES = 5;   // raw ring: int8 weight tile + two activation tiles per stage (what is in flight from HBM)
@@ -74,14 +76,23 @@ __device__ __forceinline__ void w8_widen4(uint32_t w, uint32_t& lo, uint32_t& hi
   hi = __byte_perm(__float_as_uint(f2), __float_as_uint(f3), 0x7632);
 }
 
-template <int BN, int EPI>
-__global__ void __launch_bounds__(W8_THREADS, 2)
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
+
+template <int BN, int EPI, int NCW>
+__global__ void __launch_bounds__(64 + 32 * NCW, 2)
 gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant__ CUtensorMap tma_x, const W8Params p) {
   constexpr int B_TILE_BYTES = BN * BK * 2;
   constexpr int STAGE_BYTES = 2 * B_TILE_BYTES + W8_RAW_BYTES;   // raw stage: two activation tiles (1024-aligned), then int8 weights
   constexpr int ACC_COLS = BN < 32 ? 32 : BN;
   constexpr int TMEM_COLS = 256;   // accumulator + 4 x 32 columns of widened weights, rounded up to a power of two
   constexpr bool SILU = EPI == DLI_EPI_SILU_MUL_BF16;
+  constexpr int W8_CONVERTERS = 32 * NCW;
+  constexpr int KPARTS = NCW / 4;            // warps that share a TMEM lane quarter split the k-block's 64 columns
+  constexpr int CHUNKS = 4 / KPARTS;         // 16-byte chunks (16 int8) per thread and k-block: 2 or 1
 
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t bars[2 * W8_MAX_STAGES + 2 * W8_A_SLOTS + 1];
@@ -109,7 +120,7 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
       mbar_init(empty0 + 8 * s, 1);
     }
     for (int c = 0; c < W8_A_SLOTS; ++c) {
-      mbar_init(a_full0 + 8 * c, W8_CONVERTERS / 32);   // one arrival per converter warp
+      mbar_init(a_full0 + 8 * c, NCW);   // one arrival per converter warp
       mbar_init(a_empty0 + 8 * c, 1);
     }
     mbar_init(tmem_full, 1);
@@ -199,18 +210,18 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
       // ===== converters (main loop), then epilogue =====
       const int e = threadIdx.x - 64;  // 0..255
       const int q = warp & 3;                // TMEM lane quarter this warp may access: weight rows 32 q .. 32 q + 31
-      const int half = (warp - 2) >> 2;      // two warps share a quarter: k 0..31 and k 32..63 of the k-block
+      const int half = (warp - 2) >> 2;      // the KPARTS warps of a quarter split the k-block: 64 / KPARTS int8 each
       {
         // this thread's row of the raw tile ([128 rows][128 B], 128-byte TMA swizzle: 16-byte chunk ^= row & 7): of each of
-        // the stage's two k-blocks j it widens int8 32 half .. 32 half + 31, i.e. chunks 4 j + 2 half and 4 j + 2 half + 1
+        // the stage's two k-blocks j it widens chunks 4 j + CHUNKS half .. + CHUNKS - 1
         const int r = q * 32 + lane;
-        uint32_t src[2][2];
+        uint32_t src[2][CHUNKS];
 #pragma unroll
         for (int j = 0; j < 2; ++j)
 #pragma unroll
-          for (int i = 0; i < 2; ++i)
-            src[j][i] = 2 * B_TILE_BYTES + r * W8_RAW_K + (((4 * j + 2 * half + i) ^ (r & 7)) << 4);
-        const uint32_t t_lane = tmem_d + ((uint32_t)(q * 32) << 16) + ACC_COLS + half * 16;
+          for (int i = 0; i < CHUNKS; ++i)
+            src[j][i] = 2 * B_TILE_BYTES + r * W8_RAW_K + (((4 * j + CHUNKS * half + i) ^ (r & 7)) << 4);
+        const uint32_t t_lane = tmem_d + ((uint32_t)(q * 32) << 16) + ACC_COLS + half * (8 * CHUNKS);
         int s = 0, c = 0;
         uint32_t ph = 0, cph = 0;
 #ifdef W8_TIMING
@@ -223,27 +234,23 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
           mbar_wait(raw_full0 + 8 * s, ph);
           W8_T(t_raw);
           const uint32_t raw_stage = tiles + s * STAGE_BYTES;
-          uint32_t w[2][8];
+          uint32_t w[2][4 * CHUNKS];
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int i = 0; i < CHUNKS; ++i)
+              asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[j][4 * i]), "=r"(w[j][4 * i + 1]), "=r"(w[j][4 * i + 2]), "=r"(w[j][4 * i + 3]) : "r"(raw_stage + src[j][i]));
 #pragma unroll
           for (int j = 0; j < 2; ++j) {
-            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[j][0]), "=r"(w[j][1]), "=r"(w[j][2]), "=r"(w[j][3]) : "r"(raw_stage + src[j][0]));
-            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[j][4]), "=r"(w[j][5]), "=r"(w[j][6]), "=r"(w[j][7]) : "r"(raw_stage + src[j][1]));
-          }
+            uint32_t o[8 * CHUNKS];
 #pragma unroll
-          for (int j = 0; j < 2; ++j) {
-            uint32_t o[16];
-#ifndef W8_EXP_NOCONVERT   // experiment build: skip the widening (garbage results) to time the rest alone
-#pragma unroll
-            for (int i = 0; i < 8; ++i) w8_widen4(w[j][i], o[2 * i], o[2 * i + 1]);
-#else
-#pragma unroll
-            for (int i = 0; i < 8; ++i) { o[2 * i] = w[j][i]; o[2 * i + 1] = w[j][i]; }
-#endif
+            for (int i = 0; i < 4 * CHUNKS; ++i) w8_widen4(w[j][i], o[2 * i], o[2 * i + 1]);
             W8_T(t_conv);
             mbar_wait(a_empty0 + 8 * c, cph ^ 1);   // the MMAs that last read this TMEM slot have completed
             tcgen05_fence_after();
             W8_T(t_slot);
-            tmem_st16(t_lane + c * W8_A_COLS, o);
+            if constexpr (CHUNKS == 2) tmem_st16(t_lane + c * W8_A_COLS, o);
+            else tmem_st8(t_lane + c * W8_A_COLS, o);
             tmem_st_wait();
             W8_T(t_conv);
             tcgen05_fence_before();
@@ -255,7 +262,7 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
           if (++s == stages) { s = 0; ph ^= 1; }
         }
 #ifdef W8_TIMING
-        if (p.dbg && blockIdx.x == 7 && blockIdx.y == 0 && blockIdx.z == 0 && (e == 0 || e == 224)) {
+        if (p.dbg && blockIdx.x == 7 && blockIdx.y == 0 && blockIdx.z == 0 && (e == 0 || e == W8_CONVERTERS - 32)) {
           long long* d = p.dbg + (e ? 8 : 0);
           d[0] = t_raw; d[1] = t_slot; d[2] = t_conv; d[3] = t_sync; d[4] = kb1 - kb0;   // per k-block figures = sums / this
         }
@@ -271,13 +278,13 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
       float* stage_f = reinterpret_cast<float*>(smem_raw + (tiles - smem_u32(smem_raw)));  // [BN tokens][128 lanes] over the idle raw ring
       const int lane_row = q * 32 + lane;
 #pragma unroll 1
-      for (int c0 = half * 16; c0 < BN; c0 += 32) {
+      for (int c0 = half * 16; c0 < BN; c0 += 16 * KPARTS) {
         tmem_ld16(taddr + c0, v);
         tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 16; ++j) stage_f[(c0 + j) * BM + lane_row] = __uint_as_float(v[j]);
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(W8_CONVERTERS) : "memory");
       if (SILU) {
         for (int idx = e; idx < BN * 16; idx += W8_CONVERTERS) {
           const int t = idx >> 4, f = (idx & 15) * 4;
@@ -373,22 +380,22 @@ int make_tmap_u8(CUtensorMap* map, const void* base, long long rows, long long c
   return DLI_OK;
 }
 
-template <int BN, int EPI>
+template <int BN, int EPI, int NCW>
 static int launch_w8_variant(const CUtensorMap& tw, const CUtensorMap& tx, const W8Params& p, dim3 grid, cudaStream_t st) {
   constexpr int STAGE_BYTES = 2 * BN * BK * 2 + W8_RAW_BYTES;
   const size_t smem = (size_t)p.stages * STAGE_BYTES + 1024;
-  auto kern = gemm_w8_kernel<BN, EPI>;
+  auto kern = gemm_w8_kernel<BN, EPI, NCW>;
   DLI_ONCE_PER_DEVICE(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
-  return launch_kernel("gemm_w8_kernel", kern, grid, dim3(W8_THREADS), smem, st, tw, tx, p);
+  return launch_kernel("gemm_w8_kernel", kern, grid, dim3(64 + 32 * NCW), smem, st, tw, tx, p);
 }
 
 template <int BN>
 static int launch_w8_epi(int epi, const CUtensorMap& tw, const CUtensorMap& tx, const W8Params& p, dim3 grid, cudaStream_t st) {
   switch (epi) {
-    case DLI_EPI_STORE_F32: return launch_w8_variant<BN, DLI_EPI_STORE_F32>(tw, tx, p, grid, st);
-    case DLI_EPI_ADD_F32: return launch_w8_variant<BN, DLI_EPI_ADD_F32>(tw, tx, p, grid, st);
-    case DLI_EPI_STORE_BF16: return launch_w8_variant<BN, DLI_EPI_STORE_BF16>(tw, tx, p, grid, st);
-    case DLI_EPI_SILU_MUL_BF16: return launch_w8_variant<BN, DLI_EPI_SILU_MUL_BF16>(tw, tx, p, grid, st);
+    case DLI_EPI_STORE_F32: return launch_w8_variant<BN, DLI_EPI_STORE_F32, 8>(tw, tx, p, grid, st);
+    case DLI_EPI_ADD_F32: return launch_w8_variant<BN, DLI_EPI_ADD_F32, 8>(tw, tx, p, grid, st);
+    case DLI_EPI_STORE_BF16: return launch_w8_variant<BN, DLI_EPI_STORE_BF16, 8>(tw, tx, p, grid, st);
+    case DLI_EPI_SILU_MUL_BF16: return launch_w8_variant<BN, DLI_EPI_SILU_MUL_BF16, 16>(tw, tx, p, grid, st);  // long CTAs
     default: return fail(DLI_ERR_ARG, "unknown epilogue %d", epi);
   }
 }

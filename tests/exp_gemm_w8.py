@@ -8,19 +8,23 @@ from tests import gpu_ops as ops
 
 dev = "cuda"
 M = int(os.environ.get("EXP_M", "16"))
-shapes = [(12288, 4096), (4096, 4096), (4096, 11008)]
+shapes = [(12288, 4096), (4096, 4096), (4096, 11008), (-11008, 4096)]    # negative n: gate|up with the SiLU epilogue
 only_w8 = bool(os.environ.get("EXP_ONLY_W8"))
 for (n, k) in shapes:
-    nbuf = max(2, int(400e6 // (n * k)) + 1)
+    silu = n < 0
+    n = abs(n)
+    rows = 2 * n if silu else n
+    epi = _ffi.EPI_SILU_MUL_BF16 if silu else _ffi.EPI_ADD_F32
+    nbuf = max(2, int(400e6 // (rows * k)) + 1)
     x = torch.randn(M, k, device=dev, dtype=torch.bfloat16)
-    out = torch.zeros(M, n, device=dev, dtype=torch.float32)
-    qs = [torch.randint(0, 256, (n, k), device=dev, dtype=torch.uint8) for _ in range(nbuf)]
-    sc = torch.rand(n, device=dev) * 1e-3
+    out = torch.zeros(M, n, device=dev, dtype=torch.bfloat16 if silu else torch.float32)
+    qs = [torch.randint(0, 256, (rows, k), device=dev, dtype=torch.uint8) for _ in range(nbuf)]
+    sc = torch.rand(rows, device=dev) * 1e-3
 
     def run_w8():
         for q in qs:
             _ffi.check(_ffi.lib.dli_gemm_w8(x.data_ptr(), k, q.data_ptr(), sc.data_ptr(), out.data_ptr(), n, M, n, k,
-                                            _ffi.EPI_ADD_F32, ops.stream()))
+                                            epi, ops.stream()))
 
     def timeit(fn, reps=6):
         fn()
@@ -34,11 +38,11 @@ for (n, k) in shapes:
         return e0.elapsed_time(e1) * 1e3 / (reps * nbuf)
 
     us8 = timeit(run_w8)
-    line = f"m={M} n={n:6d} k={k:6d} int8 {n*k/1e6:6.1f} MB {us8:7.2f} us {n*k/us8/1e3:7.1f} GB/s"
+    line = f"m={M} n={n:6d} k={k:6d} {'silu' if silu else 'add '} int8 {rows*k/1e6:6.1f} MB {us8:7.2f} us {rows*k/us8/1e3:7.1f} GB/s"
     if not only_w8:
-        ws = [torch.randn(n, k, device=dev, dtype=torch.bfloat16) for _ in range(nbuf)]
-        us16 = timeit(lambda: [ops.gemm(x, w, _ffi.EPI_ADD_F32, out=out) for w in ws])
-        line += f" | bf16 {us16:7.2f} us {n*k*2/us16/1e3:7.1f} GB/s | speed-up {us16/us8:.2f}"
+        ws = [torch.randn(rows, k, device=dev, dtype=torch.bfloat16) for _ in range(nbuf)]
+        us16 = timeit(lambda: [ops.gemm(x, w, epi, out=out) for w in ws])
+        line += f" | bf16 {us16:7.2f} us {rows*k*2/us16/1e3:7.1f} GB/s | speed-up {us16/us8:.2f}"
         del ws
     print(line, flush=True)
     del qs
