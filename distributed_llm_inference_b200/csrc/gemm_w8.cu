@@ -395,7 +395,7 @@ static int launch_w8_epi(int epi, const CUtensorMap& tw, const CUtensorMap& tx, 
     case DLI_EPI_STORE_F32: return launch_w8_variant<BN, DLI_EPI_STORE_F32, 8>(tw, tx, p, grid, st);
     case DLI_EPI_ADD_F32: return launch_w8_variant<BN, DLI_EPI_ADD_F32, 8>(tw, tx, p, grid, st);
     case DLI_EPI_STORE_BF16: return launch_w8_variant<BN, DLI_EPI_STORE_BF16, 8>(tw, tx, p, grid, st);
-    case DLI_EPI_SILU_MUL_BF16: return launch_w8_variant<BN, DLI_EPI_SILU_MUL_BF16, 16>(tw, tx, p, grid, st);  // long CTAs
+    case DLI_EPI_SILU_MUL_BF16: return launch_w8_variant<BN, DLI_EPI_SILU_MUL_BF16, 8>(tw, tx, p, grid, st);   // 16 warps measured no faster (the CTAs wait for data)
     default: return fail(DLI_ERR_ARG, "unknown epilogue %d", epi);
   }
 }
