@@ -231,7 +231,7 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
 #define W8_T(acc) ((void)0)
 #endif
         for (int kp = kp0; kp < kp1; ++kp) {
-          mbar_wait(raw_full0 + 8 * s, ph);
+          mbar_wait(raw_full0 + 8 * s, ph, 40);   // back off between polls: 16 spinning converter warps per SM take issue slots from the TMA and MMA warps
           W8_T(t_raw);
           const uint32_t raw_stage = tiles + s * STAGE_BYTES;
           uint32_t w[2][4 * CHUNKS];
@@ -246,7 +246,7 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
 #pragma unroll
             for (int i = 0; i < 4 * CHUNKS; ++i) w8_widen4(w[j][i], o[2 * i], o[2 * i + 1]);
             W8_T(t_conv);
-            mbar_wait(a_empty0 + 8 * c, cph ^ 1);   // the MMAs that last read this TMEM slot have completed
+            mbar_wait(a_empty0 + 8 * c, cph ^ 1, 20);   // the MMAs that last read this TMEM slot have completed
             tcgen05_fence_after();
             W8_T(t_slot);
             if constexpr (CHUNKS == 2) tmem_st16(t_lane + c * W8_A_COLS, o);
