@@ -279,11 +279,15 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
   const int t_begin = split * chunk;
   const int t_end = min(T, t_begin + chunk);
   const int n_stages = t_end > t_begin ? (t_end - t_begin + DEC_STAGE_TOK - 1) / DEC_STAGE_TOK : 0;
-  // fused RoPE + append (unsplit contexts only): the pages hold tokens [0, T - 1); the step's own key and value come
-  // from the projection buffer, go to the page AND straight into their row of the last ring stage
+  // fused RoPE + append: the pages hold tokens [0, T - 1); the step's own key and value come from the projection
+  // buffer, go to the page AND straight into their row of the last ring stage
   const DecRope rp = at_step_row<HD>(rp_in);
   const bool fused = rp.qkv != nullptr;
-  const int t_copy = fused ? T - 1 : T;  // tokens the producer takes from the pages
+  // split context: every CTA rotates its own copy of the query heads; the ONE split whose range holds position T - 1
+  // rotates and appends the step's key and value (no other split reads that page slot); the combine kernel re-zeroes
+  // the projection buffer once every split has read it
+  const bool owns_new = fused && T - 1 >= t_begin && T - 1 < t_end;
+  const int t_copy = owns_new ? T - 1 : T;  // tokens the producer takes from the pages
 
   float o[G][8], m[G], l[G];
 #pragma unroll
@@ -343,7 +347,7 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
       qf[g][6] = bf16_lo(a.w) * scale_log2; qf[g][7] = bf16_hi(a.w) * scale_log2;
     }
     const int new_row = (T - 1 - t_begin) % DEC_STAGE_TOK;  // row of the step's token inside the last stage
-    if (fused) {
+    if (owns_new) {
       newrow = new_kv_chunk<HD>(rp, b, H, KV, kvh, lane);
       if (warp == 0) append_new_kv<HD>(kv, b, KV, kvh, T - 1, lane, newrow);
     }
@@ -352,7 +356,7 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
       const int t0 = t_begin + i * DEC_STAGE_TOK;
       const uint32_t kbase = ring + slot * STAGE + (uint32_t)grp * ROW + dl * 2;
       mbar_wait(full0 + 8 * slot, (uint32_t)(i / DEC_STAGES) & 1);
-      if (fused && i == n_stages - 1 && warp == (new_row % NG) / GPW) {
+      if (owns_new && i == n_stages - 1 && warp == (new_row % NG) / GPW) {
         // the warp whose token group reads that row puts the new K and V there (the bulk copies never touch it)
         if (lane < 2 * LPT) {
           const uint32_t dst = ring + slot * STAGE + (lane < LPT ? 0u : (uint32_t)KPART) + (uint32_t)new_row * ROW +
@@ -455,16 +459,26 @@ __global__ void __launch_bounds__(DEC_THREADS_STAGED) decode_attn_kernel(const _
       if (d == 0) { dst[HD] = M; dst[HD + 1] = L; }
     }
   }
-  if (fused) zero_consumed<HD, G, DEC_THREADS_STAGED>(rp, b, H, KV, kvh);  // every read of the row is behind the barriers above
+  if (fused && n_splits == 1) zero_consumed<HD, G, DEC_THREADS_STAGED>(rp, b, H, KV, kvh);  // every read of the row is behind the barriers above
   if (threadIdx.x == 0) DLI_TRACE_EV(TR_ATTN, 2);
 }
 
 template <int HD>
 __global__ void __launch_bounds__(HD) decode_combine_kernel(const float* __restrict__ scratch, __nv_bfloat16* __restrict__ out,
-                                                            int H, int n_splits) {
+                                                            int H, int n_splits, float* __restrict__ qkv_zero, int n_all,
+                                                            int KV) {
   pdl_trigger();
   pdl_wait();
   const int h = blockIdx.x, b = blockIdx.y, d = threadIdx.x;
+  if (qkv_zero) {  // fused RoPE over a split context: every split has read the projection row by now -> re-zero it
+    float* row = qkv_zero + (long long)b * n_all;
+    row[h * HD + d] = 0.f;
+    const int G = H / KV;
+    if (h % G == 0) {
+      row[(H + h / G) * HD + d] = 0.f;
+      row[(H + KV + h / G) * HD + d] = 0.f;
+    }
+  }
   const float* src = scratch + ((long long)b * H + h) * n_splits * (HD + 2);
   float M = -INFINITY;
   for (int s = 0; s < n_splits; ++s) M = fmaxf(M, src[s * (HD + 2) + HD]);
@@ -495,17 +509,19 @@ static int launch_dec(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& 
   }
   if (rc || splits == 1) return rc;
   return launch_kernel("decode_combine_kernel", decode_combine_kernel<HD>, dim3(H, batch), dim3(HD), 0, st,
-                       (const float*)scratch, out, H, splits);
+                       (const float*)scratch, out, H, splits, const_cast<float*>(rope.qkv), rope.n_all, KV);
 }
 
-// One CTA per (sequence, KV head) is the only reader of that head's projection and the only writer of its page slot:
-// the condition under which the attention kernel can do the RoPE kernel's work.
+// The attention kernel can do the RoPE kernel's work when one CTA per (sequence, KV head) is the only reader of that
+// head's projection and the only writer of its page slot (unsplit context: any kernel), or -- staged kernel -- when the
+// context is split: every split rotates its own copy of the queries, the split that holds the step's position appends
+// the new key / value, and the combine kernel re-zeroes the projection buffer.
 bool decode_attention_fuses_rope(const KvView& kv, int batch, int H, int KV, int hd) {
   static const bool off = exp_env("DLI_DEC_DIRECT") != nullptr || exp_env("DLI_NO_ROPE_FUSE") != nullptr;
   if (off || KV <= 0 || H % KV != 0 || !(hd == 64 || hd == 128)) return false;
   const int G = H / KV;
   if (!(G == 1 || G == 2 || G == 4 || G == 8)) return false;
-  return decode_splits_for(kv, batch, H, KV, hd) == 1;
+  return decode_splits_for(kv, batch, H, KV, hd) == 1 || !decode_attn_gqa_supported(kv, G, hd);
 }
 
 int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV, int hd,
@@ -517,8 +533,8 @@ int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const Kv
   const int splits = decode_splits_for(kv, batch, H, KV, hd);
   DecRope rope{nullptr, nullptr, nullptr, 0};
   if (rope_in) {
-    DLI_REQUIRE(splits == 1 && rope_in->qkv && rope_in->cos && rope_in->sin,
-                "decode attention with fused RoPE needs an unsplit context (see decode_attention_fuses_rope)");
+    DLI_REQUIRE((splits == 1 || !gqa) && rope_in->qkv && rope_in->cos && rope_in->sin,
+                "decode attention with fused RoPE: the tensor-core GQA kernel needs an unsplit context (see decode_attention_fuses_rope)");
     rope = *rope_in;
   }
   const size_t need = (size_t)batch * H * splits * (hd + 2) * sizeof(float);
@@ -529,9 +545,9 @@ int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const Kv
     if (rc || splits == 1) return rc;
     if (hd == 128)
       return launch_kernel("decode_combine_kernel", decode_combine_kernel<128>, dim3(H, batch), dim3(128), 0, st,
-                           (const float*)scratch, out, H, splits);
+                           (const float*)scratch, out, H, splits, (float*)nullptr, 0, KV);
     return launch_kernel("decode_combine_kernel", decode_combine_kernel<64>, dim3(H, batch), dim3(64), 0, st,
-                         (const float*)scratch, out, H, splits);
+                         (const float*)scratch, out, H, splits, (float*)nullptr, 0, KV);
   }
 #define DLI_DEC_CASE(HD_, G_) \
   if (hd == HD_ && G == G_) return launch_dec<HD_, G_>(q, out, kv, batch, H, KV, splits, scratch, early_kv, rope, st)
@@ -551,7 +567,7 @@ static int launch_dec_masked(const __nv_bfloat16* q, __nv_bfloat16* out, const K
                          dim3(DEC_THREADS), 0, st, q, kv, scratch, out, H, KV, scale_log2, mask);
   if (rc || splits == 1) return rc;
   return launch_kernel("decode_combine_kernel", decode_combine_kernel<HD>, dim3(H, batch), dim3(HD), 0, st,
-                       (const float*)scratch, out, H, splits);
+                       (const float*)scratch, out, H, splits, (float*)nullptr, 0, KV);
 }
 
 int launch_decode_attention_masked(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV,
