@@ -45,6 +45,9 @@ enum dli_status {
   DLI_ERR_WORKSPACE = -4     /* workspace too small */
 };
 
+/* Activations and weights are bf16, the dtype BASELINE's north star names.  The reference casts checkpoints to fp16
+ * (utils/model.py:67-68); tcgen05 kind::f16 multiplies fp16 as well, but no fp16 instantiation exists yet: any other
+ * value is refused by dli_span_create. */
 enum dli_dtype { DLI_BF16 = 0 };
 
 typedef void* dli_stream_t; /* cudaStream_t */
