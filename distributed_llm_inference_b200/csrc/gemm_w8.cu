@@ -38,6 +38,9 @@ namespace dli {
 // each thread a quarter of a row per k-block instead of half.
 constexpr int W8_RAW_K = 2 * BK;           // a raw stage holds TWO k-blocks: 128-byte rows, like the bf16 kernel's TMA rows
 constexpr int W8_RAW_BYTES = BM * W8_RAW_K;  // 128 rows x 128 int8
+#ifndef W8_TMAP_ELT
+#define W8_TMAP_ELT 1   // bytes per element the weight tensor map is described in (experiments: 4 = uint32 view)
+#endif
 constexpr int W8_MAX_STAGES = 5;   // raw ring: int8 weight tile + two activation tiles per stage (what is in flight from HBM)
 constexpr int W8_A_SLOTS = 4;      // widened bf16 weight tiles (32 TMEM columns each) between converters and MMA warp
 constexpr int W8_A_COLS = BK / 2;  // 64 bf16 = 32 columns of bf16 pairs
@@ -144,10 +147,10 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
       auto load_weights = [&](int s, int kp) {
         const uint32_t raw = tiles + s * STAGE_BYTES + 2 * B_TILE_BYTES;
         if (SILU) {  // 64 gate rows + 64 up rows of the same 64 features
-          tma_load_2d(raw, &tma_w, raw_full0 + 8 * s, kp * W8_RAW_K, a_row0);
-          tma_load_2d(raw + W8_RAW_BYTES / 2, &tma_w, raw_full0 + 8 * s, kp * W8_RAW_K, p.up_row_offset + a_row0);
+          tma_load_2d(raw, &tma_w, raw_full0 + 8 * s, kp * (W8_RAW_K / W8_TMAP_ELT), a_row0);
+          tma_load_2d(raw + W8_RAW_BYTES / 2, &tma_w, raw_full0 + 8 * s, kp * (W8_RAW_K / W8_TMAP_ELT), p.up_row_offset + a_row0);
         } else {
-          tma_load_2d(raw, &tma_w, raw_full0 + 8 * s, kp * W8_RAW_K, a_row0);
+          tma_load_2d(raw, &tma_w, raw_full0 + 8 * s, kp * (W8_RAW_K / W8_TMAP_ELT), a_row0);
         }
       };
       auto load_acts = [&](int s, int kp) {
@@ -192,9 +195,11 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
           if (elect_one()) {
             const uint32_t tmem_a = tmem_d + ACC_COLS + c * W8_A_COLS;
             const uint64_t bdesc = umma_desc_sw128(tiles + s * STAGE_BYTES + j * B_TILE_BYTES);
+#ifndef W8_EXP_STREAM   // experiment build: no MMAs, no widening -- the TMA / barrier chain alone
 #pragma unroll
             for (int k = 0; k < BK / UMMA_K; ++k)
               w8_umma_ts(tmem_d, tmem_a + 8 * k, bdesc + 2 * k, idesc, (kp > kp0 || j > 0 || k > 0) ? 1u : 0u);
+#endif
             umma_commit(a_empty0 + 8 * c);   // the TMEM slot may be overwritten
             if (j == 1) {
               umma_commit(empty0 + 8 * s);   // the raw stage (its activation tiles) may be refilled
@@ -249,9 +254,11 @@ gemm_w8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
             mbar_wait(a_empty0 + 8 * c, cph ^ 1, 20);   // the MMAs that last read this TMEM slot have completed
             tcgen05_fence_after();
             W8_T(t_slot);
+#ifndef W8_EXP_STREAM
             if constexpr (CHUNKS == 2) tmem_st16(t_lane + c * W8_A_COLS, o);
             else tmem_st8(t_lane + c * W8_A_COLS, o);
             tmem_st_wait();
+#endif
             W8_T(t_conv);
             tcgen05_fence_before();
             __syncwarp();
@@ -369,11 +376,11 @@ int make_tmap_u8(CUtensorMap* map, const void* base, long long rows, long long c
   if (!fn) return fail(DLI_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   if ((reinterpret_cast<uintptr_t>(base) & 15) || (cols % 16) != 0)
     return fail(DLI_ERR_ARG, "int8 TMA operand needs a 16-byte aligned base and a row length that is a multiple of 16");
-  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t dims[2] = {(cuuint64_t)cols / W8_TMAP_ELT, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)cols};
-  cuuint32_t box[2] = {(cuuint32_t)W8_RAW_K, (cuuint32_t)box_rows};
+  cuuint32_t box[2] = {(cuuint32_t)W8_RAW_K / W8_TMAP_ELT, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = fn(map, W8_TMAP_ELT == 4 ? CU_TENSOR_MAP_DATA_TYPE_UINT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(DLI_ERR_CUDA, "cuTensorMapEncodeTiled (uint8) failed with CUresult %d", (int)r);
