@@ -62,7 +62,7 @@ class StageIO:
     state: Optional[torch.Tensor] = None           # int32 [4]
     wait_lag: int = 0
     chain: int = 0
-    timeout_ms: int = 2000
+    timeout_ms: int = 10000       # a rank held up by the host for seconds must not turn into a spurious time-out
 
     def to_ffi(self, ffi):
         p = lambda t: None if t is None else t.data_ptr()

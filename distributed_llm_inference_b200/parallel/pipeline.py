@@ -288,7 +288,7 @@ class PipelineStage:
         if x.data_ptr() == dst.data_ptr():
             return
         if r.steps > 0:
-            _ffi.check(_ffi.lib.dli_flag_wait(r.flags[m].data_ptr(), r.steps, r.state[m].data_ptr(), 2000,
+            _ffi.check(_ffi.lib.dli_flag_wait(r.flags[m].data_ptr(), r.steps, r.state[m].data_ptr(), 10000,
                                               _ffi.current_stream(self.device)))
         dst.copy_(x.view(dst.shape) if x.numel() == dst.numel() else x, non_blocking=True)
 
@@ -338,7 +338,7 @@ class PipelineStage:
         from distributed_llm_inference_b200 import _ffi
 
         r = self.rings[ring]
-        _ffi.check(_ffi.lib.dli_flag_wait(r.flags[m].data_ptr(), r.steps, r.state[m].data_ptr(), 2000, stream.cuda_stream))
+        _ffi.check(_ffi.lib.dli_flag_wait(r.flags[m].data_ptr(), r.steps, r.state[m].data_ptr(), 10000, stream.cuda_stream))
 
     def check_errors(self) -> None:
         """After a synchronise: raise if any in-kernel flag wait gave up (a producer never signalled)."""
@@ -355,6 +355,6 @@ class PipelineStage:
                     from distributed_llm_inference_b200 import _ffi
 
                     for m in range(len(r.gids)):
-                        _ffi.check(_ffi.lib.dli_flag_wait(r.flags[m].data_ptr(), r.steps, r.state[m].data_ptr(), 2000,
+                        _ffi.check(_ffi.lib.dli_flag_wait(r.flags[m].data_ptr(), r.steps, r.state[m].data_ptr(), 10000,
                                                           _ffi.current_stream(self.device)))
             torch.cuda.synchronize(self.device)
