@@ -200,7 +200,7 @@ class LlamaBlock(nn.Module):
     # ------------------------------------------------------------------ whole-step CUDA graph
     def graphed_decode(self, generation_id: str, cache: PartialLlamaSinkCache, max_ctx: int,
                        x: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
-                       stage: Optional[StageIO] = None) -> "GraphedDecode":
+                       stage: Optional[StageIO] = None, streaming_steps: int = 0) -> "GraphedDecode":
         """Capture ONE decode step (q_len = 1) of this span for a live generation into a CUDA graph.
 
         The reference hides decode launch latency with three small per-layer graphs (utils/cuda.py:6-77 used at
@@ -215,8 +215,11 @@ class LlamaBlock(nn.Module):
         ``stage`` (instead of ``x`` / ``out``): the step is a pipeline stage step (``dli_stage_decode_step``) whose entry
         kernel waits for the producer's flag (or gathers embedding rows by token id) and whose last kernel stores the
         result into the consumer's memory and releases its flag -- see ``StageIO``.
+        ``streaming_steps > 0`` (a generation whose sink window is FULL, ``length == window_length``): the captured step is
+        the steady state of attention-sink streaming -- evict one token and re-rotate the kept keys (cache.py:111-133),
+        then the decode step -- replayable for that many steps; ``max_ctx`` is ignored (the context stays at the window).
         """
-        return GraphedDecode(self, cache, generation_id, max_ctx, x=x, out=out, stage=stage)
+        return GraphedDecode(self, cache, generation_id, max_ctx, x=x, out=out, stage=stage, streaming_steps=streaming_steps)
 
     # ------------------------------------------------------------------ instrumentation (bench.py)
     def profile(self, enable: bool = True) -> None:
@@ -381,21 +384,33 @@ class GraphedDecode:
     (a static buffer that the next ``step`` overwrites)."""
 
     def __init__(self, block: LlamaBlock, cache: PartialLlamaSinkCache, generation_id: str, max_ctx: int,
-                 x: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None, stage: Optional[StageIO] = None):
+                 x: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None, stage: Optional[StageIO] = None,
+                 streaming_steps: int = 0):
         gen = cache.generation(generation_id)
         if gen is None or gen.length == 0:
             raise ValueError("graphed_decode needs a generation that has been prefilled through this span")
         ffi = block._ffi()
         device = gen.seq_lens.device
         B, h = gen.batch, block.config.hidden_size
+        W = cache.window_length
+        self.streaming = streaming_steps > 0
+        self.steps_left = streaming_steps
+        if self.streaming:
+            if gen.length != W or stage is not None:
+                raise ValueError("a streaming graph is captured on a generation whose window is full "
+                                 f"(length {gen.length}, window {W}) and outside a pipeline stage")
+            if W - cache.num_sink_tokens - 1 <= 0:
+                raise ValueError("window too small for its sink tokens")
+            max_ctx = W
         self.block, self.cache, self.gid, self.max_ctx = block, cache, generation_id, max_ctx
-        if max_ctx >= cache.window_length:
-            raise ValueError("graphed decode cannot cross window_length (eviction is a separate launch)")
+        if not self.streaming and max_ctx >= W:
+            raise ValueError("graphed decode cannot cross window_length; once the window is full capture the steady "
+                             "state with streaming_steps")
         cache.reserve(generation_id, B, max_ctx)                    # block table fixed for the graph's lifetime
         with torch.cuda.device(device):
             block._ensure_span(device)
             ws = block._workspace(B, B, max_ctx, device)
-        table = block._rope_table(device, gen.first_pos + gen.seen_tokens + (max_ctx - gen.length) + 1)
+        table = block._rope_table(device, gen.first_pos + gen.seen_tokens + max(max_ctx - gen.length, streaming_steps) + 1)
         for t in (x, out):
             if t is not None and (tuple(t.shape) != (B, 1, h) or t.dtype != torch.bfloat16 or not t.is_contiguous()):
                 raise ValueError(f"graphed_decode buffers must be contiguous bf16 [{B}, 1, {h}]")
@@ -418,6 +433,26 @@ class GraphedDecode:
                 raise
             return table, ws, stage
 
+        def launch_streaming():
+            # steady state of the sink window, all constants: evict one token for every layer (keys re-rotated back by one
+            # position with the generation's cos/sin history), lengths W -> W - 1, then the step appends and restores W
+            p0 = gen.first_pos
+            n_layers, KV, hd = cache._shape
+            ch, sh = table[0, p0:p0 + W], table[1, p0:p0 + W]
+            kvw = cache.kv_desc(gen, W)
+            st = ffi.current_stream(device)
+            try:
+                ffi.check(ffi.lib.dli_kv_evict(C.byref(kvw), n_layers, B, KV, hd, W, W, cache.num_sink_tokens, 1, ch.data_ptr(),
+                                               sh.data_ptr(), st))
+                gen.seq_lens.fill_(W - 1)
+                ffi.check(ffi.lib.dli_span_decode_step(block._span, C.byref(kv), B, self.x.data_ptr(), self.out.data_ptr(),
+                                                       table[0].data_ptr(), table[1].data_ptr(), self.pos.data_ptr(), 1,
+                                                       ws.data_ptr(), ws.numel(), st))
+            except ffi.DliError:
+                block._ws = None
+                raise
+            return table, ws, ch, sh
+
         def launch():
             # position and lengths live on the device: the kernels index the cos/sin tables by *pos and the span's last
             # kernel advances pos and seq_lens, so a replayed step is nothing but the span's own PDL-chained kernels
@@ -435,6 +470,8 @@ class GraphedDecode:
         warm = "__dli_graph_warmup__"
         block(warm, self.x, past_key_value=cache, cache_position=torch.zeros(1, dtype=torch.long, device=device))
         cache.close(warm)
+        if self.streaming:
+            launch = launch_streaming             # (the eviction kernel needs no one-time set-up)
         if stage is not None:
             launch = launch_stage
             if stage.lm_head is not None:     # the head's GEMM instantiation, outside capture as well
@@ -449,21 +486,31 @@ class GraphedDecode:
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.device(device), torch.cuda.graph(self.graph):
             self._keep = launch()
-        self.launches = ffi.lib.dli_last_launch_count()
-        self._len = gen.length        # host mirror of the device-side position
+        self.launches = ffi.lib.dli_last_launch_count() + (2 if self.streaming else 0)   # + eviction kernel, length reset
+        self._len = gen.length        # host mirrors of the device-side length and position
+        self._seen = gen.seen_tokens
 
     def before_replay(self) -> None:
         gen = self.cache.generation(self.gid)
-        if gen.length + 1 > self.max_ctx:
+        if self.streaming:
+            if gen.length != self.cache.window_length or self.steps_left <= 0:
+                raise RuntimeError("streaming graph: the window must be full and steps must remain "
+                                   f"(length {gen.length}, steps left {self.steps_left})")
+        elif gen.length + 1 > self.max_ctx:
             raise RuntimeError(f"graphed decode captured for at most {self.max_ctx} tokens")
-        if gen.length != self._len:                                    # eager steps ran in between: re-seed the position
+        if gen.seen_tokens != self._seen:                              # eager steps ran in between: re-seed the position
             self.pos.fill_(gen.first_pos + gen.seen_tokens)
 
     def after_replay(self) -> None:
         gen = self.cache.generation(self.gid)
-        gen.length += 1                                                # host mirror of the device-side add
+        if self.streaming:                                             # evicted one, appended one: the length stays W
+            gen.evictions += 1
+            self.steps_left -= 1
+        else:
+            gen.length += 1                                            # host mirror of the device-side add
         self._len = gen.length
         gen.seen_tokens += 1
+        self._seen = gen.seen_tokens
         self.block.last_launch_count = self.launches
 
     def step(self, x: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -321,3 +321,31 @@ def test_make_inference_graphed_callable_replays():
         torch.manual_seed(seed)
         x, y = torch.randn(8, 64, device=DEV), torch.randn(8, 64, device=DEV)
         torch.testing.assert_close(g(x, y), f(x, y))
+
+
+@pytest.mark.parametrize("name", ["gqa_evict_float", "gqa_evict_literal"])
+def test_streaming_graph_matches_reference_fixture(name):
+    """Attention-sink streaming as ONE replayed graph per step: once the window is full, eviction (all layers, keys
+    re-rotated, cache.py:111-133), the length reset and the decode step are captured together
+    (``graphed_decode(..., streaming_steps=n)``).  Same inputs as the eviction fixtures the reference produced: the first
+    three decode steps run eagerly (they fill the window and do the first eviction), the other eight are graph replays."""
+    from tests.golden.runner import span_case_inputs, span_case_weights
+
+    case = next(c for c in SPAN_CASES if c.name == name)
+    gold = np.load(os.path.join(GOLD, f"span_{name}.npz"))
+    shp, x0, steps = span_case_inputs(case, torch.bfloat16, DEV)
+    blk = gpu_make_span(shp, span_case_weights(case, torch.bfloat16, DEV), case.attn_implementation, case.rope)
+    cache = gpu_make_cache(case.window, case.sinks)
+    blk("g0", x0, past_key_value=cache)
+    graph = None
+    for i, xt in enumerate(steps):
+        if graph is None and cache.get_seq_length(0, "g0") == case.window:
+            graph = blk.graphed_decode("g0", cache, 0, streaming_steps=len(steps) - i)
+        if graph is not None:
+            y = graph.step(xt).clone()
+        else:
+            y = blk("g0", xt, past_key_value=cache, cache_position=torch.tensor([case.prefill + i], device=DEV))[0]
+        _check(f"{name}/step{i}{' (graph)' if graph is not None else ''}", y.float().cpu().numpy(), gold["decode"][i])
+    assert graph is not None and graph.steps_left == 0 and cache.get_seq_length(0, "g0") == case.window
+    with pytest.raises(RuntimeError):
+        graph.step(steps[0])
