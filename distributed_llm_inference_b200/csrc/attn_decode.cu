@@ -513,15 +513,16 @@ static int launch_dec(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& 
 }
 
 // The attention kernel can do the RoPE kernel's work when one CTA per (sequence, KV head) is the only reader of that
-// head's projection and the only writer of its page slot (unsplit context: any kernel), or -- staged kernel -- when the
-// context is split: every split rotates its own copy of the queries, the split that holds the step's position appends
-// the new key / value, and the combine kernel re-zeroes the projection buffer.
+// head's projection and the only writer of its page slot (unsplit context), or when the context is split: every split
+// rotates its own copy of the queries, the split that holds the step's position appends the new key / value, and the
+// combine kernel re-zeroes the projection buffer.
 bool decode_attention_fuses_rope(const KvView& kv, int batch, int H, int KV, int hd) {
   static const bool off = exp_env("DLI_DEC_DIRECT") != nullptr || exp_env("DLI_NO_ROPE_FUSE") != nullptr;
   if (off || KV <= 0 || H % KV != 0 || !(hd == 64 || hd == 128)) return false;
   const int G = H / KV;
   if (!(G == 1 || G == 2 || G == 4 || G == 8)) return false;
-  return decode_splits_for(kv, batch, H, KV, hd) == 1 || !decode_attn_gqa_supported(kv, G, hd);
+  (void)kv; (void)batch;
+  return true;
 }
 
 int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const KvView& kv, int batch, int H, int KV, int hd,
@@ -533,8 +534,7 @@ int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const Kv
   const int splits = decode_splits_for(kv, batch, H, KV, hd);
   DecRope rope{nullptr, nullptr, nullptr, 0};
   if (rope_in) {
-    DLI_REQUIRE((splits == 1 || !gqa) && rope_in->qkv && rope_in->cos && rope_in->sin,
-                "decode attention with fused RoPE: the tensor-core GQA kernel needs an unsplit context (see decode_attention_fuses_rope)");
+    DLI_REQUIRE(rope_in->qkv && rope_in->cos && rope_in->sin, "decode attention with fused RoPE: null projection / cos / sin");
     rope = *rope_in;
   }
   const size_t need = (size_t)batch * H * splits * (hd + 2) * sizeof(float);
@@ -545,9 +545,9 @@ int launch_decode_attention(const __nv_bfloat16* q, __nv_bfloat16* out, const Kv
     if (rc || splits == 1) return rc;
     if (hd == 128)
       return launch_kernel("decode_combine_kernel", decode_combine_kernel<128>, dim3(H, batch), dim3(128), 0, st,
-                           (const float*)scratch, out, H, splits, (float*)nullptr, 0, KV);
+                           (const float*)scratch, out, H, splits, const_cast<float*>(rope.qkv), rope.n_all, KV);
     return launch_kernel("decode_combine_kernel", decode_combine_kernel<64>, dim3(H, batch), dim3(64), 0, st,
-                         (const float*)scratch, out, H, splits, (float*)nullptr, 0, KV);
+                         (const float*)scratch, out, H, splits, const_cast<float*>(rope.qkv), rope.n_all, KV);
   }
 #define DLI_DEC_CASE(HD_, G_) \
   if (hd == HD_ && G == G_) return launch_dec<HD_, G_>(q, out, kv, batch, H, KV, splits, scratch, early_kv, rope, st)

@@ -90,11 +90,13 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
   const int t_begin = split * chunk;
   const int t_end = min(T, t_begin + chunk);
   const int n_stages = t_end > t_begin ? (t_end - t_begin + GQ_STAGE_TOK - 1) / GQ_STAGE_TOK : 0;
-  // fused RoPE + append (unsplit contexts only, rope_inline.cuh): the pages hold tokens [0, T - 1); the step's own key
-  // and value go to the page and straight into their row of the last ring stage
+  // fused RoPE + append (rope_inline.cuh): the pages hold tokens [0, T - 1); the step's own key and value go to the
+  // page and straight into their row of the last ring stage.  Split context: every split rotates its own copy of the
+  // queries, the one split whose range holds position T - 1 appends, the combine kernel re-zeroes the projection buffer.
   const DecRope rp = at_step_row<HD>(rp_in);
   const bool fused = rp.qkv != nullptr;
-  const int t_copy = fused ? T - 1 : T;
+  const bool owns_new = fused && T - 1 >= t_begin && T - 1 < t_end;
+  const int t_copy = owns_new ? T - 1 : T;
 
   const int r = lane >> 2, c = lane & 3;  // fragment row (query head of the group) and column pair
   float o[NT][4];
@@ -152,7 +154,7 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
     const int tw = warp * 16;  // this warp's token rows inside a stage
     const int new_row = (T - 1 - t_begin) % GQ_STAGE_TOK;  // row of the step's token inside the last stage
     uint4 newrow = make_uint4(0, 0, 0, 0);
-    if (fused) {
+    if (owns_new) {
       newrow = new_kv_chunk<HD>(rp, b, H, KV, kvh, lane);
       if (warp == 0) append_new_kv<HD>(kv, b, KV, kvh, T - 1, lane, newrow);
     }
@@ -161,7 +163,7 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
       const int s0 = t_begin + i * GQ_STAGE_TOK;
       const uint32_t kbase = ring + slot * STAGE, vbase = kbase + KPART;
       mbar_wait(full0 + 8 * slot, (uint32_t)(i / GQ_STAGES) & 1);
-      if (fused && i == n_stages - 1 && warp == new_row / 16) {
+      if (owns_new && i == n_stages - 1 && warp == new_row / 16) {
         // the warp that owns that token row puts the new K and V there (TMA wrote at most a stale copy of it)
         if (lane < 2 * CPR) {
           const uint32_t dst = (lane < CPR ? kbase : vbase) + gq_off(new_row, lane % CPR);
@@ -278,7 +280,7 @@ __global__ void __launch_bounds__(GQ_THREADS) decode_attn_gqa_kernel(const __gri
       if (d == 0) { dst[HD] = M; dst[HD + 1] = L; }
     }
   }
-  if (fused) zero_consumed<HD, G, GQ_THREADS>(rp, b, H, KV, kvh);  // every read of the row is behind the barriers above
+  if (fused && n_splits == 1) zero_consumed<HD, G, GQ_THREADS>(rp, b, H, KV, kvh);  // every read of the row is behind the barriers above
   if (threadIdx.x == 0) DLI_TRACE_EV(TR_ATTN_GQA, 2);
 }
 
