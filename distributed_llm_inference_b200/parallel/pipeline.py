@@ -24,7 +24,6 @@ fallback when symmetric memory is unavailable use ``torch.distributed`` ``isend/
 """
 from __future__ import annotations
 
-import ctypes as C
 from typing import Dict, List, Optional, Sequence
 
 import torch
