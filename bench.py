@@ -52,6 +52,8 @@ UNIT = "tokens/s"
 MODEL = "7b"
 BATCH = 16
 PROMPT = 512
+C5_CHUNK = 512   # config C5's 8192-token prompt travels as 16 chunks: per-stage time is flat from 512 to 2048 tokens per chunk
+                 # (tests/exp_prefill_chunks.py: 142 / 135 / 141 ms for a 10-layer 70B stage), the fill and drain of N stages is not
 GEMM_CLASSES = ("gemm_qkv", "gemm_o", "gemm_gate_up", "gemm_down")
 
 
@@ -877,6 +879,16 @@ def run_ours(args):
     ctx = Ctx(args)
     rank, world = ctx.rank, ctx.world
     K, W = args.steps, max(args.warmup, 3)
+    if args.exp_c5_chunks:   # experiments: config C5 alone, once per chunk size
+        out = {}
+        for c in (int(v) for v in args.exp_c5_chunks.split(",")):
+            r = run_workload(ctx, "70b", 1, 8192, 1, None, 4, 3, prefill_chunk=c)
+            out[str(c)] = {k: r.get(k) for k in ("prefill_pipeline", "value", "ms_per_step")}
+        if rank == 0:
+            print(json.dumps({"c5_chunks": out, "n_gpus": world}), flush=True)
+        if world > 1:
+            ctx.dist.destroy_process_group()
+        return
     parity = None
     if world > 1 and not args.no_parity:
         parity = pipeline_parity(ctx)
@@ -902,7 +914,7 @@ def run_ours(args):
             configs["c4_ii_70b_8x10_8x4"] = run_workload(ctx, "70b", 4, 512, 8, None, Kc, Wc)
             configs["c4_iii_70b_8x10_8x32"] = run_workload(ctx, "70b", 32, 512, 8, None, Kc, Wc, want_e2e=True)
         if world in (4, 8):
-            configs[f"c5_70b_prefill_8192_{world}_stages"] = run_workload(ctx, "70b", 1, 8192, 1, None, 4, 3, prefill_chunk=2048)
+            configs[f"c5_70b_prefill_8192_{world}_stages"] = run_workload(ctx, "70b", 1, 8192, 1, None, 4, 3, prefill_chunk=C5_CHUNK)
     if rank == 0:
         shape = syn.SHAPES[MODEL]
         cpu = (cpu_reference_decode(shape, main["layers_total"], BATCH * n_mb, PROMPT, budget_s=args.cpu_budget)
@@ -998,6 +1010,7 @@ def main():
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the pipeline_parity record")
     ap.add_argument("--no-configs", action="store_true", help="N > 1: skip the BASELINE configs 3-5 records")
     ap.add_argument("--no-e2e", action="store_true", help="skip the token-ring e2e measurement")
+    ap.add_argument("--exp-c5-chunks", default=None, help="experiments: run config C5 alone with these chunk sizes (comma-separated)")
     ap.add_argument("--w8", action="store_true", help="run the main workload with row-wise int8 weights (experiments)")
     ap.add_argument("--no-w8", action="store_true", help="one GPU: skip the decode_int8_weights record")
     ap.add_argument("--no-chain", action="store_true", help="experiments: a stream barrier in front of every stage step instead "
