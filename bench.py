@@ -45,6 +45,7 @@ if ROOT not in sys.path:
 
 import torch  # noqa: E402
 
+from distributed_llm_inference_b200.parallel.pipeline import PREFILL_CHUNK_TOKENS  # noqa: E402
 from distributed_llm_inference_b200.utils import synthetic as syn  # noqa: E402
 
 METRIC = "decode_tokens_per_sec"
@@ -52,8 +53,6 @@ UNIT = "tokens/s"
 MODEL = "7b"
 BATCH = 16
 PROMPT = 512
-C5_CHUNK = 512   # config C5's 8192-token prompt travels as 16 chunks: per-stage time is flat from 512 to 2048 tokens per chunk
-                 # (tests/exp_prefill_chunks.py: 142 / 135 / 141 ms for a 10-layer 70B stage), the fill and drain of N stages is not
 GEMM_CLASSES = ("gemm_qkv", "gemm_o", "gemm_gate_up", "gemm_down")
 
 
@@ -419,11 +418,9 @@ def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layer
     # s + 1 works on chunk c - 1 (config C5: one 8k-token sequence over 4 or 8 stages)
     chunk = min(prefill_chunk or prompt, prompt)
     prompts = [syn.make_hidden(shape, batch, prompt, seed=99 + m, device=dev) for m in range(n_mb)] if first else None
-    chunks = [(c0, [p[:, c0:c0 + chunk].contiguous() for p in prompts] if first else None) for c0 in range(0, prompt, chunk)]
 
     def prefill_round(ids):
-        for c0, ins in chunks:
-            stage.run_round(ids, ins, batch, min(chunk, prompt - c0), c0, feed_back=False)
+        stage.prefill(ids, prompts, batch, prompt, chunk_tokens=chunk)
 
     if world > 1:   # untimed pass on throw-away generations: one-time descriptor / workspace / communicator set-up
         warm_ids = [f"pfw{m}" for m in range(n_mb)]
@@ -468,7 +465,7 @@ def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layer
                    "peak_source": f"MEASURED_PEAKS.json ({peak_kind}, bf16_tflops_sustained)",
                    "flops": flops, "chunk": f"{batch} x {prompt} tokens, causal, warm (best of 3)",
                    "kernel_ms": {c: round(v[0], 3) for c, v in pf_prof.items()}}
-    del prompts, chunks
+    del prompts
 
     # ---- decode: warm-up, then K timed rounds over the hidden-state ring ----
     # one GPU: the whole stage step is one CUDA graph (LlamaBlock.graphed_decode); pipeline: the stage step's own entry /
@@ -914,7 +911,7 @@ def run_ours(args):
             configs["c4_ii_70b_8x10_8x4"] = run_workload(ctx, "70b", 4, 512, 8, None, Kc, Wc)
             configs["c4_iii_70b_8x10_8x32"] = run_workload(ctx, "70b", 32, 512, 8, None, Kc, Wc, want_e2e=True)
         if world in (4, 8):
-            configs[f"c5_70b_prefill_8192_{world}_stages"] = run_workload(ctx, "70b", 1, 8192, 1, None, 4, 3, prefill_chunk=C5_CHUNK)
+            configs[f"c5_70b_prefill_8192_{world}_stages"] = run_workload(ctx, "70b", 1, 8192, 1, None, 4, 3, prefill_chunk=PREFILL_CHUNK_TOKENS)
     if rank == 0:
         shape = syn.SHAPES[MODEL]
         cpu = (cpu_reference_decode(shape, main["layers_total"], BATCH * n_mb, PROMPT, budget_s=args.cpu_budget)

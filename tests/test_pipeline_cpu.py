@@ -38,10 +38,15 @@ def _worker(rank, world, port, out):
         if rank == 0:
             hist.append([float(t[0, 0, 0]) for t in xs])
     final = stage.run_round(gids, xs, 3, 1, 103, feed_back=False)
+    launches = stage.launches_per_round
+    # chunked prefill: a 10-token prompt in chunks of 4 -> chunks at positions 0, 4, 8 (the last one ragged, 2 tokens)
+    prompts = [torch.arange(10, dtype=torch.float32).view(1, 10, 1).expand(3, 10, 4).contiguous()] if rank == 0 else None
+    pre = stage.prefill(["p"], prompts, 3, 10, chunk_tokens=4)
     if rank == world - 1:
-        out.put(("last", [float(t[0, 0, 0]) for t in final], stage.launches_per_round))
+        out.put(("last", [float(t[0, 0, 0]) for t in final], launches))
+        out.put(("prefill", [list(pre[0].shape), [float(v) for v in pre[0][0, :, 0]]], 0))
     if rank == 0:
-        out.put(("first", hist, stage.launches_per_round))
+        out.put(("first", hist, launches))
     stage._reap()
     dist.barrier()
     dist.destroy_process_group()
@@ -54,7 +59,7 @@ def test_two_stage_pipeline_over_gloo():
     procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
     [p.start() for p in procs]
     got = dict()
-    for _ in range(2):
+    for _ in range(3):
         tag, vals, launches = q.get(timeout=120)
         got[tag] = (vals, launches)
     [p.join(timeout=60) for p in procs]
@@ -76,3 +81,7 @@ def test_two_stage_pipeline_over_gloo():
     assert got["first"][0] == ref[:3]
     assert got["last"][0] == ref[3]
     assert got["first"][1] == 14 and got["last"][1] == 14      # 2 micro-batches x 7 launches per stage
+    # prefill: the last stage holds the LAST chunk (tokens 8, 9 at position 8; third call of generation "p" on each stage)
+    shape, vals = got["prefill"][0]
+    assert shape == [3, 2, 4]
+    assert vals == [((t * 2.0 + 8 + 2) * 3.0 + 8 + 2) for t in (8.0, 9.0)]
