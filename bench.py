@@ -375,7 +375,7 @@ def free_cuda():
 
 
 def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layers_total, K: int, W: int,
-                 prefill_chunk=None, full: bool = False, want_e2e: bool = False, page_tokens: int = 16, w8: bool = False):
+                 prefill_chunk=None, full: bool = False, want_e2e: bool = False, page_tokens: int = 16, w8: bool = False, a8: bool = False):
     """One decode measurement of ``model`` cut into ``ctx.world`` stages: prefill (timed), warm-up, K timed rounds of
     ``n_mb`` micro-batches x ``batch`` sequences over the hidden-state ring.  ``full``: also the instrumented per-class
     pass, the dominant-kernel roofline, batch-1 latency, warm prefill (one GPU).  ``want_e2e``: the token ring
@@ -395,7 +395,7 @@ def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layer
 
     blk = build_span(shape, layer_ids, dev, max_positions=max(8192, total_ctx + 64))
     if w8:
-        blk.quantize_w8()                     # row-wise int8 weights (convert_to_optimized_block(quantize=True))
+        blk.quantize_w8(activations="int8" if a8 else "bf16")   # row-wise int8 weights (convert_to_optimized_block(quantize=True))
         free_cuda()
     cache = PartialLlamaSinkCache(1 << 20, 4, page_tokens=page_tokens,
                                   capacity_tokens=n_mb * batch * (total_ctx + 16) + batch * 192 +
@@ -557,7 +557,7 @@ def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layer
     sb = decode_step_bytes(shape, len(layer_ids), batch, ctx_mid, w8=w8)
     stage_gbs = sb["total"] / (ms_per_step / n_mb * 1e-3) / 1e9
     res = {
-        "model": shape.name, "weights": "int8 rows + fp32 scales, bf16 activations" if w8 else "bf16", "layers_total": n_total, "layers_per_stage": len(layer_ids), "batch": batch, "micro_batches": n_mb,
+        "model": shape.name, "weights": ("int8 rows + fp32 scales, " + ("int8 activations per token, threshold 5.0 (LLM.int8)" if a8 else "bf16 activations")) if w8 else "bf16", "layers_total": n_total, "layers_per_stage": len(layer_ids), "batch": batch, "micro_batches": n_mb,
         "prompt": prompt, "value": round(value, 1), "ms_per_step": round(ms_per_step, 4),
         "ms_per_stage_step": round(ms_per_step / n_mb, 4), "p50_ms_per_token": round(lat[len(lat) // 2] / n_mb, 4),
         "tokens_per_step": tokens_per_step, "steps": K, "launches": int(launches), "clocks": clocks,
@@ -890,10 +890,10 @@ def run_ours(args):
     if world > 1 and not args.no_parity:
         parity = pipeline_parity(ctx)
     n_mb = args.micro_batches or world   # micro-batches in flight (default: the pipeline depth)
-    main = run_workload(ctx, MODEL, BATCH, PROMPT, n_mb, args.layers, K, W, prefill_chunk=args.prefill_chunk, full=not args.w8,
-                        want_e2e=not args.no_e2e, page_tokens=args.page_tokens, w8=args.w8)
+    main = run_workload(ctx, MODEL, BATCH, PROMPT, n_mb, args.layers, K, W, prefill_chunk=args.prefill_chunk, full=not (args.w8 or args.a8),
+                        want_e2e=not args.no_e2e, page_tokens=args.page_tokens, w8=args.w8 or args.a8, a8=args.a8)
     w8_rec = None
-    if world == 1 and not args.w8 and not args.no_w8:
+    if world == 1 and not (args.w8 or args.a8) and not args.no_w8:
         # the same workload with the weights stored as row-wise int8 (the reference's optimised mode keeps its weights
         # in that format, utils/model.py:93-123): a second, clearly labelled record -- the headline stays bf16
         r8 = run_workload(ctx, MODEL, BATCH, PROMPT, n_mb, args.layers, min(K, 32), 3, w8=True)
@@ -1009,6 +1009,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true", help="skip the token-ring e2e measurement")
     ap.add_argument("--exp-c5-chunks", default=None, help="experiments: run config C5 alone with these chunk sizes (comma-separated)")
     ap.add_argument("--w8", action="store_true", help="run the main workload with row-wise int8 weights (experiments)")
+    ap.add_argument("--a8", action="store_true", help="with int8 weights also quantise the activations per token (LLM.int8; experiments)")
     ap.add_argument("--no-w8", action="store_true", help="one GPU: skip the decode_int8_weights record")
     ap.add_argument("--no-chain", action="store_true", help="experiments: a stream barrier in front of every stage step instead "
                                                             "of chaining the micro-batches' steps with programmatic dependent launch")

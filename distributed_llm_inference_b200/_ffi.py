@@ -30,6 +30,8 @@ EXPORTS = (
     "dli_span_forward_masked", "dli_prefill_attention_masked", "dli_decode_attention_masked",
     "dli_quantize_rows_w8", "dli_dequantize_rows_w8", "dli_gemm_w8", "dli_span_bind_weights_w8",
     "dli_span_dequant_scratch_bytes", "dli_span_set_dequant_scratch",
+    "dli_act_i8_bytes", "dli_act_i8_carve", "dli_quantize_act_i8", "dli_gemm_i8",
+    "dli_span_act_i8_scratch_bytes", "dli_span_set_act_i8",
 )
 
 
@@ -59,6 +61,11 @@ class LayerWeightsW8(C.Structure):
     _fields_ = [("wqkv", C.c_void_p), ("sqkv", C.c_void_p), ("wo", C.c_void_p), ("so", C.c_void_p),
                 ("wgu", C.c_void_p), ("sgu", C.c_void_p), ("wdown", C.c_void_p), ("sdown", C.c_void_p),
                 ("g_in", C.c_void_p), ("g_post", C.c_void_p)]
+
+
+class ActI8(C.Structure):
+    _fields_ = [("q", C.c_void_p), ("scale", C.c_void_p), ("ksum", C.c_void_p), ("q2", C.c_void_p),
+                ("scale2", C.c_void_p), ("ksum2", C.c_void_p)]
 
 
 class AttnMask(C.Structure):
@@ -111,6 +118,12 @@ def _load() -> C.CDLL:
         "dli_span_bind_weights_w8": (C.c_int, [vp, i32, C.POINTER(LayerWeightsW8)]),
         "dli_span_dequant_scratch_bytes": (sz, [vp]),
         "dli_span_set_dequant_scratch": (C.c_int, [vp, vp, sz]),
+        "dli_act_i8_bytes": (sz, [i32, i32, i32]),
+        "dli_act_i8_carve": (C.c_int, [vp, sz, i32, i32, i32, C.POINTER(ActI8)]),
+        "dli_quantize_act_i8": (C.c_int, [vp, i64, i32, i32, f32, C.POINTER(ActI8), vp]),
+        "dli_gemm_i8": (C.c_int, [C.POINTER(ActI8), vp, vp, vp, i64, i32, i32, i32, i32, vp]),
+        "dli_span_act_i8_scratch_bytes": (sz, [vp]),
+        "dli_span_set_act_i8": (C.c_int, [vp, vp, sz, f32]),
         "dli_span_forward_masked": (C.c_int, [vp, C.POINTER(KvDesc), i32, i32, i32, C.POINTER(AttnMask), vp, vp, vp, vp, vp, vp, sz, vp]),
         "dli_prefill_attention_masked": (C.c_int, [vp, vp, C.POINTER(KvDesc), i32, i32, i32, i32, i32, i32, i32, C.POINTER(AttnMask), vp]),
         "dli_decode_attention_masked": (C.c_int, [vp, vp, C.POINTER(KvDesc), i32, i32, i32, i32, i32, C.POINTER(AttnMask), vp, sz, vp]),

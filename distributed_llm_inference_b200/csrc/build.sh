@@ -24,7 +24,7 @@ if [ -n "${DLI_VARIANT:-}" ]; then  # A/B experiments on one box: -D$DLI_VARIANT
   BUILD=build_$DLI_VARIANT
 fi
 mkdir -p $BUILD
-SRCS="gemm_tcgen05 gemm_w8 norm_rope attn_decode attn_decode_gqa attn_prefill attn_prefill_tc attn_prefill_tc2 span"
+SRCS="gemm_tcgen05 gemm_w8 gemm_i8 norm_rope attn_decode attn_decode_gqa attn_prefill attn_prefill_tc attn_prefill_tc2 span"
 HDR_HASH=$(cat *.cuh ../../include/dli_b200.h | sha256sum | cut -d' ' -f1)
 pids=()
 relink=0

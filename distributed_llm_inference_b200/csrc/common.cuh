@@ -140,6 +140,16 @@ int launch_gemm_w8(const void* x, long long ldx, const void* q, const float* sca
                    int k, int epilogue, cudaStream_t st);
 int launch_quantize_rows_w8(const void* w_bf16, long long n, long long k, void* q_u8, float* scale, cudaStream_t st);
 int launch_dequantize_rows_w8(const void* q_u8, const float* scale, long long n, long long k, void* w_bf16, cudaStream_t st);
+// int8 x int8 (gemm_i8.cu): activation quantiser and the kind::i8 decode GEMM
+GemmPlan plan_gemm_i8(int m, int n, int k, int epilogue);
+int launch_gemm_i8_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const CUtensorMap& tmap_x2, const CUtensorMap& tmap_w,
+                           const dli_act_i8& x, const float* w_scale, void* out, long long ldo, int m, int n, int epilogue,
+                           cudaStream_t st);
+int launch_gemm_i8(const dli_act_i8* x, const void* q, const float* w_scale, void* out, long long ldo, int m, int n, int k,
+                   int epilogue, cudaStream_t st);
+int launch_quantize_act_i8(const void* x_bf16, long long ldx, int m, int k, float threshold, const dli_act_i8* dst, cudaStream_t st);
+size_t act_i8_bytes(int m, int k, int planes);
+int act_i8_carve(void* base, size_t bytes, int m, int k, int planes, dli_act_i8* out);
 
 // Decode step whose position lives on the device (dli_span_decode_step): which table row to use, and what the span's
 // last kernel advances afterwards.

@@ -124,6 +124,9 @@ struct dli_span {
   void* dq_scratch = nullptr;            // caller-allocated bf16 scratch a w8 span dequantises into at prefill
   size_t dq_scratch_bytes = 0;
   std::vector<dli::ScratchMaps> dq_maps;
+  dli_act_i8 a8{};                       // int8 activations (dli_span_set_act_i8): the one quantised operand of the GEMM about to run
+  float a8_threshold = 0.f;
+  std::vector<dli::ActMapKey> a8_maps;   // uint8 maps over a8.q, keyed by (rows, cols, box)
   const void* head_ptr = nullptr;        // lm_head matrix the maps below describe (dli_stage_decode_step)
   int head_vocab = 0;
   dli::WeightMaps head;
@@ -240,6 +243,30 @@ static int span_gemm(dli_span* s, const void* x, const WeightMaps& wm, void* out
                      int epilogue, cudaStream_t st, const RopeArgs* rope, const W8Maps* w8) {
   if (w8 && w8->q) {
     if (m > 128 || epilogue == DLI_EPI_QKV_ROPE_INTERNAL) return span_gemm_dequant(s, x, *w8, out, ldo, m, n, k, epilogue, st, rope);
+    if (s->a8.q) {  // int8 activations: quantise the operand (one CTA per token), then the kind::i8 GEMM
+      int rc8 = launch_quantize_act_i8(x, k, m, k, s->a8_threshold, &s->a8, st);
+      if (rc8) return rc8;
+      const GemmPlan gi = plan_gemm_i8(m, n, k, epilogue);
+      auto xq_map = [&](const void* base, const CUtensorMap** out_map) -> int {
+        for (auto& e : s->a8_maps)
+          if (e.ptr == base && e.rows == m && e.cols == k && e.box == gi.b_box_rows) { *out_map = &e.map; return DLI_OK; }
+        ActMapKey e{base, m, k, gi.b_box_rows, {}};
+        int r = make_tmap_u8(&e.map, base, m, k, gi.b_box_rows);
+        if (r) return r;
+        s->a8_maps.push_back(e);
+        *out_map = &s->a8_maps.back().map;
+        return DLI_OK;
+      };
+      const CUtensorMap *t1 = nullptr, *t2 = nullptr;
+      if ((rc8 = xq_map(s->a8.q, &t1))) return rc8;
+      t2 = t1;
+      if (s->a8.q2) {
+        if ((rc8 = xq_map(s->a8.q2, &t2))) return rc8;
+        if ((rc8 = xq_map(s->a8.q, &t1))) return rc8;   // the vector may have grown: take the address again
+      }
+      return launch_gemm_i8_planned(gi, *t1, *t2, gi.a_box_rows == 64 ? w8->box64 : w8->box128, s->a8, w8->scale, out, ldo, m, n,
+                                    epilogue, st);
+    }
     const GemmPlan g8 = plan_gemm(m, n, k, epilogue);
     const CUtensorMap* tx8 = nullptr;
     int rc8 = act_map(s, x, m, k, g8.b_box_rows, &tx8);
@@ -443,6 +470,33 @@ size_t dli_span_dequant_scratch_bytes(const dli_span* s) {
   const size_t a = (size_t)s->n_qkv * d.hidden_size, b = (size_t)d.hidden_size * d.n_heads * d.head_dim,
                c = (size_t)2 * d.intermediate_size * d.hidden_size;
   return 2 * std::max(a, std::max(b, c));
+}
+
+static int a8_kmax(const dli_span* s) {
+  const dli_span_desc& d = s->d;
+  return std::max(d.hidden_size, std::max(d.n_heads * d.head_dim, d.intermediate_size));
+}
+size_t dli_span_act_i8_scratch_bytes(const dli_span* s) { return s ? act_i8_bytes(128, a8_kmax(s), 2) : 0; }
+
+int dli_span_set_act_i8(dli_span* s, void* scratch, size_t bytes, float threshold) {
+  DLI_REQUIRE(s, "dli_span_set_act_i8: null span");
+  s->a8_maps.clear();
+  s->a8 = dli_act_i8{};
+  s->a8_threshold = threshold;
+  if (!scratch) return DLI_OK;
+  return act_i8_carve(scratch, bytes, 128, a8_kmax(s), threshold > 0.f ? 2 : 1, &s->a8);
+}
+
+size_t dli_act_i8_bytes(int m, int k, int planes) { return (m > 0 && k > 0 && (planes == 1 || planes == 2)) ? act_i8_bytes(m, k, planes) : 0; }
+int dli_act_i8_carve(void* base, size_t bytes, int m, int k, int planes, dli_act_i8* out) {
+  return act_i8_carve(base, bytes, m, k, planes, out);
+}
+int dli_quantize_act_i8(const void* x_bf16, int64_t ldx, int m, int k, float threshold, const dli_act_i8* dst, dli_stream_t stream) {
+  return launch_quantize_act_i8(x_bf16, ldx, m, k, threshold, dst, (cudaStream_t)stream);
+}
+int dli_gemm_i8(const dli_act_i8* x, const void* q_u8, const float* w_scale, void* out, int64_t ldo, int m, int n, int k, int epilogue,
+                dli_stream_t stream) {
+  return launch_gemm_i8(x, q_u8, w_scale, out, ldo, m, n, k, epilogue, (cudaStream_t)stream);
 }
 
 int dli_gemm_w8(const void* x_bf16, int64_t ldx, const void* q_u8, const float* scale, void* out, int64_t ldo, int m, int n,

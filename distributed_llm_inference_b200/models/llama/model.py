@@ -109,6 +109,9 @@ class LlamaBlock(nn.Module):
         self._ws_key = (0, 0, 0)
         self._scratch_cache: Optional[PartialLlamaSinkCache] = None
         self._dq: Optional[torch.Tensor] = None
+        self._a8_threshold: Optional[float] = None     # quantize_w8(activations="int8"): LLM.int8 threshold, None = bf16 activations
+        self._a8_applied = None
+        self._a8: Optional[torch.Tensor] = None
         self.last_launch_count = 0
 
     # ------------------------------------------------------------------ native span object
@@ -133,6 +136,7 @@ class LlamaBlock(nn.Module):
                          (layer._wqkv, layer.self_attn.o_proj.weight, layer._wgu, layer.mlp.down_proj.weight,
                           layer.input_layernorm.weight, layer.post_attention_layernorm.weight))
         if self._span is not None and ptrs == self._bound_ptrs:
+            self._sync_act_i8(device)
             return
         cfg = self.config
         if self._span is None:
@@ -162,11 +166,35 @@ class LlamaBlock(nn.Module):
                 self._dq = torch.empty(nbytes, dtype=torch.uint8, device=device)
             ffi.check(ffi.lib.dli_span_set_dequant_scratch(self._span, self._dq.data_ptr(), self._dq.numel()))
         self._bound_ptrs = ptrs
+        self._a8_applied = None
+        self._sync_act_i8(device)
 
-    def quantize_w8(self) -> "LlamaBlock":
-        """Row-wise int8 weights for every layer of the span (see ``OptimizedLlamaDecoderLayer.quantize_w8``)."""
+    def _sync_act_i8(self, device):
+        """Hands the span its int8-activation scratch (or takes it away) when the requested mode changed."""
+        want = self._a8_threshold if all(layer.w8 is not None for layer in self.layers) else None
+        if want == self._a8_applied:
+            return
+        ffi = self._ffi()
+        if want is None:
+            ffi.check(ffi.lib.dli_span_set_act_i8(self._span, None, 0, 0.0))
+        else:
+            nbytes = ffi.lib.dli_span_act_i8_scratch_bytes(self._span)
+            if self._a8 is None or self._a8.numel() < nbytes or self._a8.device != device:
+                self._a8 = torch.empty(nbytes, dtype=torch.uint8, device=device)
+            ffi.check(ffi.lib.dli_span_set_act_i8(self._span, self._a8.data_ptr(), self._a8.numel(), float(want)))
+        self._a8_applied = want
+
+    def quantize_w8(self, activations: str = "bf16", threshold: float = 5.0) -> "LlamaBlock":
+        """Row-wise int8 weights for every layer of the span (see ``OptimizedLlamaDecoderLayer.quantize_w8``).
+        ``activations="int8"``: decode steps (chunks of <= 128 tokens) also quantise the ACTIVATIONS per token row and
+        multiply int8 x int8 on the tensor cores, entries with ``|x| >= threshold`` kept in 16 bits -- the arithmetic of
+        the reference's ``Linear8bitLt(threshold=...)`` (utils/model.py:93-123); ``"bf16"`` keeps 16-bit activations."""
+        if activations not in ("bf16", "int8"):
+            raise ValueError("activations must be 'bf16' or 'int8'")
         for layer in self.layers:
-            layer.quantize_w8()
+            if layer.w8 is None:
+                layer.quantize_w8()
+        self._a8_threshold = float(threshold) if activations == "int8" else None
         return self
 
     def __del__(self):

@@ -254,6 +254,45 @@ int dli_span_bind_weights_w8(dli_span* span, int layer, const dli_layer_weights_
 size_t dli_span_dequant_scratch_bytes(const dli_span* span);
 int dli_span_set_dequant_scratch(dli_span* span, void* scratch_bf16, size_t bytes);
 
+/* ------------------------------------------------------------------------------------------------
+ * int8 activations on int8 weights -- the arithmetic of the reference's optimised mode itself: bitsandbytes
+ * Linear8bitLt(threshold, has_fp16_weights=False), utils/model.py:93-123 ("LLM.int8"): per token row the entries below
+ * the threshold are quantised with the row's absmax over those entries (scale = absmax / 127, code = round(x / scale)),
+ * the product runs int8 x int8 -> int32 on the tensor cores (tcgen05.mma.kind::i8) and is scaled by x_scale[m] *
+ * w_scale[n]; the entries at or above the threshold (outliers) do not enter that scale.  bitsandbytes multiplies their
+ * columns in fp16; here they form a SECOND int8 plane of the same row with its own scale (absmax over the outliers /
+ * 127), multiplied against the same weight tiles into a second accumulator -- the outliers are kept to 1/254 of the
+ * row's largest one, at a cost independent of their number.  Decode shapes only (m <= 128).
+ * A dli_act_i8 describes one quantised activation matrix [m, k] in caller-allocated device memory:
+ *   q int8 [m, k] (16-byte aligned, k % 16 == 0), scale fp32 [m], ksum int32 [m, ceil(k / 128)] (sum of the row's codes
+ *   per 128-element block: the weights are stored biased, so the GEMM subtracts 128 * ksum); q2 / scale2 / ksum2 the
+ *   same for the outlier plane, or all NULL for a one-plane activation (no threshold: plain row-wise absmax).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct dli_act_i8 {
+  void* q;
+  float* scale;
+  int32_t* ksum;
+  void* q2;
+  float* scale2;
+  int32_t* ksum2;
+} dli_act_i8;
+/* bytes of one dli_act_i8 with `planes` (1 or 2) planes for up to m rows of k entries (each array 256-byte aligned),
+ * and its carving */
+size_t dli_act_i8_bytes(int m, int k, int planes);
+int dli_act_i8_carve(void* base, size_t bytes, int m, int k, int planes, dli_act_i8* out);
+/* threshold <= 0 or a one-plane destination: every entry goes to the first plane */
+int dli_quantize_act_i8(const void* x_bf16, int64_t ldx, int m, int k, float threshold, const dli_act_i8* dst,
+                        dli_stream_t stream);
+/* out[m, n] (+)= w_scale[n] * sum over planes of scale_p[m] * sum_k q_p[m, k] * (q[n, k] - 128), n % 4 == 0; epilogues
+ * as dli_gemm_w8 (DLI_EPI_SILU_MUL_BF16: q and w_scale hold 2n rows, gate then up) */
+int dli_gemm_i8(const dli_act_i8* x, const void* q_u8, const float* w_scale, void* out, int64_t ldo, int m, int n, int k,
+                int epilogue, dli_stream_t stream);
+/* A span bound with dli_span_bind_weights_w8 runs its decode GEMMs (chunks of <= 128 tokens) in this mode once it has
+ * been given a scratch of dli_span_act_i8_scratch_bytes(span) bytes (256-byte aligned, caller-allocated, borrowed until
+ * replaced or the span is destroyed; NULL switches back to bf16 activations).  threshold <= 0: one plane, no outliers. */
+size_t dli_span_act_i8_scratch_bytes(const dli_span* span);
+int dli_span_set_act_i8(dli_span* span, void* scratch, size_t bytes, float threshold);
+
 /* Bytes of caller-allocated device workspace dli_span_forward needs for chunks of up to max_tokens
  * (= batch * q_len) tokens, batch <= max_batch, context <= max_ctx. */
 size_t dli_span_workspace_bytes(const dli_span* span, int max_tokens, int max_batch, int max_ctx);

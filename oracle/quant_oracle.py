@@ -12,8 +12,10 @@ cannot be (no network, no sm_100 build), so its algorithm is restated here from 
 
 Parity pinning: NONE — there is no bitsandbytes here to run, and the reference has no fixtures for this mode, so this
 file is *unpinned* ("parity unpinned" applies to everything that depends on it).  The B200 path implements the WEIGHT
-half exactly (``quantize_rowwise`` below is what ``dli_quantize_rows_w8`` must reproduce bit for bit) and keeps
-activations in bf16; ``linear_w8`` is its arithmetic in fp32, ``linear_llm_int8`` the reference's for comparison.
+half exactly (``quantize_rowwise`` below is what ``dli_quantize_rows_w8`` must reproduce bit for bit); activations are
+either kept in bf16 (``linear_w8`` is that arithmetic in fp32) or quantised per token row (``quantize_act_rowwise`` /
+``linear_llm_int8_rowwise`` are what ``dli_quantize_act_i8`` / ``dli_gemm_i8`` must reproduce); ``linear_llm_int8`` is
+the reference's column-wise outlier rule for comparison.
 """
 from __future__ import annotations
 
@@ -42,17 +44,47 @@ def linear_w8(x: torch.Tensor, q: torch.Tensor, scale: torch.Tensor) -> torch.Te
     return (x.float() @ q.float().t()) * scale[None, :].float()
 
 
-def linear_llm_int8(x: torch.Tensor, q: torch.Tensor, scale: torch.Tensor, threshold: float = 5.0) -> torch.Tensor:
-    """bitsandbytes MatMul8bitLt.forward for has_fp16_weights=False, restated [recall]: outlier columns in 16 bits, the
-    rest int8 x int8 -> int32 with row-wise activation scales."""
+def quantize_act_rowwise(x: torch.Tensor, threshold: float = 5.0):
+    """LLM.int8 activation quantisation of ``x [m, k]`` as ``dli_quantize_act_i8`` does it, per token row:
+    -> (c1 int8 [m, k], s1 fp32 [m], c2 int8 [m, k], s2 fp32 [m]).  Entries with ``|x| >= threshold`` are outliers: they
+    are 0 in c1 and do not enter s1 = absmax of the remaining entries / 127 (bitsandbytes' row statistics likewise leave
+    them out [recall]); c1 = round(x * (127 / absmax)) clamped to +-127, ties to even.  The outliers form the second
+    plane, quantised the same way with s2 = absmax over the outliers / 127 (c2 is 0 elsewhere)."""
     x = x.float()
-    outlier_cols = (x.abs() >= threshold).any(dim=0) if threshold > 0 else torch.zeros(x.shape[1], dtype=torch.bool)
-    xin = x.clone()
-    xin[:, outlier_cols] = 0
-    sca = xin.abs().amax(dim=1).clamp_min(1e-30)
-    ca = torch.round(xin * (127.0 / sca)[:, None]).clamp_(-127, 127)
-    out = (ca @ q.float().t()) * (sca[:, None] * (scale * 127.0)[None, :] / (127.0 * 127.0))
-    if outlier_cols.any():
-        wd = dequantize_rowwise(q, scale)[:, outlier_cols]
-        out = out + x[:, outlier_cols] @ wd.t()
-    return out
+    out = (x.abs() >= threshold) if threshold > 0 else torch.zeros_like(x, dtype=torch.bool)
+
+    def plane(mask):
+        absmax = torch.where(mask, x.abs(), torch.zeros_like(x)).amax(dim=1)
+        inv = torch.where(absmax > 0, torch.full_like(absmax, 127.0) / absmax, torch.zeros_like(absmax))
+        codes = torch.round(x * inv[:, None]).clamp_(-127, 127)
+        return torch.where(mask, codes, torch.zeros_like(codes)).to(torch.int8), absmax / 127.0
+
+    c1, s1 = plane(~out)
+    c2, s2 = plane(out)
+    return c1, s1, c2, s2
+
+
+def linear_llm_int8_rowwise(x: torch.Tensor, q: torch.Tensor, scale: torch.Tensor, threshold: float = 5.0) -> torch.Tensor:
+    """What ``dli_gemm_i8`` computes: both activation planes int8 x int8 in exact integers, each times the token's plane
+    scale, summed, times the feature's weight scale."""
+    c1, s1, c2, s2 = quantize_act_rowwise(x, threshold)
+    qd = q.double()
+    res = (c1.double() @ qd.t()).float() * s1[:, None] + (c2.double() @ qd.t()).float() * s2[:, None]
+    return res * scale[None, :].float()
+
+
+def linear_llm_int8(x: torch.Tensor, q: torch.Tensor, scale: torch.Tensor, threshold: float = 5.0) -> torch.Tensor:
+    """bitsandbytes MatMul8bitLt.forward for has_fp16_weights=False, restated [recall]: a value at or above the threshold
+    makes its COLUMN an outlier column for every row of the batch; those columns are multiplied in 16 bits against the
+    dequantised weight columns, the rest int8 x int8 -> int32 with row-wise activation scales (row absmax over the
+    entries below the threshold).  ``linear_llm_int8_rowwise`` differs in the outlier columns only: 8 bits relative to
+    the row's largest outlier there (and to the regular scale for the other rows' entries), 16 bits here."""
+    x = x.float()
+    c1, s1, _, _ = quantize_act_rowwise(x, threshold)
+    cols = (x.abs() >= threshold).any(dim=0) if threshold > 0 else torch.zeros(x.shape[1], dtype=torch.bool)
+    c1 = c1.clone()
+    c1[:, cols] = 0
+    res = (c1.double() @ q.double().t()).float() * s1[:, None]
+    if cols.any():
+        res = res + x[:, cols] @ q.float()[:, cols].t()
+    return res * scale[None, :].float()

@@ -57,6 +57,11 @@ class SpanShape:
 # ----------------------------------------------------------------------------------------------
 # elementary ops
 # ----------------------------------------------------------------------------------------------
+
+# The seven linear layers of a decoder layer go through this name, so that the tests of the quantised modes can swap in
+# the arithmetic of oracle/quant_oracle.py (int8 weights and/or activations); by default it is the reference's nn.Linear.
+LINEAR = F.linear
+
 def rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float = 1e-6) -> torch.Tensor:
     """transformers 4.43.3 ``LlamaRMSNorm.forward`` as called at modules.py:162,179."""
     dt = x.dtype
@@ -275,9 +280,9 @@ def attention_forward(
     """``OptimizedLlamaInferenceAttention.forward`` (modules.py:36-114), pretraining_tp == 1."""
     H, KV, hd = shape.num_attention_heads, shape.num_key_value_heads, shape.head_dim
     bsz, q_len, _ = x.shape
-    q = F.linear(x, w.q_proj).view(bsz, q_len, H, hd).transpose(1, 2)      # :61,67
-    k = F.linear(x, w.k_proj).view(bsz, q_len, KV, hd).transpose(1, 2)     # :62,68
-    v = F.linear(x, w.v_proj).view(bsz, q_len, KV, hd).transpose(1, 2)     # :63,69
+    q = LINEAR(x, w.q_proj).view(bsz, q_len, H, hd).transpose(1, 2)      # :61,67
+    k = LINEAR(x, w.k_proj).view(bsz, q_len, KV, hd).transpose(1, 2)     # :62,68
+    v = LINEAR(x, w.v_proj).view(bsz, q_len, KV, hd).transpose(1, 2)     # :63,69
     q, k = apply_rotary_pos_emb(q, k, cos, sin)                            # :73-76
     if cache is not None:                                                  # :78-85
         k, v = cache.update(k, v, layer_idx=local_layer_idx,
@@ -290,7 +295,7 @@ def attention_forward(
     p = F.softmax(s, dim=-1, dtype=torch.float32).to(q.dtype)              # :96
     o = torch.matmul(p, v)                                                 # :97
     o = o.transpose(1, 2).contiguous().reshape(bsz, q_len, -1)             # :105
-    return F.linear(o, w.o_proj)                                           # :112
+    return LINEAR(o, w.o_proj)                                           # :112
 
 
 def layer_forward(shape, w, x, generation_id, cos, sin, mask, cache, local_layer_idx):
@@ -301,7 +306,7 @@ def layer_forward(shape, w, x, generation_id, cos, sin, mask, cache, local_layer
     h = h + residual                                                                   # :173
     residual = h
     h = rmsnorm(h + residual, w.post_attention_layernorm, shape.rms_eps)               # :179 (D6: norm of 2h)
-    h = F.linear(F.silu(F.linear(h, w.gate_proj)) * F.linear(h, w.up_proj), w.down_proj)  # :181 LlamaMLP
+    h = LINEAR(F.silu(LINEAR(h, w.gate_proj)) * LINEAR(h, w.up_proj), w.down_proj)  # :181 LlamaMLP
     return h + residual                                                                # :182
 
 

@@ -71,12 +71,8 @@ def test_gemm_w8_matches_oracle(m, n, k, epi):
     assert err <= tol * scale + 1e-5, msg
 
 
-@pytest.mark.parametrize("shape_name,B,L1,L2", [("test_hd128", 2, 40, 3), ("test_gqa", 2, 200, 150)])
-def test_quantised_span_matches_oracle_on_dequantised_weights(shape_name, B, L1, L2):
-    shp = syn.SHAPES[shape_name]
-    W = syn.make_span_weights(shp, [0, 1, 2], norm_jitter=0.1)
-    blk = convert_to_optimized_block(gpu_make_span(shp, W, "eager", "float"), quantize=True)
-    assert all(layer.w8 is not None and layer.self_attn.q_proj.weight.numel() == 0 for layer in blk.layers)
+def _dequantised_weights(W):
+    """The weights the GPU path multiplies by: every fused matrix quantised row-wise and widened again (oracle side)."""
     Wd = []
     for w in W:                                                    # the oracle sees the weights the GPU path multiplies by
         d = dict(w)
@@ -93,7 +89,16 @@ def test_quantised_span_matches_oracle_on_dequantised_weights(shape_name, B, L1,
             else:
                 d[name] = dq
         Wd.append(d)
-    osp = oracle_make_span(shp, Wd, "eager", "float")
+    return Wd
+
+
+@pytest.mark.parametrize("shape_name,B,L1,L2", [("test_hd128", 2, 40, 3), ("test_gqa", 2, 200, 150)])
+def test_quantised_span_matches_oracle_on_dequantised_weights(shape_name, B, L1, L2):
+    shp = syn.SHAPES[shape_name]
+    W = syn.make_span_weights(shp, [0, 1, 2], norm_jitter=0.1)
+    blk = convert_to_optimized_block(gpu_make_span(shp, W, "eager", "float"), quantize=True)
+    assert all(layer.w8 is not None and layer.self_attn.q_proj.weight.numel() == 0 for layer in blk.layers)
+    osp = oracle_make_span(shp, _dequantised_weights(W), "eager", "float")
     gc, oc = PartialLlamaSinkCache(4096, 4, capacity_tokens=4096), so.SinkCacheOracle(4096, 4)
     pos = 0
     for step, L in enumerate([L1, L2, 1, 1]):
