@@ -395,7 +395,7 @@ def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layer
 
     blk = build_span(shape, layer_ids, dev, max_positions=max(8192, total_ctx + 64))
     if w8:
-        blk.quantize_w8(activations="int8" if a8 else "bf16")   # row-wise int8 weights (convert_to_optimized_block(quantize=True))
+        blk.quantize_w8(activations="int8" if a8 else "bf16", threshold=args.a8_threshold)   # row-wise int8 weights (convert_to_optimized_block(quantize=True))
         free_cuda()
     cache = PartialLlamaSinkCache(1 << 20, 4, page_tokens=page_tokens,
                                   capacity_tokens=n_mb * batch * (total_ctx + 16) + batch * 192 +
@@ -557,7 +557,7 @@ def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layer
     sb = decode_step_bytes(shape, len(layer_ids), batch, ctx_mid, w8=w8)
     stage_gbs = sb["total"] / (ms_per_step / n_mb * 1e-3) / 1e9
     res = {
-        "model": shape.name, "weights": ("int8 rows + fp32 scales, " + ("int8 activations per token, threshold 5.0 (LLM.int8)" if a8 else "bf16 activations")) if w8 else "bf16", "layers_total": n_total, "layers_per_stage": len(layer_ids), "batch": batch, "micro_batches": n_mb,
+        "model": shape.name, "weights": ("int8 rows + fp32 scales, " + ("int8 activations per token, threshold %g (LLM.int8)" % args.a8_threshold if a8 else "bf16 activations")) if w8 else "bf16", "layers_total": n_total, "layers_per_stage": len(layer_ids), "batch": batch, "micro_batches": n_mb,
         "prompt": prompt, "value": round(value, 1), "ms_per_step": round(ms_per_step, 4),
         "ms_per_stage_step": round(ms_per_step / n_mb, 4), "p50_ms_per_token": round(lat[len(lat) // 2] / n_mb, 4),
         "tokens_per_step": tokens_per_step, "steps": K, "launches": int(launches), "clocks": clocks,
@@ -892,7 +892,7 @@ def run_ours(args):
     n_mb = args.micro_batches or world   # micro-batches in flight (default: the pipeline depth)
     main = run_workload(ctx, MODEL, BATCH, PROMPT, n_mb, args.layers, K, W, prefill_chunk=args.prefill_chunk, full=not (args.w8 or args.a8),
                         want_e2e=not args.no_e2e, page_tokens=args.page_tokens, w8=args.w8 or args.a8, a8=args.a8)
-    w8_rec = None
+    w8_rec = a8_rec = None
     if world == 1 and not (args.w8 or args.a8) and not args.no_w8:
         # the same workload with the weights stored as row-wise int8 (the reference's optimised mode keeps its weights
         # in that format, utils/model.py:93-123): a second, clearly labelled record -- the headline stays bf16
@@ -900,6 +900,12 @@ def run_ours(args):
         w8_rec = {k: r8[k] for k in ("weights", "value", "ms_per_step", "p50_ms_per_token", "stage_roofline", "launches",
                                      "prefill_first_call_tokens_per_sec")}
         w8_rec["vs_bf16"] = round(r8["value"] / main["value"], 3)
+        # ... and with the activations quantised per token as well: the arithmetic of that mode itself (LLM.int8,
+        # convert_to_optimized_block(quantize=True)); int8 x int8 on the tensor cores, no widening of the weights
+        ra = run_workload(ctx, MODEL, BATCH, PROMPT, n_mb, args.layers, min(K, 32), 3, w8=True, a8=True)
+        a8_rec = {k: ra[k] for k in ("weights", "value", "ms_per_step", "p50_ms_per_token", "stage_roofline", "launches",
+                                     "prefill_first_call_tokens_per_sec")}
+        a8_rec["vs_bf16"] = round(ra["value"] / main["value"], 3)
     configs = None
     if world > 1 and not args.no_configs and MODEL == "7b" and not args.layers:
         configs = {}
@@ -947,7 +953,7 @@ def run_ours(args):
             "cpu_baseline": cpu, "decode_batch1": main.get("decode_batch1"),
             "stage_step_alone_ms": main.get("stage_step_alone_ms"),
             "pipeline_vs_slowest_stage": main.get("pipeline_vs_slowest_stage"),
-            "decode_int8_weights": w8_rec,
+            "decode_int8_weights": w8_rec, "decode_llm_int8": a8_rec,
             "pipeline_parity": parity, "configs": configs,
         }
         print(json.dumps(line), flush=True)
@@ -1010,6 +1016,7 @@ def main():
     ap.add_argument("--exp-c5-chunks", default=None, help="experiments: run config C5 alone with these chunk sizes (comma-separated)")
     ap.add_argument("--w8", action="store_true", help="run the main workload with row-wise int8 weights (experiments)")
     ap.add_argument("--a8", action="store_true", help="with int8 weights also quantise the activations per token (LLM.int8; experiments)")
+    ap.add_argument("--a8-threshold", type=float, default=5.0, help="LLM.int8 outlier threshold of --a8 (0: one plane, no outliers)")
     ap.add_argument("--no-w8", action="store_true", help="one GPU: skip the decode_int8_weights record")
     ap.add_argument("--no-chain", action="store_true", help="experiments: a stream barrier in front of every stage step instead "
                                                             "of chaining the micro-batches' steps with programmatic dependent launch")

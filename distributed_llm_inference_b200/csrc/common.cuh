@@ -193,13 +193,21 @@ int launch_decode_attention_masked(const __nv_bfloat16* q, __nv_bfloat16* out, c
                                    int hd, const AttnMask& mask, float* scratch, size_t scratch_bytes, cudaStream_t st);
 
 // ---- other launchers ----------------------------------------------------------------------------------
+// RMSNorm launches that also leave their output quantised for the int8 x int8 GEMM that follows (norm_rope.cu)
+struct QuantArgs {
+  dli_act_i8 d;      // d.q == nullptr: no quantised output
+  float threshold;
+  int k_blocks;      // ceil(h / 128)
+};
+bool rmsnorm_can_quantize(int h);
 int launch_rmsnorm_entry(const void* x, const __nv_bfloat16* w, __nv_bfloat16* y, float* resid_out, int rows, int h, float eps,
-                         const EntryArgs& ea, cudaStream_t st);
+                         const EntryArgs& ea, cudaStream_t st, const QuantArgs* quant = nullptr);
 int launch_argmax(const float* logits, int32_t* tokens_out, int batch, int vocab, cudaStream_t st, const StepState* adv,
                   const ExitArgs& xa);
 int launch_flag_wait(const uint32_t* flag, uint32_t at_least, uint32_t* state, unsigned long long timeout_ns, cudaStream_t st);
 int launch_rmsnorm(const void* x, bool x_is_f32, const __nv_bfloat16* w, __nv_bfloat16* y, float* resid_out,
-                   __nv_bfloat16* copy_out, int rows, int h, float eps, float pre_scale, cudaStream_t st);
+                   __nv_bfloat16* copy_out, int rows, int h, float eps, float pre_scale, cudaStream_t st,
+                   const QuantArgs* quant = nullptr);
 int launch_rope_kv_append(float* qkv, bool zero_after, const float* cos, const float* sin, __nv_bfloat16* q_out,
                           const KvView& kv, int batch, int q_len, int H, int KV, int hd, cudaStream_t st,
                           const long long* pos = nullptr);  // pos: cos/sin are tables, first row = *pos
@@ -292,6 +300,27 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 }
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
+
+// LLM.int8 activation codes of 8 consecutive entries of a row (gemm_i8.cu): entries below `thr` go to the first plane
+// (code = round(v * inv)), the others to the outlier plane (round(v * inv2)); an entry is 0 in the plane it does not
+// belong to.  p1 / p2: the 8 codes of each plane as bytes; s1 / s2: their sums.
+__device__ __forceinline__ void i8_codes8(const float (&v)[8], float thr, float inv, float inv2, uint2& p1, uint2& p2, int& s1, int& s2) {
+  uint32_t o[2] = {0, 0}, o2[2] = {0, 0};
+  s1 = 0;
+  s2 = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const bool out = fabsf(v[j]) >= thr;
+    const int c = max(-127, min(127, __float2int_rn(v[j] * (out ? inv2 : inv))));
+    const int c1 = out ? 0 : c, c2 = out ? c : 0;
+    s1 += c1;
+    s2 += c2;
+    o[j >> 2] |= ((uint32_t)c1 & 0xffu) << (8 * (j & 3));
+    o2[j >> 2] |= ((uint32_t)c2 & 0xffu) << (8 * (j & 3));
+  }
+  p1 = make_uint2(o[0], o[1]);
+  p2 = make_uint2(o2[0], o2[1]);
+}
 // ---- cross-GPU flags (system scope) ---------------------------------------------------------------------
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;

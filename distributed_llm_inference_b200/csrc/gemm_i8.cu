@@ -11,7 +11,7 @@
 // split-K over gridDim.z -- at half the weight bytes and with no conversion work.
 //   * Outliers are a SECOND int8 plane of the activation (c2: the entries at or above the threshold, quantised with the
 //     row's absmax over those entries; c1 holds 0 there and vice versa): every weight tile in shared memory is
-//     multiplied by both planes into two accumulators.  bitsandbytes multiplies its outlier columns in fp16; a second
+//     multiplied by both planes at once (their tiles are adjacent rows of the B operand: one MMA of N = 2 BN).  bitsandbytes multiplies its outlier columns in fp16; a second
 //     8-bit plane keeps them to 1/254 of the row's largest outlier -- the resolution the regular entries have relative
 //     to the threshold -- at a cost that does not depend on how many there are (a first cut added them in the epilogue
 //     from per-row lists, reading weight columns byte by byte: with ~100 scattered outliers per row, as silu(gate) * up
@@ -25,6 +25,7 @@
 #include "tc_ptx.cuh"
 
 #include <algorithm>
+#include <stdlib.h>
 
 namespace dli {
 
@@ -66,8 +67,8 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
                const I8Params p) {
   constexpr int B_TILE_BYTES = BN * I8_BK;
   constexpr int STAGE_BYTES = I8_A_TILE_BYTES + PLANES * B_TILE_BYTES;
-  constexpr int ACC_COLS = BN < 32 ? 32 : BN;
-  constexpr int TMEM_COLS = PLANES * ACC_COLS;   // 32 .. 256: a power of two
+  constexpr int MMA_N = PLANES * BN;              // both planes are ONE MMA: their tiles are adjacent rows of the B operand
+  constexpr int TMEM_COLS = MMA_N < 32 ? 32 : MMA_N;   // accumulator columns [0, BN) = first plane, [BN, 2 BN) = outlier plane
   constexpr bool SILU = EPI == DLI_EPI_SILU_MUL_BF16;
 
   extern __shared__ uint8_t smem_raw[];
@@ -154,8 +155,8 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
         if (++s == stages) { s = 0; ph ^= 1; }
       }
     } else if (warp == 1) {
-      // ===== MMA issuer: every weight tile against both activation planes =====
-      constexpr uint32_t idesc = umma_idesc_i8(BN);
+      // ===== MMA issuer: every weight tile against both activation planes (one MMA of N = 2 BN) =====
+      constexpr uint32_t idesc = umma_idesc_i8(MMA_N);
       int s = 0;
       uint32_t ph = 0;
       for (int kb = kb0; kb < kb1; ++kb) {
@@ -165,11 +166,8 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
           const uint32_t a_src = tiles + s * STAGE_BYTES;
           const uint64_t adesc = umma_desc_sw128(a_src), bdesc = umma_desc_sw128(a_src + I8_A_TILE_BYTES);
 #pragma unroll
-          for (int k = 0; k < I8_BK / I8_UMMA_K; ++k) {  // 32 int8 = 32 bytes along K inside the swizzle atom: +2 in the (addr >> 4) field
+          for (int k = 0; k < I8_BK / I8_UMMA_K; ++k)   // 32 int8 = 32 bytes along K inside the swizzle atom: +2 in the (addr >> 4) field
             umma_i8(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-            if (PLANES == 2)
-              umma_i8(tmem_d + ACC_COLS, adesc + 2 * k, bdesc + (B_TILE_BYTES >> 4) + 2 * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-          }
           umma_commit(empty0 + 8 * s);
           if (kb + 1 == kb1) umma_commit(tmem_full);
         }
@@ -208,7 +206,7 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tma_w, const __grid_constant_
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 16) {
         tmem_ld16(taddr + c0, v);
-        if (PLANES == 2) tmem_ld16(taddr + ACC_COLS + c0, u);
+        if (PLANES == 2) tmem_ld16(taddr + BN + c0, u);
         tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
@@ -310,7 +308,12 @@ int launch_gemm_i8_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const C
   p.k_blocks = g.k_blocks;
   p.kb_per_split = g.kb_per_split;
   const int stage_bytes = I8_A_TILE_BYTES + planes * g.bn * I8_BK;
-  int stages = std::min(I8_MAX_STAGES, (112 * 1024 - 2048) / stage_bytes);   // two CTAs per SM
+  static int ring_kb = 0;   // shared memory per CTA for the operand ring; experiments build: DLI_I8_RING_KB
+  if (!ring_kb) {
+    const char* e = exp_env("DLI_I8_RING_KB");
+    ring_kb = e ? std::max(24, atoi(e)) : 110;
+  }
+  int stages = std::min(I8_MAX_STAGES, (ring_kb * 1024) / stage_bytes);   // 110 KB: two CTAs per SM
   stages = std::max(2, std::min(stages, g.kb_per_split));
   while (stages * stage_bytes < g.bn * 512) ++stages;   // the epilogue's transposition buffer overlays the ring
   p.stages = stages;
@@ -363,24 +366,35 @@ int launch_gemm_i8(const dli_act_i8* x, const void* q, const float* w_scale, voi
 // at or above it.  Pass 2: the two planes of codes (round to nearest even, clamped to +-127; an entry is 0 in the plane
 // it does not belong to) and the per-128-block sums of the codes.  `x` is read after the dependency wait.
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) quantize_act_i8_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, int k, int k_blocks,
-                                                              float threshold, dli_act_i8 d) {
-  __shared__ float red[2][8];
+constexpr int QA_THREADS = 512;
+constexpr int QA_CHUNKS = 8;   // rows of up to 512 * 8 * 8 = 32768 entries are read once and kept in registers
+__global__ void __launch_bounds__(QA_THREADS) quantize_act_i8_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, int k, int k_blocks,
+                                                                     float threshold, dli_act_i8 d) {
+  __shared__ float red[2][QA_THREADS / 32];
   pdl_trigger();
   const int row = blockIdx.x;
   const __nv_bfloat16* src = x + (long long)row * ldx;
   const bool two = d.q2 != nullptr && threshold > 0.f;
   const float thr = two ? threshold : INFINITY;
+  const int i0 = threadIdx.x * 8;
   pdl_wait();
-  float mx = 0.f, mo = 0.f;
-  for (int i = threadIdx.x * 8; i < k; i += 256 * 8) {
-    const uint4 a = *reinterpret_cast<const uint4*>(src + i);
-    const uint32_t u[4] = {a.x, a.y, a.z, a.w};
+  uint4 a[QA_CHUNKS];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float v0 = fabsf(bf16_lo(u[j])), v1 = fabsf(bf16_hi(u[j]));
-      if (v0 < thr) mx = fmaxf(mx, v0); else mo = fmaxf(mo, v0);
-      if (v1 < thr) mx = fmaxf(mx, v1); else mo = fmaxf(mo, v1);
+  for (int c = 0; c < QA_CHUNKS; ++c) {
+    const int i = i0 + c * QA_THREADS * 8;
+    if (i < k) a[c] = *reinterpret_cast<const uint4*>(src + i);
+  }
+  float mx = 0.f, mo = 0.f;
+#pragma unroll
+  for (int c = 0; c < QA_CHUNKS; ++c) {
+    if (i0 + c * QA_THREADS * 8 < k) {
+      const uint32_t u[4] = {a[c].x, a[c].y, a[c].z, a[c].w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float v0 = fabsf(bf16_lo(u[j])), v1 = fabsf(bf16_hi(u[j]));
+        if (v0 < thr) mx = fmaxf(mx, v0); else mo = fmaxf(mo, v0);
+        if (v1 < thr) mx = fmaxf(mx, v1); else mo = fmaxf(mo, v1);
+      }
     }
   }
   mx = warp_max(mx);
@@ -390,7 +404,7 @@ __global__ void __launch_bounds__(256) quantize_act_i8_kernel(const __nv_bfloat1
   mx = red[0][0];
   mo = red[1][0];
 #pragma unroll
-  for (int i = 1; i < 8; ++i) { mx = fmaxf(mx, red[0][i]); mo = fmaxf(mo, red[1][i]); }
+  for (int i = 1; i < QA_THREADS / 32; ++i) { mx = fmaxf(mx, red[0][i]); mo = fmaxf(mo, red[1][i]); }
   const float inv = mx > 0.f ? 127.0f / mx : 0.f, inv2 = mo > 0.f ? 127.0f / mo : 0.f;
   if (threadIdx.x == 0) {
     d.scale[row] = mx / 127.0f;
@@ -400,27 +414,18 @@ __global__ void __launch_bounds__(256) quantize_act_i8_kernel(const __nv_bfloat1
   int8_t* dst2 = (int8_t*)d.q2 + (long long)row * k;
   int32_t* ks = d.ksum + (long long)row * k_blocks;
   int32_t* ks2 = d.ksum2 + (long long)row * k_blocks;
-  // a sweep covers 2048 entries = 16 blocks of 128; 16 consecutive threads share a block (whole sweeps: every lane takes part in the shuffles)
-  for (int i0 = 0; i0 < k; i0 += 256 * 8) {
-    const int i = i0 + threadIdx.x * 8;
+#pragma unroll
+  for (int c = 0; c < QA_CHUNKS; ++c) {   // 16 consecutive threads share a 128-entry block; every lane takes part in the shuffles
+    const int i = i0 + c * QA_THREADS * 8;
+    if (c * QA_THREADS * 8 >= k) break;   // uniform over the CTA
     int sum = 0, sum2 = 0;
     if (i < k) {
-      const uint4 a = *reinterpret_cast<const uint4*>(src + i);
-      const uint32_t u[4] = {a.x, a.y, a.z, a.w};
-      uint32_t o[2] = {0, 0}, o2[2] = {0, 0};
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float v = (j & 1) ? bf16_hi(u[j >> 1]) : bf16_lo(u[j >> 1]);
-        const bool out = fabsf(v) >= thr;
-        const int c = max(-127, min(127, __float2int_rn(v * (out ? inv2 : inv))));
-        const int c1 = out ? 0 : c, c2 = out ? c : 0;
-        sum += c1;
-        sum2 += c2;
-        o[j >> 2] |= ((uint32_t)c1 & 0xffu) << (8 * (j & 3));
-        o2[j >> 2] |= ((uint32_t)c2 & 0xffu) << (8 * (j & 3));
-      }
-      *reinterpret_cast<uint2*>(dst + i) = make_uint2(o[0], o[1]);
-      if (d.q2) *reinterpret_cast<uint2*>(dst2 + i) = make_uint2(o2[0], o2[1]);
+      const float v[8] = {bf16_lo(a[c].x), bf16_hi(a[c].x), bf16_lo(a[c].y), bf16_hi(a[c].y),
+                          bf16_lo(a[c].z), bf16_hi(a[c].z), bf16_lo(a[c].w), bf16_hi(a[c].w)};
+      uint2 p1, p2;
+      i8_codes8(v, thr, inv, inv2, p1, p2, sum, sum2);
+      *reinterpret_cast<uint2*>(dst + i) = p1;
+      if (d.q2) *reinterpret_cast<uint2*>(dst2 + i) = p2;
     }
 #pragma unroll
     for (int off = 8; off > 0; off >>= 1) {
@@ -438,7 +443,8 @@ int launch_quantize_act_i8(const void* x_bf16, long long ldx, int m, int k, floa
   DLI_REQUIRE(x_bf16 && dst && dst->q && dst->scale && dst->ksum, "dli_quantize_act_i8: null pointer");
   DLI_REQUIRE(!dst->q2 || (dst->scale2 && dst->ksum2), "dli_quantize_act_i8: the outlier plane needs its scales and sums");
   DLI_REQUIRE(m > 0 && k > 0 && k % 16 == 0 && ldx % 8 == 0, "dli_quantize_act_i8: m=%d k=%d ldx=%lld (k %% 16 == 0, ldx %% 8 == 0)", m, k, ldx);
-  return launch_kernel("quantize_act_i8_kernel", quantize_act_i8_kernel, dim3((unsigned)m), dim3(256), 0, st,
+  DLI_REQUIRE(k <= QA_THREADS * 8 * QA_CHUNKS, "dli_quantize_act_i8: rows of more than %d entries are not supported (k = %d)", QA_THREADS * 8 * QA_CHUNKS, k);
+  return launch_kernel("quantize_act_i8_kernel", quantize_act_i8_kernel, dim3((unsigned)m), dim3(QA_THREADS), 0, st,
                        (const __nv_bfloat16*)x_bf16, ldx, k, (k + I8_BK - 1) / I8_BK, threshold, *dst);
 }
 

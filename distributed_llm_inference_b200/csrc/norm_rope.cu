@@ -45,8 +45,9 @@ template <bool F32IN, bool ENTRY = false>
 __global__ void __launch_bounds__(NORM_THREADS) rmsnorm_kernel(const void* __restrict__ x, const __nv_bfloat16* __restrict__ w,
                                                                __nv_bfloat16* __restrict__ y, float* __restrict__ resid_out,
                                                                __nv_bfloat16* __restrict__ copy_out, int h, float eps,
-                                                               float s, EntryArgs ea) {
+                                                               float s, EntryArgs ea, QuantArgs qa) {
   __shared__ float red[NORM_THREADS / 32];
+  __shared__ float red_q[2][NORM_THREADS / 32];
   pdl_trigger();
   if (threadIdx.x == 0) DLI_TRACE_EV(TR_RMSNORM, 0);
   long long in_base = (long long)blockIdx.x * h;
@@ -101,16 +102,72 @@ __global__ void __launch_bounds__(NORM_THREADS) rmsnorm_kernel(const void* __res
 #pragma unroll
     for (int k = 0; k < NORM_THREADS / 32; ++k) t += red[k];  // same order in every thread: one value per row
     const float r = rsqrtf(t * s * s / (float)h + eps) * s;
+    uint32_t ob[NORM_CHUNKS][4];
 #pragma unroll
     for (int c = 0; c < NORM_CHUNKS; ++c) {
       const int i = i0 + c * NORM_THREADS * 8;
       if (i < h) {
         const float g[8] = {bf16_lo(wv[c].x), bf16_hi(wv[c].x), bf16_lo(wv[c].y), bf16_hi(wv[c].y),
                             bf16_lo(wv[c].z), bf16_hi(wv[c].z), bf16_lo(wv[c].w), bf16_hi(wv[c].w)};
-        uint32_t o[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) o[j] = pack_bf16(g[2 * j] * (v[c][2 * j] * r), g[2 * j + 1] * (v[c][2 * j + 1] * r));
-        *reinterpret_cast<uint4*>(y + base + i) = make_uint4(o[0], o[1], o[2], o[3]);
+        for (int j = 0; j < 4; ++j) ob[c][j] = pack_bf16(g[2 * j] * (v[c][2 * j] * r), g[2 * j + 1] * (v[c][2 * j + 1] * r));
+        *reinterpret_cast<uint4*>(y + base + i) = make_uint4(ob[c][0], ob[c][1], ob[c][2], ob[c][3]);
+      }
+    }
+    if (qa.d.q != nullptr) {
+      // the row also leaves quantised for the int8 x int8 GEMM that follows (what quantize_act_i8_kernel would make of y)
+      const float thr = (qa.d.q2 != nullptr && qa.threshold > 0.f) ? qa.threshold : INFINITY;
+      float mx = 0.f, mo = 0.f;
+#pragma unroll
+      for (int c = 0; c < NORM_CHUNKS; ++c) {
+        if (i0 + c * NORM_THREADS * 8 < h) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float v0 = fabsf(bf16_lo(ob[c][j])), v1 = fabsf(bf16_hi(ob[c][j]));
+            if (v0 < thr) mx = fmaxf(mx, v0); else mo = fmaxf(mo, v0);
+            if (v1 < thr) mx = fmaxf(mx, v1); else mo = fmaxf(mo, v1);
+          }
+        }
+      }
+      mx = warp_max(mx);
+      mo = warp_max(mo);
+      if ((threadIdx.x & 31) == 0) { red_q[0][threadIdx.x >> 5] = mx; red_q[1][threadIdx.x >> 5] = mo; }
+      __syncthreads();
+      mx = red_q[0][0];
+      mo = red_q[1][0];
+#pragma unroll
+      for (int k = 1; k < NORM_THREADS / 32; ++k) { mx = fmaxf(mx, red_q[0][k]); mo = fmaxf(mo, red_q[1][k]); }
+      const float inv = mx > 0.f ? 127.0f / mx : 0.f, inv2 = mo > 0.f ? 127.0f / mo : 0.f;
+      const long long row = blockIdx.x;
+      if (threadIdx.x == 0) {
+        qa.d.scale[row] = mx / 127.0f;
+        if (qa.d.q2) qa.d.scale2[row] = mo / 127.0f;
+      }
+      int8_t* dst = (int8_t*)qa.d.q + row * h;
+      int8_t* dst2 = (int8_t*)qa.d.q2 + row * h;
+      int32_t* ks = qa.d.ksum + row * qa.k_blocks;
+      int32_t* ks2 = qa.d.ksum2 + row * qa.k_blocks;
+#pragma unroll
+      for (int c = 0; c < NORM_CHUNKS; ++c) {   // 16 consecutive threads share a 128-entry block; every lane takes part in the shuffles
+        const int i = i0 + c * NORM_THREADS * 8;
+        int sum = 0, sum2 = 0;
+        if (i < h) {
+          const float f[8] = {bf16_lo(ob[c][0]), bf16_hi(ob[c][0]), bf16_lo(ob[c][1]), bf16_hi(ob[c][1]),
+                              bf16_lo(ob[c][2]), bf16_hi(ob[c][2]), bf16_lo(ob[c][3]), bf16_hi(ob[c][3])};
+          uint2 p1, p2;
+          i8_codes8(f, thr, inv, inv2, p1, p2, sum, sum2);
+          *reinterpret_cast<uint2*>(dst + i) = p1;
+          if (qa.d.q2) *reinterpret_cast<uint2*>(dst2 + i) = p2;
+        }
+#pragma unroll
+        for (int off = 8; off > 0; off >>= 1) {
+          sum += __shfl_xor_sync(0xffffffffu, sum, off);
+          sum2 += __shfl_xor_sync(0xffffffffu, sum2, off);
+        }
+        if ((threadIdx.x & 15) == 0 && i < h) {
+          ks[i >> 7] = sum;
+          if (qa.d.q2) ks2[i >> 7] = sum2;
+        }
       }
     }
     if (threadIdx.x == 0) DLI_TRACE_EV(TR_RMSNORM, 2);
@@ -156,22 +213,27 @@ __global__ void __launch_bounds__(NORM_THREADS) rmsnorm_kernel(const void* __res
   }
 }
 
+// quant: also leave the rows quantised for the int8 x int8 GEMM (rows of up to 8192 entries only: rmsnorm_can_quantize)
+bool rmsnorm_can_quantize(int h) { return h <= NORM_THREADS * 8 * NORM_CHUNKS && h % 16 == 0; }
+
 int launch_rmsnorm(const void* x, bool x_is_f32, const __nv_bfloat16* w, __nv_bfloat16* y, float* resid_out,
-                   __nv_bfloat16* copy_out, int rows, int h, float eps, float pre_scale, cudaStream_t st) {
+                   __nv_bfloat16* copy_out, int rows, int h, float eps, float pre_scale, cudaStream_t st, const QuantArgs* quant) {
   DLI_REQUIRE(x && w && y, "dli_rmsnorm: null pointer");
   DLI_REQUIRE(rows > 0 && h > 0 && h % 8 == 0, "dli_rmsnorm: rows=%d h=%d (h must be a positive multiple of 8)", rows, h);
+  DLI_REQUIRE(!quant || rmsnorm_can_quantize(h), "rmsnorm with quantised output: h = %d not supported", h);
   return launch_kernel("rmsnorm_kernel", x_is_f32 ? rmsnorm_kernel<true> : rmsnorm_kernel<false>, dim3(rows),
-                       dim3(NORM_THREADS), 0, st, x, w, y, resid_out, copy_out, h, eps, pre_scale, EntryArgs{});
+                       dim3(NORM_THREADS), 0, st, x, w, y, resid_out, copy_out, h, eps, pre_scale, EntryArgs{},
+                       quant ? *quant : QuantArgs{});
 }
 
 int launch_rmsnorm_entry(const void* x, const __nv_bfloat16* w, __nv_bfloat16* y, float* resid_out, int rows, int h, float eps,
-                         const EntryArgs& ea, cudaStream_t st) {
+                         const EntryArgs& ea, cudaStream_t st, const QuantArgs* quant) {
   DLI_REQUIRE(x && w && y && resid_out, "stage step entry: null pointer");
   DLI_REQUIRE(rows > 0 && h > 0 && h % 8 == 0 && h <= NORM_THREADS * 8 * NORM_CHUNKS,
               "stage step entry: rows=%d h=%d (h must be a multiple of 8, at most %d)", rows, h, NORM_THREADS * 8 * NORM_CHUNKS);
   DLI_REQUIRE(!ea.wait_flag || ea.state, "stage step entry: a wait flag needs the step state");
   return launch_kernel("rmsnorm_kernel<entry>", rmsnorm_kernel<false, true>, dim3(rows), dim3(NORM_THREADS), 0, st, x, w, y,
-                       resid_out, (__nv_bfloat16*)nullptr, h, eps, 1.0f, ea);
+                       resid_out, (__nv_bfloat16*)nullptr, h, eps, 1.0f, ea, quant ? *quant : QuantArgs{});
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -126,6 +126,7 @@ struct dli_span {
   std::vector<dli::ScratchMaps> dq_maps;
   dli_act_i8 a8{};                       // int8 activations (dli_span_set_act_i8): the one quantised operand of the GEMM about to run
   float a8_threshold = 0.f;
+  bool a8_ready = false;                 // the RMSNorm launch just issued has already left its output quantised in a8
   std::vector<dli::ActMapKey> a8_maps;   // uint8 maps over a8.q, keyed by (rows, cols, box)
   const void* head_ptr = nullptr;        // lm_head matrix the maps below describe (dli_stage_decode_step)
   int head_vocab = 0;
@@ -244,7 +245,9 @@ static int span_gemm(dli_span* s, const void* x, const WeightMaps& wm, void* out
   if (w8 && w8->q) {
     if (m > 128 || epilogue == DLI_EPI_QKV_ROPE_INTERNAL) return span_gemm_dequant(s, x, *w8, out, ldo, m, n, k, epilogue, st, rope);
     if (s->a8.q) {  // int8 activations: quantise the operand (one CTA per token), then the kind::i8 GEMM
-      int rc8 = launch_quantize_act_i8(x, k, m, k, s->a8_threshold, &s->a8, st);
+      static const bool skip_quant = exp_env("DLI_A8_SKIP_QUANT") != nullptr;   // experiments build only (results are garbage)
+      int rc8 = (s->a8_ready || skip_quant) ? DLI_OK : launch_quantize_act_i8(x, k, m, k, s->a8_threshold, &s->a8, st);
+      s->a8_ready = false;
       if (rc8) return rc8;
       const GemmPlan gi = plan_gemm_i8(m, n, k, epilogue);
       auto xq_map = [&](const void* base, const CUtensorMap** out_map) -> int {
@@ -657,22 +660,28 @@ static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int 
   // that what precedes it in the stream belongs to OTHER generations (micro-batches of a pipeline round): then the
   // steps are chained like the kernels inside one
   if (!(io && io->chain)) pdl_barrier_next_launch();
+  // int8 activations: the two RMSNorm launches of a layer leave their output quantised for the GEMM that follows
+  const QuantArgs qnorm{s->a8, s->a8_threshold, (h + 127) / 128};
+  s->a8_ready = false;
   for (int j = 0; j < d.n_layers; ++j) {
     Layer& L = s->layers[j];
     KvView view;
     if ((rc = kv_view(kv, j, &view))) return rc;
+    const QuantArgs* qn = (L.w8 && s->a8.q && skinny && rmsnorm_can_quantize(h)) ? &qnorm : nullptr;
     // input_layernorm (modules.py:162); layer 0 also opens the fp32 residual stream (and is never skipped)
     DLI_MARK(DLI_PROF_RMSNORM);
     if (j == 0 && io) {  // pipeline stage step: flag wait and/or embedding gather inside the entry kernel
       const EntryArgs ea{io->token_ids, io->wait_flag, io->state, io->wait_lag,
                          (unsigned long long)(io->timeout_ms > 0 ? io->timeout_ms : 2000) * 1000000ull};
       rc = launch_rmsnorm_entry(io->token_ids ? io->embed_table : hidden_in, (const __nv_bfloat16*)L.w.g_in, w.xn, w.resid, M, h,
-                                d.eps_input, ea, st);
+                                d.eps_input, ea, st, qn);
       if (rc) return rc;
+      s->a8_ready = qn != nullptr;
     } else if (j == 0 || !DLI_SKIPPED(DLI_PROF_RMSNORM)) {
       rc = launch_rmsnorm(j == 0 ? hidden_in : (const void*)w.resid, j != 0, (const __nv_bfloat16*)L.w.g_in, w.xn,
-                          j == 0 ? w.resid : nullptr, hs ? hs + (size_t)j * M * h : nullptr, M, h, d.eps_input, 1.0f, st);
+                          j == 0 ? w.resid : nullptr, hs ? hs + (size_t)j * M * h : nullptr, M, h, d.eps_input, 1.0f, st, qn);
       if (rc) return rc;
+      s->a8_ready = qn != nullptr;
     }
     // q|k|v projection (modules.py:61-63), RoPE and cache append (modules.py:73-85, cache.py:103-109):
     //   prefill  RoPE + append are the epilogue of the projection GEMM (whole heads per 256-column tile);
@@ -718,7 +727,8 @@ static int span_forward_impl(dli_span* s, const dli_kv_desc* kv, int batch, int 
     DLI_STEP(DLI_PROF_GEMM_O, span_gemm(s, w.attn, L.o, w.resid, h, M, h, qdim, DLI_EPI_ADD_F32, st, nullptr, L.w8 ? &L.o8 : nullptr));
     // post_attention_layernorm of h + h (modules.py:179)
     DLI_STEP(DLI_PROF_RMSNORM, launch_rmsnorm(w.resid, true, (const __nv_bfloat16*)L.w.g_post, w.xn, nullptr, nullptr, M, h,
-                                              d.eps_post, d.post_prescale, st));
+                                              d.eps_post, d.post_prescale, st, qn));
+    s->a8_ready = qn != nullptr && !DLI_SKIPPED(DLI_PROF_RMSNORM);
     // MLP (modules.py:181,182): gate|up with silu(gate) * up as the GEMM epilogue on both paths (64 gate + 64 up weight
     // rows per CTA at decode, 128 + 128 accumulator columns per CTA pair at prefill), then down + residual
     DLI_STEP(DLI_PROF_GEMM_GATE_UP, span_gemm(s, w.xn, L.gu, w.act, inter, M, inter, h, DLI_EPI_SILU_MUL_BF16, st, nullptr, L.w8 ? &L.gu8 : nullptr));

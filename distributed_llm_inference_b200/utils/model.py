@@ -89,18 +89,21 @@ def load_block(model_name: str, layer_ids: List[int], use_quantized: bool = Fals
     return block
 
 
-def convert_to_optimized_block(block: LlamaBlock, quantize: bool = False, threshold: float = 5.0) -> LlamaBlock:
-    """utils/model.py:116-123: move the block to the GPU and, with ``quantize=True``, store every linear weight as
-    row-wise absmax int8 + one fp32 scale per output row -- the weight format of the reference's
-    ``Linear8bitLt(has_fp16_weights=False)`` (utils/model.py:102-108).  The reference converts regardless of the flag
-     and also quantises the ACTIVATIONS vector-wise to int8, with the columns that hold a value above
-    ``threshold`` kept in fp16 (LLM.int8); here activations stay bf16, so there is nothing for ``threshold`` to
-    protect and it is unused -- the result is closer to the unquantised model than the reference's, not identical to
-    it.  ``quantize=False`` keeps the bf16 span (the north star's dtype)."""
+def convert_to_optimized_block(block: LlamaBlock, quantize: bool = False, threshold: float = 5.0,
+                               activations: str = "int8") -> LlamaBlock:
+    """utils/model.py:116-123: move the block to the GPU and, with ``quantize=True``, run its linear layers the way the
+    reference's ``Linear8bitLt(threshold=threshold, has_fp16_weights=False)`` does (utils/model.py:102-108, "LLM.int8"):
+    every weight stored as row-wise absmax int8 + one fp32 scale per output row, and at decode (chunks of <= 128 tokens)
+    the ACTIVATIONS quantised per token row to int8 as well, the entries with ``|x| >= threshold`` kept out of the row's
+    scale in a second int8 plane, the products int8 x int8 -> int32 on the tensor cores (``dli_gemm_i8``).  Longer
+    chunks (prefill) multiply 16-bit activations by the dequantised weights.  ``activations="bf16"`` keeps 16-bit
+    activations everywhere (weight-only int8, ``dli_gemm_w8``): closer to the unquantised model than the reference's
+    mode, and slower at decode.  The reference converts regardless of ``quantize``; here ``quantize=False``
+    keeps the bf16 span (the north star's dtype)."""
     if not torch.cuda.is_available():
         raise NotImplementedError("the B200 span needs a CUDA device" if not quantize else
                                   "Quantization is only supported on CUDA devices")      # utils/model.py:117-118
     block = block.to(torch.device("cuda"))
     if quantize:
-        block.quantize_w8()
+        block.quantize_w8(activations=activations, threshold=threshold)
     return block

@@ -38,7 +38,22 @@ for (n, k) in shapes:
         return e0.elapsed_time(e1) * 1e3 / (reps * nbuf)
 
     us8 = timeit(run_w8)
-    line = f"m={M} n={n:6d} k={k:6d} {'silu' if silu else 'add '} int8 {rows*k/1e6:6.1f} MB {us8:7.2f} us {rows*k/us8/1e3:7.1f} GB/s"
+    # int8 activations (two planes, threshold 5) quantised once; the kind::i8 GEMM alone
+    import ctypes as C
+    nb = _ffi.lib.dli_act_i8_bytes(M, k, 2)
+    abuf = torch.zeros(nb, dtype=torch.uint8, device=dev)
+    ad = _ffi.ActI8()
+    _ffi.check(_ffi.lib.dli_act_i8_carve(abuf.data_ptr(), nb, M, k, 2, C.byref(ad)))
+    _ffi.check(_ffi.lib.dli_quantize_act_i8(x.data_ptr(), k, M, k, 5.0, C.byref(ad), ops.stream()))
+    ad1 = _ffi.ActI8(ad.q, ad.scale, ad.ksum, None, None, None)
+
+    def run_i8(a):
+        for q in qs:
+            _ffi.check(_ffi.lib.dli_gemm_i8(C.byref(a), q.data_ptr(), sc.data_ptr(), out.data_ptr(), n, M, n, k, epi, ops.stream()))
+
+    usi2 = timeit(lambda: run_i8(ad))
+    usi1 = timeit(lambda: run_i8(ad1))
+    line = f"m={M} n={n:6d} k={k:6d} {'silu' if silu else 'add '} int8 {rows*k/1e6:6.1f} MB {us8:7.2f} us {rows*k/us8/1e3:7.1f} GB/s | i8 2 planes {usi2:7.2f} us {rows*k/usi2/1e3:7.1f} GB/s, 1 plane {usi1:7.2f} us"
     if not only_w8:
         ws = [torch.randn(rows, k, device=dev, dtype=torch.bfloat16) for _ in range(nbuf)]
         us16 = timeit(lambda: [ops.gemm(x, w, epi, out=out) for w in ws])

@@ -2,6 +2,7 @@
 `ncu --profile-from-start off`.   python tests/prof_step.py decode | decode_w8 | stage
   decode     32 layers, batch 16, context 512: LlamaBlock.graphed_decode (dli_span_decode_step)
   decode_w8  the same with row-wise int8 weights (gemm_w8_kernel)
+  decode_a8  int8 weights and int8 activations (gemm_i8_kernel, LLM.int8)
   stage      8 layers as a one-GPU token-ring stage step (dli_stage_decode_step: embedding gather + flag wait at entry,
              final norm -> lm_head -> argmax -> flag release at exit)"""
 import os
@@ -25,6 +26,8 @@ n_layers = 8 if mode == "stage" else 32
 blk = build_span(shape, list(range(n_layers)), dev)
 if mode == "decode_w8":
     blk.quantize_w8()
+if mode == "decode_a8":
+    blk.quantize_w8(activations="int8", threshold=5.0)
 cache = PartialLlamaSinkCache(1 << 20, 4, capacity_tokens=2 * B * (T + 64) + 2048)
 blk("g", syn.make_hidden(shape, B, T, seed=1, device=dev), past_key_value=cache)
 x = syn.make_hidden(shape, B, 1, seed=2, device=dev)

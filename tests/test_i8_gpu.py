@@ -137,7 +137,9 @@ def test_int8_activation_span_matches_oracle(shape_name, B, L1, L2, threshold):
 
     shp = syn.SHAPES[shape_name]
     W = syn.make_span_weights(shp, [0, 1, 2], norm_jitter=0.1)
-    blk = gpu_make_span(shp, W, "eager", "float").to(DEV).quantize_w8(activations="int8", threshold=threshold)
+    from distributed_llm_inference_b200.utils.model import convert_to_optimized_block
+
+    blk = convert_to_optimized_block(gpu_make_span(shp, W, "eager", "float"), quantize=True, threshold=threshold)   # the reference's call
     osp = oracle_make_span(shp, _dequantised_weights(W), "eager", "float")
     gc, oc = PartialLlamaSinkCache(4096, 4, capacity_tokens=4096), so.SinkCacheOracle(4096, 4)
     so.LINEAR = _act_quant_linear(threshold)

@@ -96,7 +96,7 @@ def _dequantised_weights(W):
 def test_quantised_span_matches_oracle_on_dequantised_weights(shape_name, B, L1, L2):
     shp = syn.SHAPES[shape_name]
     W = syn.make_span_weights(shp, [0, 1, 2], norm_jitter=0.1)
-    blk = convert_to_optimized_block(gpu_make_span(shp, W, "eager", "float"), quantize=True)
+    blk = convert_to_optimized_block(gpu_make_span(shp, W, "eager", "float"), quantize=True, activations="bf16")
     assert all(layer.w8 is not None and layer.self_attn.q_proj.weight.numel() == 0 for layer in blk.layers)
     osp = oracle_make_span(shp, _dequantised_weights(W), "eager", "float")
     gc, oc = PartialLlamaSinkCache(4096, 4, capacity_tokens=4096), so.SinkCacheOracle(4096, 4)
