@@ -41,7 +41,7 @@ constexpr int NORM_CHUNKS = 4;
 // previous stage fills over NVLink -- thread 0 waits for the producer's flag after the dependency wait, the rows are
 // then read with coherent loads -- or rows of an embedding table picked by device-resident token ids (stage 0 of a
 // token ring; the ids are what the flag guards).
-template <bool F32IN, bool ENTRY = false>
+template <bool F32IN, bool ENTRY = false, bool QUANT = false>
 __global__ void __launch_bounds__(NORM_THREADS) rmsnorm_kernel(const void* __restrict__ x, const __nv_bfloat16* __restrict__ w,
                                                                __nv_bfloat16* __restrict__ y, float* __restrict__ resid_out,
                                                                __nv_bfloat16* __restrict__ copy_out, int h, float eps,
@@ -114,7 +114,7 @@ __global__ void __launch_bounds__(NORM_THREADS) rmsnorm_kernel(const void* __res
         *reinterpret_cast<uint4*>(y + base + i) = make_uint4(ob[c][0], ob[c][1], ob[c][2], ob[c][3]);
       }
     }
-    if (qa.d.q != nullptr) {
+    if (QUANT) {   // its own instantiation: the 16-bit path runs the kernel without this tail
       // the row also leaves quantised for the int8 x int8 GEMM that follows (what quantize_act_i8_kernel would make of y)
       const float thr = (qa.d.q2 != nullptr && qa.threshold > 0.f) ? qa.threshold : INFINITY;
       float mx = 0.f, mo = 0.f;
@@ -221,9 +221,10 @@ int launch_rmsnorm(const void* x, bool x_is_f32, const __nv_bfloat16* w, __nv_bf
   DLI_REQUIRE(x && w && y, "dli_rmsnorm: null pointer");
   DLI_REQUIRE(rows > 0 && h > 0 && h % 8 == 0, "dli_rmsnorm: rows=%d h=%d (h must be a positive multiple of 8)", rows, h);
   DLI_REQUIRE(!quant || rmsnorm_can_quantize(h), "rmsnorm with quantised output: h = %d not supported", h);
-  return launch_kernel("rmsnorm_kernel", x_is_f32 ? rmsnorm_kernel<true> : rmsnorm_kernel<false>, dim3(rows),
-                       dim3(NORM_THREADS), 0, st, x, w, y, resid_out, copy_out, h, eps, pre_scale, EntryArgs{},
-                       quant ? *quant : QuantArgs{});
+  auto kern = quant ? (x_is_f32 ? rmsnorm_kernel<true, false, true> : rmsnorm_kernel<false, false, true>)
+                    : (x_is_f32 ? rmsnorm_kernel<true> : rmsnorm_kernel<false>);
+  return launch_kernel("rmsnorm_kernel", kern, dim3(rows), dim3(NORM_THREADS), 0, st, x, w, y, resid_out, copy_out, h, eps, pre_scale,
+                       EntryArgs{}, quant ? *quant : QuantArgs{});
 }
 
 int launch_rmsnorm_entry(const void* x, const __nv_bfloat16* w, __nv_bfloat16* y, float* resid_out, int rows, int h, float eps,
@@ -232,8 +233,9 @@ int launch_rmsnorm_entry(const void* x, const __nv_bfloat16* w, __nv_bfloat16* y
   DLI_REQUIRE(rows > 0 && h > 0 && h % 8 == 0 && h <= NORM_THREADS * 8 * NORM_CHUNKS,
               "stage step entry: rows=%d h=%d (h must be a multiple of 8, at most %d)", rows, h, NORM_THREADS * 8 * NORM_CHUNKS);
   DLI_REQUIRE(!ea.wait_flag || ea.state, "stage step entry: a wait flag needs the step state");
-  return launch_kernel("rmsnorm_kernel<entry>", rmsnorm_kernel<false, true>, dim3(rows), dim3(NORM_THREADS), 0, st, x, w, y,
-                       resid_out, (__nv_bfloat16*)nullptr, h, eps, 1.0f, ea, quant ? *quant : QuantArgs{});
+  return launch_kernel("rmsnorm_kernel<entry>", quant ? rmsnorm_kernel<false, true, true> : rmsnorm_kernel<false, true>, dim3(rows),
+                       dim3(NORM_THREADS), 0, st, x, w, y, resid_out, (__nv_bfloat16*)nullptr, h, eps, 1.0f, ea,
+                       quant ? *quant : QuantArgs{});
 }
 
 // ---------------------------------------------------------------------------------------------------
