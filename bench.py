@@ -916,6 +916,8 @@ def run_ours(args):
             configs["c4_i_70b_8x10_1x32"] = run_workload(ctx, "70b", 32, 512, 1, None, Kc, Wc)
             configs["c4_ii_70b_8x10_8x4"] = run_workload(ctx, "70b", 4, 512, 8, None, Kc, Wc)
             configs["c4_iii_70b_8x10_8x32"] = run_workload(ctx, "70b", 32, 512, 8, None, Kc, Wc, want_e2e=True)
+            # the same schedule in the reference's int8 mode (LLM.int8: int8 weights, per-token int8 activations)
+            configs["c4_iii_70b_8x10_8x32_llm_int8"] = run_workload(ctx, "70b", 32, 512, 8, None, Kc, Wc, w8=True, a8=True)
         if world in (4, 8):
             configs[f"c5_70b_prefill_8192_{world}_stages"] = run_workload(ctx, "70b", 1, 8192, 1, None, 4, 3, prefill_chunk=PREFILL_CHUNK_TOKENS)
     if rank == 0:

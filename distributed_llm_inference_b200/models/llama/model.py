@@ -188,7 +188,8 @@ class LlamaBlock(nn.Module):
         """Row-wise int8 weights for every layer of the span (see ``OptimizedLlamaDecoderLayer.quantize_w8``).
         ``activations="int8"``: decode steps (chunks of <= 128 tokens) also quantise the ACTIVATIONS per token row and
         multiply int8 x int8 on the tensor cores, entries with ``|x| >= threshold`` kept in 16 bits -- the arithmetic of
-        the reference's ``Linear8bitLt(threshold=...)`` (utils/model.py:93-123); ``"bf16"`` keeps 16-bit activations."""
+        the reference's ``Linear8bitLt(threshold=...)`` (utils/model.py:93-123); ``"bf16"`` keeps 16-bit activations.
+        Decode graphs captured before a change of mode keep the mode they were captured in: capture them again."""
         if activations not in ("bf16", "int8"):
             raise ValueError("activations must be 'bf16' or 'int8'")
         for layer in self.layers:
