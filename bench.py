@@ -530,8 +530,8 @@ def run_workload(ctx: Ctx, model: str, batch: int, prompt: int, n_mb: int, layer
         solo = [round(t.item(), 4) for t in allms]
         del gs
         cache.close("solo")
+    sampler = ClockSampler(ctx.local)   # NVML set-up takes milliseconds and differs between ranks: outside the bracket
     ctx.barrier()
-    sampler = ClockSampler(ctx.local)
     sampler.start()
     evs = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
     evs[0].record()
