@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Per-kernel SASS evidence for libdli_b200.so: counts of the Blackwell mnemonics that prove tcgen05 / TMEM / TMA use
-(UTCHMMA = tcgen05.mma, LDTM / STTM = tcgen05.ld / .st, UTMALDG = TMA tensor load, UBLKCP = bulk copy, UTCBAR =
+(UTCHMMA = tcgen05.mma kind::f16, UTCIMMA = kind::i8, LDTM / STTM = tcgen05.ld / .st, UTMALDG = TMA tensor load, UBLKCP = bulk copy, UTCBAR =
 tcgen05.commit, HMMA = mma.sync) plus registers and shared memory from the ptxas logs of the build.
 
     python profiles/sass_summary.py > profiles/r02_sass_summary.txt     (no GPU needed)
@@ -13,7 +13,7 @@ import subprocess
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, "distributed_llm_inference_b200", "csrc")
-MNEMONICS = ("UTCHMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UBLKCP", "HMMA", "LDSM", "RED", "MUFU.EX2", "ACQBULK")
+MNEMONICS = ("UTCHMMA", "UTCIMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UBLKCP", "HMMA", "LDSM", "RED", "MUFU.EX2", "ACQBULK")
 
 
 def demangle(names):
