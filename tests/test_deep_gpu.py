@@ -11,7 +11,6 @@ Also here: the bound on run-to-run differences.  Split-K partial sums and residu
 ``red.global.add.f32`` whose order varies between runs, so outputs are reproducible to fp32 rounding of the sums, not
 bit for bit; the test runs the same prefill + decode steps on two generations and bounds what that costs.
 """
-import numpy as np
 import pytest
 import torch
 

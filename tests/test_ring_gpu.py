@@ -3,7 +3,6 @@ itself -- the same entry kernel (flag wait / embedding gather), exit kernel (sto
 (final RMSNorm -> lm_head -> argmax) and round graph that run between GPUs, checked against the plain span path and the
 sequential client.  The multi-GPU run of the same protocol is checked by ``bench.py``'s ``pipeline_parity`` record
 (N-stage output against the same layers as one span and against the oracle) on every N > 1 launch."""
-import ctypes as C
 
 import pytest
 import torch

@@ -3,7 +3,6 @@ utils/model.py:93-123): quantisation kernel bit for bit against the oracle's res
 oracle's arithmetic, and a quantised span -- short and long prefill, eager and graphed decode -- against the fp32 oracle
 span run on the dequantised weights.  (The oracle for this mode is restated from bitsandbytes' published algorithm and
 is unpinned: oracle/quant_oracle.py.)"""
-import math
 
 import pytest
 import torch
