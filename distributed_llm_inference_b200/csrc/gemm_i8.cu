@@ -299,6 +299,7 @@ int launch_gemm_i8_planned(const GemmPlan& g, const CUtensorMap& tmap_x, const C
                            cudaStream_t st) {
   if (!g.swap) return fail(DLI_ERR_UNSUPPORTED, "the int8 x int8 GEMM is the decode kernel: m = %d > 128", m);
   if (n % 4) return fail(DLI_ERR_ARG, "dli_gemm_i8: n = %d must be a multiple of 4", n);
+  if (g.k_blocks > 512) return fail(DLI_ERR_UNSUPPORTED, "dli_gemm_i8: k > 65536 could overflow the int32 accumulators (127 * 255 * k)");
   const int planes = x.q2 ? 2 : 1;
   I8Params p{};
   p.out = out;
